@@ -1,0 +1,174 @@
+/*
+ * wgs_rasterizer.h — C ABI of the B200-native differentiable Gaussian rasterizer with
+ * camera-pose gradients (libwgs_rasterizer.so, sm_100a only).
+ *
+ * This is the drop-in boundary for ONE path of yuhang1008/WildGS-SLAM-Blackwell: the
+ * native layer under `diff_gaussian_rasterization` (reference:
+ * thirdparty/diff-gaussian-rasterization-w-pose, "RAST/" below).  Each entry point names
+ * the reference interface it replaces.  No C++/torch types cross the boundary: plain
+ * pointers (DEVICE pointers unless the field says host), sizes and scalars.  All work is
+ * enqueued on the caller's stream; kernels never allocate.
+ *
+ * Memory is caller-owned (the Python host keeps it in torch uint8 tensors so autograd
+ * lifetime rules match RAST/rasterize_points.cu:27-33,69-82): query sizes with
+ * wgs_workspace_sizes() and pass the five workspaces in.  Every workspace pointer must be
+ * 256-byte aligned.
+ */
+#ifndef WGS_RASTERIZER_H_
+#define WGS_RASTERIZER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WGS_ABI_VERSION 3
+
+/* status codes (negative = error) */
+#define WGS_OK 0
+#define WGS_ERR_INVALID_ARGUMENT (-1) /* bad shape/null pointer; reference: AT_ERROR, rasterize_points.cu:58-60 */
+#define WGS_ERR_CUDA (-2)             /* a CUDA call failed; see wgs_last_error() */
+#define WGS_ERR_CAPACITY (-3)         /* num_rendered > instance capacity; *num_rendered holds the needed size; grow `binning` and call again */
+#define WGS_ERR_NO_COLOR_SOURCE (-4)  /* neither sh nor colors_precomp; reference: std::runtime_error, rasterizer_impl.cu:245-248 */
+#define WGS_ERR_ARCH (-5)             /* device is not sm_100 */
+
+typedef struct WgsContext WgsContext; /* per-device: pinned readback word, event, SM count */
+
+/* Workspace byte sizes for a problem of P Gaussians, W x H pixels and room for
+ * `capacity` (Gaussian,tile) instances.  Replaces required<GeometryState/BinningState/
+ * ImageState>() (RAST/cuda_rasterizer/rasterizer_impl.h:64-72, rasterizer_impl.cu:155-194).
+ * geom: 48 B/Gaussian; tile: 16 B/tile; binning: 56 B/instance (+20 with keys export);
+ * image: 8 B/pixel; grad: 48 B/Gaussian + pose partials. */
+typedef struct WgsWorkspaceSizes {
+  size_t geom_bytes;
+  size_t tile_bytes;
+  size_t binning_bytes;
+  size_t image_bytes;
+  size_t grad_bytes;
+} WgsWorkspaceSizes;
+
+/* Arguments of the forward pass.  Replaces RasterizeGaussiansCUDA
+ * (RAST/rasterize_points.cu:35-122) + CudaRasterizer::Rasterizer::forward
+ * (RAST/cuda_rasterizer/rasterizer.h:32-58, rasterizer_impl.cu:198-344).
+ * A null pointer means "absent", as the reference's empty tensors do. */
+typedef struct WgsForwardArgs {
+  int32_t P;          /* number of Gaussians (0 is legal: outputs are background-only) */
+  int32_t sh_degree;  /* active SH degree D (0..3) */
+  int32_t M;          /* SH coefficients stored per Gaussian (sh is (P,M,3)); 0 if sh absent */
+  int32_t width, height;
+  float tanfovx, tanfovy;
+  float scale_modifier;
+  int32_t prefiltered; /* reference traps on a culled point when set (auxiliary.h:154-161); we set radii=0 and report via status word */
+  int32_t debug;       /* synchronise + check after every stage (CHECK_CUDA, auxiliary.h:166-173) */
+  /* inputs (device) */
+  const float* background;     /* (3,) */
+  const float* means3D;        /* (P,3) */
+  const float* sh;             /* (P,M,3) or null */
+  const float* colors_precomp; /* (P,3) or null */
+  const float* opacities;      /* (P,1) */
+  const float* scales;         /* (P,3) or null */
+  const float* rotations;      /* (P,4) w,x,y,z; NOT re-normalised (forward.cu:129) or null */
+  const float* cov3D_precomp;  /* (P,6) or null */
+  const float* viewmatrix;     /* (4,4) = W2C^T, i.e. column-major W2C */
+  const float* projmatrix;     /* (4,4) = viewmatrix @ P^T */
+  const float* campos;         /* (3,) */
+  /* outputs (device, caller-allocated, need NOT be pre-zeroed) */
+  float* out_color;   /* (3,H,W) planar */
+  float* out_depth;   /* (1,H,W) */
+  float* out_opacity; /* (1,H,W) */
+  int32_t* radii;     /* (P,) */
+  int32_t* n_touched; /* (P,) */
+  /* workspaces (device) */
+  void* geom;
+  void* tile;
+  void* binning;
+  void* image;
+  int64_t capacity;   /* instance capacity the binning workspace was sized for */
+  int32_t export_keys; /* binning workspace has room for, and kernels write, reference-format point_list_keys / point_list (parity tests) */
+} WgsForwardArgs;
+
+/* Arguments of the backward pass.  Replaces RasterizeGaussiansBackwardCUDA
+ * (RAST/rasterize_points.cu:124-211) + CudaRasterizer::Rasterizer::backward
+ * (rasterizer.h:60-91, rasterizer_impl.cu:348-455) + the torch.sum over dL_dtau in
+ * RAST/diff_gaussian_rasterization/__init__.py:152-154 (folded into the kernel). */
+typedef struct WgsBackwardArgs {
+  int32_t P, sh_degree, M, width, height;
+  float tanfovx, tanfovy, scale_modifier;
+  int32_t debug;
+  const float* background;
+  const float* means3D;
+  const float* sh;
+  const float* colors_precomp;
+  const float* scales;
+  const float* rotations;
+  const float* cov3D_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* projmatrix_raw; /* (4,4) = P^T */
+  const float* campos;
+  const int32_t* radii;        /* forward output */
+  /* cotangents (device); dL_dopacity-image is ignored like the reference (__init__.py:108) */
+  const float* dL_dout_color;  /* (3,H,W) */
+  const float* dL_dout_depth;  /* (1,H,W) */
+  /* gradient outputs (device, caller-allocated, need NOT be pre-zeroed; any may be null) */
+  float* dL_dmeans3D;   /* (P,3) */
+  float* dL_dmeans2D;   /* (P,3), z = 0 */
+  float* dL_dsh;        /* (P,M,3)   (sh path) */
+  float* dL_dcolors;    /* (P,3)     (colors_precomp path) */
+  float* dL_dopacity;   /* (P,1) */
+  float* dL_dscales;    /* (P,3) */
+  float* dL_drotations; /* (P,4) */
+  float* dL_dcov3D;     /* (P,6)     (cov3D_precomp path) */
+  float* dL_dtau;       /* (6,) rho then theta — already summed over Gaussians */
+  /* workspaces written by the matching forward */
+  const void* geom;
+  const void* tile;
+  const void* binning;
+  const void* image;
+  void* grad;           /* accumulators; must be zero before the FIRST backward that uses it (kernels re-zero it) */
+  int64_t capacity;
+} WgsBackwardArgs;
+
+/* library / device */
+int wgs_abi_version(void);
+const char* wgs_last_error(void);
+WgsContext* wgs_context_create(int device);  /* null on failure (see wgs_last_error) */
+void wgs_context_destroy(WgsContext* ctx);
+
+int wgs_workspace_sizes(int32_t P, int32_t width, int32_t height, int64_t capacity,
+                        int32_t export_keys, WgsWorkspaceSizes* out);
+
+/* Forward.  On return *num_rendered (host) holds R = number of (Gaussian,tile) instances
+ * (the reference's return value, rasterizer_impl.cu:343).  The only host wait is on the
+ * 4-byte R readback, issued after all kernels are already enqueued. */
+int wgs_forward(WgsContext* ctx, const WgsForwardArgs* args, void* cuda_stream,
+                int64_t* num_rendered);
+
+int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* args, void* cuda_stream);
+
+/* Replaces markVisible (RAST/rasterize_points.cu:213-232, rasterizer_impl.cu:54-66,141-153):
+ * present[i] = view-space z > 0.2.  `present` is (P,) bytes (torch.bool). */
+int wgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, void* cuda_stream);
+
+/* Parity/debug export of the binning state in the REFERENCE's format
+ * (BinningState / ImageState, rasterizer_impl.h:42-62): sorted 64-bit keys
+ * tile<<32|depth_bits, sorted Gaussian ids, per-tile [start,end) with (0,0) for empty tiles,
+ * and the per-pixel n_contrib / final_T.  Requires a forward run with export_keys=1.
+ * Destinations are device pointers; any may be null. */
+int wgs_export_binning(const WgsForwardArgs* args, int64_t num_rendered,
+                       uint64_t* point_list_keys, uint32_t* point_list, uint32_t* ranges,
+                       uint32_t* n_contrib, float* final_T, void* cuda_stream);
+
+/* Parity/debug export of the per-Gaussian forward state in the reference's GeometryState
+ * terms (rasterizer_impl.h:21-40): depths (P), means2D (2P), conic_opacity (4P), rgb (3P),
+ * clamped (3P bytes).  Entries of culled Gaussians (radii==0) are written as 0. */
+int wgs_export_geometry(const WgsForwardArgs* args, float* depths, float* means2D,
+                        float* conic_opacity, float* rgb, uint8_t* clamped, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WGS_RASTERIZER_H_ */
