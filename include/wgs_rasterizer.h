@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define WGS_ABI_VERSION 3
+#define WGS_ABI_VERSION 4
 
 /* status codes (negative = error) */
 #define WGS_OK 0
@@ -39,8 +39,9 @@ typedef struct WgsContext WgsContext; /* per-device: pinned readback word, event
 /* Workspace byte sizes for a problem of P Gaussians, W x H pixels and room for
  * `capacity` (Gaussian,tile) instances.  Replaces required<GeometryState/BinningState/
  * ImageState>() (RAST/cuda_rasterizer/rasterizer_impl.h:64-72, rasterizer_impl.cu:155-194).
- * geom: 48 B/Gaussian; tile: 16 B/tile; binning: 56 B/instance (+20 with keys export);
- * image: 8 B/pixel; grad: 48 B/Gaussian + pose partials. */
+ * geom: 57 B/Gaussian; tile: 20 B/tile; binning: 8 B/instance; image: 8 B/pixel;
+ * grad: 48 B/Gaussian + pose partials (the reference: 79 B/Gaussian, 24 B/instance + CUB
+ * temporaries, 16 B/pixel, and eleven zero-filled gradient tensors per backward). */
 typedef struct WgsWorkspaceSizes {
   size_t geom_bytes;
   size_t tile_bytes;
@@ -86,7 +87,6 @@ typedef struct WgsForwardArgs {
   void* binning;
   void* image;
   int64_t capacity;   /* instance capacity the binning workspace was sized for */
-  int32_t export_keys; /* binning workspace has room for, and kernels write, reference-format point_list_keys / point_list (parity tests) */
 } WgsForwardArgs;
 
 /* Arguments of the backward pass.  Replaces RasterizeGaussiansBackwardCUDA
@@ -138,11 +138,14 @@ WgsContext* wgs_context_create(int device);  /* null on failure (see wgs_last_er
 void wgs_context_destroy(WgsContext* ctx);
 
 int wgs_workspace_sizes(int32_t P, int32_t width, int32_t height, int64_t capacity,
-                        int32_t export_keys, WgsWorkspaceSizes* out);
+                        WgsWorkspaceSizes* out);
 
 /* Forward.  On return *num_rendered (host) holds R = number of (Gaussian,tile) instances
  * (the reference's return value, rasterizer_impl.cu:343).  The only host wait is on the
- * 4-byte R readback, issued after all kernels are already enqueued. */
+ * 4-byte R word (written to pinned memory by the tile-scan kernel), and it happens after all
+ * kernels of the forward are already enqueued.  The `tile` workspace needs no initialisation.
+ * Returns WGS_ERR_CAPACITY (outputs invalid, nothing written out of bounds) when R exceeds
+ * args->capacity; the caller grows `binning` to *num_rendered entries and calls again. */
 int wgs_forward(WgsContext* ctx, const WgsForwardArgs* args, void* cuda_stream,
                 int64_t* num_rendered);
 
@@ -156,8 +159,8 @@ int wgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
 /* Parity/debug export of the binning state in the REFERENCE's format
  * (BinningState / ImageState, rasterizer_impl.h:42-62): sorted 64-bit keys
  * tile<<32|depth_bits, sorted Gaussian ids, per-tile [start,end) with (0,0) for empty tiles,
- * and the per-pixel n_contrib / final_T.  Requires a forward run with export_keys=1.
- * Destinations are device pointers; any may be null. */
+ * and the per-pixel n_contrib / final_T, reconstructed from the state of the forward that
+ * `args` describes.  Destinations are device pointers; any may be null. */
 int wgs_export_binning(const WgsForwardArgs* args, int64_t num_rendered,
                        uint64_t* point_list_keys, uint32_t* point_list, uint32_t* ranges,
                        uint32_t* n_contrib, float* final_T, void* cuda_stream);

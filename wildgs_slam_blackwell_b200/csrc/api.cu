@@ -1,0 +1,284 @@
+// C-ABI of libwgs_rasterizer.so (see include/wgs_rasterizer.h): argument checks, workspace
+// carving and stage sequencing.  Replaces RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA
+// (rasterize_points.cu:35-211) and CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+// (rasterizer_impl.cu:141-455).
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/wgs_rasterizer.h"
+#include "common.cuh"
+#include "kernels.h"
+
+using namespace wgs;
+
+struct WgsContext {
+    int device = 0;
+    int num_sms = 0;
+    unsigned int* host_R = nullptr;  // pinned + mapped
+    unsigned int* dev_R = nullptr;   // device alias of host_R
+    cudaEvent_t ev_R = nullptr;
+};
+
+namespace {
+thread_local char g_err[512] = "";
+void set_err(const char* what, cudaError_t e) {
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, e == cudaSuccess ? "" : cudaGetErrorString(e));
+}
+#define CK(call)                                  \
+    do {                                          \
+        cudaError_t e_ = (call);                  \
+        if (e_ != cudaSuccess) {                  \
+            set_err(#call, e_);                   \
+            return WGS_ERR_CUDA;                  \
+        }                                         \
+    } while (0)
+// CHECK_CUDA(A, debug) of the reference (auxiliary.h:166-173)
+#define STAGE(debug, stream, name)                                 \
+    do {                                                           \
+        cudaError_t e_ = cudaGetLastError();                       \
+        if (e_ == cudaSuccess && (debug)) e_ = cudaStreamSynchronize(stream); \
+        if (e_ != cudaSuccess) {                                   \
+            set_err(name, e_);                                     \
+            return WGS_ERR_CUDA;                                   \
+        }                                                          \
+    } while (0)
+
+bool aligned256(const void* p) { return ((uintptr_t)p & 255u) == 0; }
+}  // namespace
+
+extern "C" {
+
+int wgs_abi_version(void) { return WGS_ABI_VERSION; }
+const char* wgs_last_error(void) { return g_err; }
+
+WgsContext* wgs_context_create(int device) {
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+        set_err("wgs_context_create: no such CUDA device", cudaGetLastError());
+        return nullptr;
+    }
+    if (prop.major != 10) {
+        snprintf(g_err, sizeof(g_err), "wgs_context_create: device is sm_%d%d, this library is sm_100a only",
+                 prop.major, prop.minor);
+        return nullptr;
+    }
+    WgsContext* c = new WgsContext();
+    c->device = device;
+    c->num_sms = prop.multiProcessorCount;
+    cudaError_t e = cudaHostAlloc((void**)&c->host_R, 64, cudaHostAllocMapped);
+    if (e == cudaSuccess) e = cudaHostGetDevicePointer((void**)&c->dev_R, c->host_R, 0);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_R, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = (cudaError_t)configure_binning();
+    if (e != cudaSuccess) {
+        set_err("wgs_context_create", e);
+        delete c;
+        return nullptr;
+    }
+    return c;
+}
+
+void wgs_context_destroy(WgsContext* c) {
+    if (!c) return;
+    if (c->ev_R) cudaEventDestroy(c->ev_R);
+    if (c->host_R) cudaFreeHost(c->host_R);
+    delete c;
+}
+
+int wgs_workspace_sizes(int32_t P, int32_t width, int32_t height, int64_t capacity, WgsWorkspaceSizes* out) {
+    if (!out || P < 0 || width <= 0 || height <= 0 || capacity < 0) {
+        set_err("wgs_workspace_sizes: invalid argument", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    const size_t tiles = (size_t)((width + 15) / 16) * ((height + 15) / 16);
+    out->geom_bytes = geom_bytes((size_t)(P > 0 ? P : 1));
+    out->tile_bytes = tile_bytes(tiles);
+    out->binning_bytes = align_up((size_t)(capacity > 0 ? capacity : 1) * 8);
+    out->image_bytes = image_bytes((size_t)width * height);
+    out->grad_bytes = grad_bytes((size_t)(P > 0 ? P : 1));
+    return WGS_OK;
+}
+
+int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int64_t* num_rendered) {
+    if (!ctx || !a || !num_rendered) { set_err("wgs_forward: null argument", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    *num_rendered = 0;
+    if (a->P < 0 || a->width <= 0 || a->height <= 0 || a->width > 65535 * 16 || a->height > 65535 * 16 ||
+        a->sh_degree < 0 || a->sh_degree > 3) {
+        set_err("wgs_forward: bad P / image size / sh_degree", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    if (!a->background || !a->viewmatrix || !a->projmatrix || !a->out_color || !a->out_depth || !a->out_opacity ||
+        !a->tile || !a->image || !aligned256(a->tile) || !aligned256(a->image)) {
+        set_err("wgs_forward: null/misaligned required pointer", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    if (a->P > 0) {
+        if (!a->means3D || !a->opacities || !a->radii || !a->n_touched || !a->geom || !a->binning || !a->campos ||
+            !aligned256(a->geom) || !aligned256(a->binning)) {
+            set_err("wgs_forward: null/misaligned required pointer", cudaSuccess);
+            return WGS_ERR_INVALID_ARGUMENT;
+        }
+        if (!a->sh && !a->colors_precomp) {
+            set_err("wgs_forward: provide sh or colors_precomp", cudaSuccess);
+            return WGS_ERR_NO_COLOR_SOURCE;
+        }
+        if (a->sh && !a->colors_precomp && a->M < (a->sh_degree + 1) * (a->sh_degree + 1)) {
+            set_err("wgs_forward: sh has fewer coefficients than sh_degree needs", cudaSuccess);
+            return WGS_ERR_INVALID_ARGUMENT;
+        }
+        if (!a->cov3D_precomp && (!a->scales || !a->rotations)) {
+            set_err("wgs_forward: provide scales+rotations or cov3D_precomp", cudaSuccess);
+            return WGS_ERR_INVALID_ARGUMENT;
+        }
+    }
+    const int gx = (a->width + 15) / 16, gy = (a->height + 15) / 16, tiles = gx * gy;
+    const size_t Pn = (size_t)(a->P > 0 ? a->P : 1);
+    GeomView geom = geom_view(a->geom, Pn);
+    TileView tile = tile_view(a->tile, (size_t)tiles);
+    ImageView image = image_view(a->image, (size_t)a->width * a->height);
+
+    CK(cudaMemsetAsync(tile.count, 0, tile_clear_bytes((size_t)tiles), s));
+
+    PreFwdParams pp;
+    pp.P = a->P; pp.D = a->sh_degree; pp.M = a->M; pp.W = a->width; pp.H = a->height; pp.gx = gx; pp.gy = gy;
+    pp.prefiltered = a->prefiltered;
+    pp.tanfovx = a->tanfovx; pp.tanfovy = a->tanfovy;
+    pp.focal_y = a->height / (2.0f * a->tanfovy);  // rasterizer_impl.cu:225-226
+    pp.focal_x = a->width / (2.0f * a->tanfovx);
+    pp.scale_modifier = a->scale_modifier;
+    pp.means3D = a->means3D; pp.sh = a->colors_precomp ? nullptr : a->sh; pp.colors_precomp = a->colors_precomp;
+    pp.opacities = a->opacities; pp.scales = a->scales; pp.rotations = a->rotations; pp.cov3D_precomp = a->cov3D_precomp;
+    pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
+    pp.radii = a->radii; pp.n_touched = a->n_touched; pp.geom = geom; pp.tile = tile;
+    launch_preprocess_fwd(pp, s);
+    STAGE(a->debug, s, "preprocess_fwd");
+
+    BinParams bp;
+    bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.capacity = a->capacity;
+    bp.geom = geom; bp.tile = tile; bp.bucket = (unsigned long long*)a->binning; bp.host_R = ctx->dev_R;
+    launch_tile_scan(bp, s);
+    CK(cudaEventRecord(ctx->ev_R, s));
+    STAGE(a->debug, s, "tile_scan");
+    launch_binning(bp, ctx->num_sms, s);
+    STAGE(a->debug, s, "binning");
+
+    RenderFwdParams rp;
+    rp.W = a->width; rp.H = a->height; rp.gx = gx; rp.gy = gy; rp.bg = a->background;
+    rp.geom = geom; rp.tile = tile; rp.image = image; rp.bucket = bp.bucket;
+    rp.out_color = a->out_color; rp.out_depth = a->out_depth; rp.out_opacity = a->out_opacity;
+    rp.n_touched = a->n_touched;
+    launch_render_fwd(rp, s);
+    STAGE(a->debug, s, "render_fwd");
+
+    // Everything is enqueued; now wait for R only (the GPU keeps running the later stages).
+    CK(cudaEventSynchronize(ctx->ev_R));
+    const int64_t R = (int64_t)*(volatile unsigned int*)ctx->host_R;
+    *num_rendered = R;
+    if (R > a->capacity) {
+        snprintf(g_err, sizeof(g_err), "wgs_forward: %lld instances exceed capacity %lld", (long long)R,
+                 (long long)a->capacity);
+        return WGS_ERR_CAPACITY;
+    }
+    return WGS_OK;
+}
+
+int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
+    if (!ctx || !a) { set_err("wgs_backward: null argument", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    if (a->P < 0 || a->width <= 0 || a->height <= 0) {
+        set_err("wgs_backward: bad P / image size", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    if (a->P == 0) {
+        if (a->dL_dtau) CK(cudaMemsetAsync(a->dL_dtau, 0, 6 * sizeof(float), s));
+        return WGS_OK;
+    }
+    if (!a->background || !a->means3D || !a->viewmatrix || !a->projmatrix || !a->projmatrix_raw || !a->campos ||
+        !a->radii || !a->dL_dout_color || !a->dL_dout_depth || !a->geom || !a->tile || !a->binning || !a->image ||
+        !a->grad || !aligned256(a->grad)) {
+        set_err("wgs_backward: null/misaligned required pointer", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    if (!a->cov3D_precomp && (!a->scales || !a->rotations)) {
+        set_err("wgs_backward: provide scales+rotations or cov3D_precomp", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    const bool use_sh = a->sh && !a->colors_precomp;
+    if (use_sh && !a->dL_dsh) { set_err("wgs_backward: dL_dsh is required on the SH path", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    const int gx = (a->width + 15) / 16, gy = (a->height + 15) / 16, tiles = gx * gy;
+    GeomView geom = geom_view(const_cast<void*>(a->geom), (size_t)a->P);
+    TileView tile = tile_view(const_cast<void*>(a->tile), (size_t)tiles);
+    ImageView image = image_view(const_cast<void*>(a->image), (size_t)a->width * a->height);
+    GradView grad = grad_view(a->grad, (size_t)a->P);
+
+    RenderBwdParams rb;
+    rb.W = a->width; rb.H = a->height; rb.gx = gx; rb.gy = gy; rb.bg = a->background;
+    rb.geom = geom; rb.tile = tile; rb.image = image; rb.bucket = (const unsigned long long*)a->binning;
+    rb.dL_dcolor = a->dL_dout_color; rb.dL_ddepth = a->dL_dout_depth; rb.grad = grad;
+    launch_render_bwd(rb, s);
+    STAGE(a->debug, s, "render_bwd");
+
+    PreBwdParams pb;
+    pb.P = a->P; pb.D = a->sh_degree; pb.M = a->M; pb.W = a->width; pb.H = a->height;
+    pb.tanfovx = a->tanfovx; pb.tanfovy = a->tanfovy;
+    pb.focal_y = a->height / (2.0f * a->tanfovy);
+    pb.focal_x = a->width / (2.0f * a->tanfovx);
+    pb.scale_modifier = a->scale_modifier;
+    pb.means3D = a->means3D; pb.sh = use_sh ? a->sh : nullptr; pb.colors_precomp = a->colors_precomp;
+    pb.scales = a->scales; pb.rotations = a->rotations; pb.cov3D_precomp = a->cov3D_precomp;
+    pb.viewmatrix = a->viewmatrix; pb.projmatrix = a->projmatrix; pb.projmatrix_raw = a->projmatrix_raw;
+    pb.campos = a->campos; pb.radii = a->radii; pb.geom = geom; pb.grad = grad;
+    pb.dL_dmeans3D = a->dL_dmeans3D; pb.dL_dmeans2D = a->dL_dmeans2D; pb.dL_dsh = a->dL_dsh;
+    pb.dL_dcolors = a->dL_dcolors; pb.dL_dopacity = a->dL_dopacity; pb.dL_dscales = a->dL_dscales;
+    pb.dL_drotations = a->dL_drotations; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dtau = a->dL_dtau;
+    launch_preprocess_bwd(pb, s);
+    STAGE(a->debug, s, "preprocess_bwd");
+    return WGS_OK;
+}
+
+int wgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* cuda_stream) {
+    (void)projmatrix;  // the reference's test only uses the view-space depth (auxiliary.h:152)
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) {
+        set_err("wgs_mark_visible: invalid argument", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)cuda_stream);
+    STAGE(0, (cudaStream_t)cuda_stream, "mark_visible");
+    return WGS_OK;
+}
+
+int wgs_export_binning(const WgsForwardArgs* a, int64_t num_rendered, uint64_t* point_list_keys,
+                       uint32_t* point_list, uint32_t* ranges, uint32_t* n_contrib, float* final_T,
+                       void* cuda_stream) {
+    if (!a || !a->tile || !a->image || num_rendered > a->capacity) {
+        set_err("wgs_export_binning: invalid argument", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    const int gx = (a->width + 15) / 16, gy = (a->height + 15) / 16, tiles = gx * gy;
+    BinParams bp;
+    bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.capacity = a->capacity;
+    bp.geom = geom_view(a->geom, (size_t)(a->P > 0 ? a->P : 1));
+    bp.tile = tile_view(a->tile, (size_t)tiles);
+    bp.bucket = (unsigned long long*)a->binning; bp.host_R = nullptr;
+    launch_export_binning(bp, image_view(a->image, (size_t)a->width * a->height), a->width, a->height,
+                          (unsigned long long*)point_list_keys, point_list, ranges, n_contrib, final_T,
+                          (cudaStream_t)cuda_stream);
+    STAGE(0, (cudaStream_t)cuda_stream, "export_binning");
+    return WGS_OK;
+}
+
+int wgs_export_geometry(const WgsForwardArgs* a, float* depths, float* means2D, float* conic_opacity, float* rgb,
+                        uint8_t* clamped, void* cuda_stream) {
+    if (!a || (a->P > 0 && (!a->geom || !a->radii))) {
+        set_err("wgs_export_geometry: invalid argument", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    launch_export_geometry(a->P, geom_view(a->geom, (size_t)(a->P > 0 ? a->P : 1)), a->radii, depths, means2D,
+                           conic_opacity, rgb, clamped, (cudaStream_t)cuda_stream);
+    STAGE(0, (cudaStream_t)cuda_stream, "export_geometry");
+    return WGS_OK;
+}
+
+}  // extern "C"

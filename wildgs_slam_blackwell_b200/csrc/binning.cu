@@ -1,0 +1,234 @@
+// Binning: (tile | depth) ordering of the (Gaussian, tile) instances.
+//
+// Replaces the reference's InclusiveSum + duplicateWithKeys + cub::DeviceRadixSort::SortPairs
+// over 64-bit tile<<32|depth keys + identifyTileRanges (rasterizer_impl.cu:70-138, 280-321)
+// with an MSD-first formulation sized for B200's shared memory:
+//   1. the tile digit is histogrammed by preprocess_fwd (one RED per instance),
+//   2. tile_scan_kernel turns the histogram into per-tile [start,end) ranges (this IS
+//      identifyTileRanges) and publishes R = num_rendered,
+//   3. scatter_kernel drops depth_bits<<32|gaussian_id into its tile's segment,
+//   4. each tile segment is sorted in shared memory (up to 24576 entries, 192 KB) by one CTA.
+// Because gaussian ids are unique inside a tile, ordering by (depth_bits, id) is a total order
+// and equals the order the reference's STABLE radix sort produces (ties keep emission order =
+// ascending id), so sorted ids, keys and ranges are bit-identical.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace wgs {
+
+constexpr int SMALL_MAX = 4096;    // 32 KB of keys, 512-thread CTA, 4 CTAs/SM
+constexpr int LARGE_MAX = 24576;   // 192 KB of keys, 1024-thread CTA, 1 CTA/SM
+constexpr int SMALL_THREADS = 512;
+constexpr int LARGE_THREADS = 1024;
+
+__global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__ BinParams p) {
+    __shared__ uint32_t warp_sums[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t carry = 0;
+    for (int base = 0; base < p.tiles; base += 1024) {
+        const int t = base + tid;
+        const uint32_t c = t < p.tiles ? p.tile.count[t] : 0u;
+        uint32_t v = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += u;
+        }
+        if (lane == 31) warp_sums[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t s = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, s, o);
+                if (lane >= o) s += u;
+            }
+            warp_sums[lane] = s;
+        }
+        __syncthreads();
+        const uint32_t excl = carry + (warp ? warp_sums[warp - 1] : 0u) + v - c;
+        if (t < p.tiles) {
+            p.tile.ranges[t] = make_uint2(excl, excl + c);
+            p.tile.cursor[t] = excl;
+            if (c > (uint32_t)SMALL_MAX) p.tile.large_list[atomicAdd(p.tile.misc + MISC_N_LARGE, 1u)] = t;
+        }
+        carry += warp_sums[31];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        p.tile.misc[MISC_NUM_RENDERED] = carry;
+        p.tile.misc[MISC_OVERFLOW] = (long long)carry > p.capacity;
+        if (p.host_R) {
+            *(volatile unsigned int*)p.host_R = carry;
+            __threadfence_system();
+        }
+    }
+}
+
+// duplicateWithKeys (rasterizer_impl.cu:70-111), tile digit already consumed
+__global__ void __launch_bounds__(256) scatter_kernel(const __grid_constant__ BinParams p) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    unsigned long long key = 0;
+    if (idx < p.P) {
+        const uint2 r = p.geom.rect[idx];
+        x0 = r.x & 0xffffu; y0 = r.x >> 16; x1 = r.y & 0xffffu; y1 = r.y >> 16;
+        if (r.y != r.x) {
+            const float depth = ((const float*)(p.geom.rec + 2 * idx + 1))[2];
+            key = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned)idx;
+        }
+    }
+    const uint32_t w = x1 - x0, n = w * (y1 - y0);
+    const bool wide = n > 32;
+    if (n && !wide) {
+        for (uint32_t y = y0; y < y1; y++)
+            for (uint32_t x = x0; x < x1; x++) {
+                const uint32_t slot = atomicAdd(p.tile.cursor + y * p.gx + x, 1u);
+                if ((long long)slot < p.capacity) p.bucket[slot] = key;
+            }
+    }
+    unsigned m = __ballot_sync(0xffffffffu, wide);
+    while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1;
+        const uint32_t sx0 = __shfl_sync(0xffffffffu, x0, src), sy0 = __shfl_sync(0xffffffffu, y0, src);
+        const uint32_t sw = __shfl_sync(0xffffffffu, w, src), sn = __shfl_sync(0xffffffffu, n, src);
+        const unsigned long long skey = __shfl_sync(0xffffffffu, key, src);
+        for (uint32_t i = lane; i < sn; i += 32) {
+            const uint32_t slot = atomicAdd(p.tile.cursor + (sy0 + i / sw) * p.gx + sx0 + i % sw, 1u);
+            if ((long long)slot < p.capacity) p.bucket[slot] = skey;
+        }
+    }
+}
+
+// All-ascending bitonic network (no padding needed: comparators whose upper index is >= n
+// compare against +inf and never swap).  `a` may be shared or global memory.
+__device__ __forceinline__ void bitonic_sort(unsigned long long* a, int n, int tid, int nthreads) {
+    int n_pad = 2;
+    while (n_pad < n) n_pad <<= 1;
+    const int half = n_pad >> 1;
+    for (int k = 2; k <= n_pad; k <<= 1) {
+        const int hk = k >> 1;
+        for (int t = tid; t < half; t += nthreads) {
+            const int i = (t / hk) * k + (t % hk);
+            const int l = i ^ (k - 1);
+            if (l < n) {
+                const unsigned long long u = a[i], v = a[l];
+                if (u > v) { a[i] = v; a[l] = u; }
+            }
+        }
+        __syncthreads();
+        for (int j = k >> 2; j > 0; j >>= 1) {
+            for (int t = tid; t < half; t += nthreads) {
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int l = i | j;
+                if (l < n) {
+                    const unsigned long long u = a[i], v = a[l];
+                    if (u > v) { a[i] = v; a[l] = u; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __grid_constant__ BinParams p) {
+    __shared__ unsigned long long keys[SMALL_MAX];
+    const uint2 r = p.tile.ranges[blockIdx.x];
+    const int n = (int)(r.y - r.x);
+    if (n < 2 || n > SMALL_MAX || p.tile.misc[MISC_OVERFLOW]) return;
+    unsigned long long* seg = p.bucket + r.x;
+    for (int i = threadIdx.x; i < n; i += SMALL_THREADS) keys[i] = seg[i];
+    __syncthreads();
+    bitonic_sort(keys, n, threadIdx.x, SMALL_THREADS);
+    for (int i = threadIdx.x; i < n; i += SMALL_THREADS) seg[i] = keys[i];
+}
+
+__global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __grid_constant__ BinParams p) {
+    extern __shared__ unsigned long long lkeys[];
+    if (p.tile.misc[MISC_OVERFLOW]) return;
+    const int n_large = (int)p.tile.misc[MISC_N_LARGE];
+    for (int q = blockIdx.x; q < n_large; q += gridDim.x) {
+        const uint2 r = p.tile.ranges[p.tile.large_list[q]];
+        const int n = (int)(r.y - r.x);
+        unsigned long long* seg = p.bucket + r.x;
+        if (n <= LARGE_MAX) {
+            for (int i = threadIdx.x; i < n; i += LARGE_THREADS) lkeys[i] = seg[i];
+            __syncthreads();
+            bitonic_sort(lkeys, n, threadIdx.x, LARGE_THREADS);
+            for (int i = threadIdx.x; i < n; i += LARGE_THREADS) seg[i] = lkeys[i];
+            __syncthreads();
+        } else {
+            __syncthreads();
+            bitonic_sort(seg, n, threadIdx.x, LARGE_THREADS);  // in global memory (L2-resident)
+        }
+    }
+}
+
+// ---- parity/debug exports in the reference's BinningState / ImageState terms ----
+__global__ void export_binning_kernel(BinParams p, unsigned long long* keys, unsigned int* list,
+                                      unsigned int* ranges) {
+    const int t = blockIdx.x;
+    const uint2 r = p.tile.ranges[t];
+    if (ranges && threadIdx.x == 0) {
+        const bool empty = r.x == r.y;  // the reference leaves empty tiles at the memset value
+        ranges[2 * t] = empty ? 0u : r.x;
+        ranges[2 * t + 1] = empty ? 0u : r.y;
+    }
+    for (uint32_t i = r.x + threadIdx.x; i < r.y; i += blockDim.x) {
+        const unsigned long long e = p.bucket[i];
+        if (keys) keys[i] = ((unsigned long long)t << 32) | (e >> 32);
+        if (list) list[i] = (unsigned int)e;
+    }
+}
+
+__global__ void export_geometry_kernel(int P, GeomView g, const int* radii, float* depths, float* means2D,
+                                       float* conic_opacity, float* rgb, uint8_t* clamped) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const bool vis = radii[i] > 0;
+    const float4 a = vis ? g.rec[2 * i] : make_float4(0, 0, 0, 0);
+    const float4 b = vis ? g.rec[2 * i + 1] : make_float4(0, 0, 0, 0);
+    const float4 c = vis ? g.col[i] : make_float4(0, 0, 0, 0);
+    const uint8_t cb = vis ? g.clamped[i] : 0;
+    if (depths) depths[i] = b.z;
+    if (means2D) { means2D[2 * i] = a.x; means2D[2 * i + 1] = a.y; }
+    if (conic_opacity) {
+        conic_opacity[4 * i] = a.z; conic_opacity[4 * i + 1] = a.w;
+        conic_opacity[4 * i + 2] = b.x; conic_opacity[4 * i + 3] = b.y;
+    }
+    if (rgb) { rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z; }
+    if (clamped) { clamped[3 * i] = cb & 1; clamped[3 * i + 1] = (cb >> 1) & 1; clamped[3 * i + 2] = (cb >> 2) & 1; }
+}
+
+void launch_tile_scan(const BinParams& p, cudaStream_t s) { tile_scan_kernel<<<1, 1024, 0, s>>>(p); }
+
+void launch_binning(const BinParams& p, int num_sms, cudaStream_t s) {
+    if (p.P > 0) scatter_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p);
+    tile_sort_small_kernel<<<p.tiles, SMALL_THREADS, 0, s>>>(p);
+    tile_sort_large_kernel<<<num_sms, LARGE_THREADS, LARGE_MAX * 8, s>>>(p);
+}
+
+void launch_export_binning(const BinParams& p, const ImageView& image, int W, int H, unsigned long long* keys,
+                           unsigned int* list, unsigned int* ranges, unsigned int* n_contrib, float* final_T,
+                           cudaStream_t s) {
+    export_binning_kernel<<<p.tiles, 256, 0, s>>>(p, keys, list, ranges);
+    const size_t N = (size_t)W * H;
+    if (n_contrib) cudaMemcpyAsync(n_contrib, image.n_contrib, N * 4, cudaMemcpyDeviceToDevice, s);
+    if (final_T) cudaMemcpyAsync(final_T, image.final_T, N * 4, cudaMemcpyDeviceToDevice, s);
+}
+
+void launch_export_geometry(int P, const GeomView& g, const int* radii, float* depths, float* means2D,
+                            float* conic_opacity, float* rgb, uint8_t* clamped, cudaStream_t s) {
+    if (P > 0)
+        export_geometry_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, g, radii, depths, means2D, conic_opacity, rgb,
+                                                               clamped);
+}
+
+int configure_binning() {
+    return (int)cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     LARGE_MAX * 8);
+}
+
+}  // namespace wgs

@@ -34,8 +34,7 @@ namespace wgs {
 enum MiscSlot : int {
     MISC_NUM_RENDERED = 0,   // R: total (Gaussian,tile) instances of this forward
     MISC_OVERFLOW = 1,       // set if R > capacity
-    MISC_N_MID = 2,          // number of tiles sorted by the mid-size kernel
-    MISC_N_BIG = 3,          // number of tiles sorted by the global-memory kernel
+    MISC_N_LARGE = 2,        // number of tiles handed to the large sort kernel
     MISC_PREFILTER_HIT = 4,  // a point was culled although prefiltered was set
     MISC_TICKET = 5,
     MISC_WORDS = 32
@@ -53,8 +52,7 @@ struct TileView {
     uint32_t* cursor;
     uint2* ranges;
     uint32_t* misc;
-    uint32_t* mid_list;  // tile ids with SMALL_MAX < n <= MID_MAX
-    uint32_t* big_list;  // tile ids with n > MID_MAX
+    uint32_t* large_list;  // tile ids whose segment is too long for the small sort kernel
 };
 
 struct ImageView {
@@ -82,18 +80,19 @@ __host__ __device__ inline GeomView geom_view(void* base, size_t P) {
     g.clamped = (uint8_t*)p;
     return g;
 }
+// count[] and misc[] are adjacent so that one memset clears both at the start of a forward
+__host__ __device__ inline size_t tile_clear_bytes(size_t tiles) { return align_up(tiles * 4) + align_up(MISC_WORDS * 4); }
 __host__ __device__ inline size_t tile_bytes(size_t tiles) {
-    return 4 * align_up(tiles * 4) + align_up(tiles * 8) + align_up(MISC_WORDS * 4);
+    return tile_clear_bytes(tiles) + 2 * align_up(tiles * 4) + align_up(tiles * 8);
 }
 __host__ __device__ inline TileView tile_view(void* base, size_t tiles) {
     char* p = (char*)base;
     TileView t;
     t.count = (uint32_t*)p; p += align_up(tiles * 4);
+    t.misc = (uint32_t*)p; p += align_up(MISC_WORDS * 4);
     t.cursor = (uint32_t*)p; p += align_up(tiles * 4);
-    t.mid_list = (uint32_t*)p; p += align_up(tiles * 4);
-    t.big_list = (uint32_t*)p; p += align_up(tiles * 4);
-    t.ranges = (uint2*)p; p += align_up(tiles * 8);
-    t.misc = (uint32_t*)p;
+    t.large_list = (uint32_t*)p; p += align_up(tiles * 4);
+    t.ranges = (uint2*)p;
     return t;
 }
 __host__ __device__ inline size_t image_bytes(size_t N) { return 2 * align_up(N * 4); }

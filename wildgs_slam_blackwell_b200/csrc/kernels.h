@@ -1,0 +1,76 @@
+// Kernel parameter blocks and host launchers (internal; the public surface is
+// include/wgs_rasterizer.h).
+#pragma once
+#include "common.cuh"
+
+namespace wgs {
+
+struct PreFwdParams {
+    int P, D, M, W, H, gx, gy, prefiltered;
+    float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
+    const float *means3D, *sh, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
+    const float *viewmatrix, *projmatrix, *campos;
+    int* radii;
+    int* n_touched;
+    GeomView geom;
+    TileView tile;
+};
+
+struct BinParams {
+    int P, gx, gy, tiles;
+    long long capacity;
+    GeomView geom;
+    TileView tile;
+    unsigned long long* bucket;
+    unsigned int* host_R;  // mapped pinned word (may be null)
+};
+
+struct RenderFwdParams {
+    int W, H, gx, gy;
+    const float* bg;
+    GeomView geom;
+    TileView tile;
+    ImageView image;
+    const unsigned long long* bucket;
+    float *out_color, *out_depth, *out_opacity;
+    int* n_touched;
+};
+
+struct RenderBwdParams {
+    int W, H, gx, gy;
+    const float* bg;
+    GeomView geom;
+    TileView tile;
+    ImageView image;
+    const unsigned long long* bucket;
+    const float *dL_dcolor, *dL_ddepth;
+    GradView grad;
+};
+
+struct PreBwdParams {
+    int P, D, M, W, H;
+    float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
+    const float *means3D, *sh, *colors_precomp, *scales, *rotations, *cov3D_precomp;
+    const float *viewmatrix, *projmatrix, *projmatrix_raw, *campos;
+    const int* radii;
+    GeomView geom;
+    GradView grad;
+    float *dL_dmeans3D, *dL_dmeans2D, *dL_dsh, *dL_dcolors, *dL_dopacity, *dL_dscales, *dL_drotations,
+        *dL_dcov3D, *dL_dtau;
+};
+
+void launch_preprocess_fwd(const PreFwdParams& p, cudaStream_t s);
+void launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s);
+void launch_tile_scan(const BinParams& p, cudaStream_t s);   // ranges + R
+void launch_binning(const BinParams& p, int num_sms, cudaStream_t s);  // scatter + per-tile sorts
+void launch_render_fwd(const RenderFwdParams& p, cudaStream_t s);
+void launch_render_bwd(const RenderBwdParams& p, cudaStream_t s);
+void launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s);
+void launch_export_binning(const BinParams& p, const ImageView& image, int W, int H, unsigned long long* keys,
+                           unsigned int* list, unsigned int* ranges, unsigned int* n_contrib, float* final_T,
+                           cudaStream_t s);
+void launch_export_geometry(int P, const GeomView& g, const int* radii, float* depths, float* means2D,
+                            float* conic_opacity, float* rgb, uint8_t* clamped, cudaStream_t s);
+int configure_binning();  // one-time cudaFuncSetAttribute calls; returns cudaError_t
+
+}  // namespace wgs

@@ -1,0 +1,323 @@
+// Backward per-Gaussian stage, one fused pass.  Replaces reference computeCov2DCUDA
+// (cuda_rasterizer/backward.cu:150-346), preprocessCUDA (backward, :418-539), the SH backward
+// (:21-145), the cov3D backward (:350-413) and the torch.sum over the (P,6) dL_dtau buffer in
+// diff_gaussian_rasterization/__init__.py:152-154.
+//
+// Each thread consumes (and re-zeroes) the 48-byte accumulator record render_bwd filled,
+// recomputes the forward intermediates it needs (cov3D, T = W*J) instead of reading a stored
+// copy, writes every per-Gaussian output exactly once (so outputs need no pre-zeroing), and
+// the six pose-gradient terms are reduced warp -> block -> grid (per-block partials, last
+// block sums them in a fixed order: deterministic, no (P,6) buffer, no atomics on dL_dtau).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace wgs {
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+    return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+
+__device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const float* q4, float c[6], float R[9],
+                                              float s[3]) {
+    // R[3*col + row] as GLM stores it (reference computeCov3D, forward.cu:120-154)
+    const float r = q4[0], x = q4[1], y = q4[2], z = q4[3];
+    R[0] = 1.f - 2.f * (y * y + z * z); R[1] = 2.f * (x * y - r * z); R[2] = 2.f * (x * z + r * y);
+    R[3] = 2.f * (x * y + r * z); R[4] = 1.f - 2.f * (x * x + z * z); R[5] = 2.f * (y * z - r * x);
+    R[6] = 2.f * (x * z - r * y); R[7] = 2.f * (y * z + r * x); R[8] = 1.f - 2.f * (x * x + y * y);
+    s[0] = mod * s3[0]; s[1] = mod * s3[1]; s[2] = mod * s3[2];
+    float M[9];  // M = S*R : M[c][r] = s_r R[c][r]
+#pragma unroll
+    for (int cc = 0; cc < 3; cc++)
+#pragma unroll
+        for (int rr = 0; rr < 3; rr++) M[3 * cc + rr] = s[rr] * R[3 * cc + rr];
+    // Sigma = M^T M : Sigma[c][r] = dot(M[r][:], M[c][:])
+    c[0] = M[0] * M[0] + M[1] * M[1] + M[2] * M[2];
+    c[1] = M[0] * M[3] + M[1] * M[4] + M[2] * M[5];
+    c[2] = M[0] * M[6] + M[1] * M[7] + M[2] * M[8];
+    c[3] = M[3] * M[3] + M[4] * M[4] + M[5] * M[5];
+    c[4] = M[3] * M[6] + M[4] * M[7] + M[5] * M[8];
+    c[5] = M[6] * M[6] + M[7] * M[7] + M[8] * M[8];
+}
+
+__global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
+    const int idx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
+    float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (idx < p.P) {
+        const bool vis = p.radii[idx] > 0;
+        float4 g0 = make_float4(0, 0, 0, 0), g1 = g0, g2 = g0;
+        if (vis) {
+            g0 = p.grad.acc[3 * idx]; g1 = p.grad.acc[3 * idx + 1]; g2 = p.grad.acc[3 * idx + 2];
+            const float4 z4 = make_float4(0, 0, 0, 0);
+            p.grad.acc[3 * idx] = z4; p.grad.acc[3 * idx + 1] = z4; p.grad.acc[3 * idx + 2] = z4;
+        }
+        const float dm2x = g0.x, dm2y = g0.y;              // dL/dmean2D (NDC-scaled)
+        const float dcx = g0.z, dcy = g0.w, dcz = g1.x;    // dL/dconic (x, y, w)
+        const float dop = g1.y;
+        const float dcol[3] = {g1.z, g1.w, g2.x};
+        const float ddepth = g2.y;
+        V3 dmean = {0.f, 0.f, 0.f};
+        float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        float dscale[3] = {0.f, 0.f, 0.f}, drot[4] = {0.f, 0.f, 0.f, 0.f};
+        if (vis) {
+            const float* __restrict__ V = p.viewmatrix;
+            const float* __restrict__ Pm = p.projmatrix;
+            const V3 m = {__ldg(p.means3D + 3 * idx), __ldg(p.means3D + 3 * idx + 1), __ldg(p.means3D + 3 * idx + 2)};
+            float c3[6], Rq[9], sc[3], q4[4];
+            if (p.cov3D_precomp) {
+#pragma unroll
+                for (int k = 0; k < 6; k++) c3[k] = __ldg(p.cov3D_precomp + 6 * idx + k);
+            } else {
+                const float s3[3] = {__ldg(p.scales + 3 * idx), __ldg(p.scales + 3 * idx + 1), __ldg(p.scales + 3 * idx + 2)};
+#pragma unroll
+                for (int k = 0; k < 4; k++) q4[k] = __ldg(p.rotations + 4 * idx + k);
+                cov3d_natural(s3, p.scale_modifier, q4, c3, Rq, sc);
+            }
+            // ---- computeCov2DCUDA (backward.cu:150-346) ----
+            V3 t = {V[0] * m.x + V[4] * m.y + V[8] * m.z + V[12], V[1] * m.x + V[5] * m.y + V[9] * m.z + V[13],
+                    V[2] * m.x + V[6] * m.y + V[10] * m.z + V[14]};
+            const float limx = 1.3f * p.tanfovx, limy = 1.3f * p.tanfovy;
+            const float txtz = t.x / t.z, tytz = t.y / t.z;
+            t.x = fminf(limx, fmaxf(-limx, txtz)) * t.z;
+            t.y = fminf(limy, fmaxf(-limy, tytz)) * t.z;
+            const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+            const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+            const float hx = p.focal_x, hy = p.focal_y;
+            const float J00 = hx / t.z, J02 = -(hx * t.x) / (t.z * t.z), J11 = hy / t.z, J12 = -(hy * t.y) / (t.z * t.z);
+            // T = W*J, T[c][r]; W[c][r] with W = mat3(V0,V4,V8, V1,V5,V9, V2,V6,V10)
+            const float T00 = V[0] * J00 + V[2] * J02, T01 = V[4] * J00 + V[6] * J02, T02 = V[8] * J00 + V[10] * J02;
+            const float T10 = V[1] * J11 + V[2] * J12, T11 = V[5] * J11 + V[6] * J12, T12 = V[9] * J11 + V[10] * J12;
+            // Vrk rows dotted with T rows
+            const float A0 = T00 * c3[0] + T01 * c3[1] + T02 * c3[2], A1 = T00 * c3[1] + T01 * c3[3] + T02 * c3[4],
+                        A2 = T00 * c3[2] + T01 * c3[4] + T02 * c3[5];
+            const float B0 = T10 * c3[0] + T11 * c3[1] + T12 * c3[2], B1 = T10 * c3[1] + T11 * c3[3] + T12 * c3[4],
+                        B2 = T10 * c3[2] + T11 * c3[4] + T12 * c3[5];
+            const float a = T00 * A0 + T01 * A1 + T02 * A2 + 0.3f;
+            const float b = T00 * B0 + T01 * B1 + T02 * B2;
+            const float c = T10 * B0 + T11 * B1 + T12 * B2 + 0.3f;
+            const float denom = a * c - b * b;
+            const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+            float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
+            if (denom2inv != 0.f) {
+                dL_da = denom2inv * (-c * c * dcx + 2.f * b * c * dcy + (denom - a * c) * dcz);
+                dL_dc = denom2inv * (-a * a * dcz + 2.f * a * b * dcy + (denom - a * c) * dcx);
+                dL_db = denom2inv * 2.f * (b * c * dcx - (denom + 2.f * b * b) * dcy + a * b * dcz);
+                dcov[0] = T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc;
+                dcov[3] = T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc;
+                dcov[5] = T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc;
+                dcov[1] = 2.f * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + 2.f * T10 * T11 * dL_dc;
+                dcov[2] = 2.f * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2.f * T10 * T12 * dL_dc;
+                dcov[4] = 2.f * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2.f * T11 * T12 * dL_dc;
+            }
+            // A* = T[0][:]·Vrk[k][:], B* = T[1][:]·Vrk[k][:]  (Vrk symmetric)
+            const float dT00 = 2.f * A0 * dL_da + B0 * dL_db, dT01 = 2.f * A1 * dL_da + B1 * dL_db,
+                        dT02 = 2.f * A2 * dL_da + B2 * dL_db;
+            const float dT10 = 2.f * B0 * dL_dc + A0 * dL_db, dT11 = 2.f * B1 * dL_dc + A1 * dL_db,
+                        dT12 = 2.f * B2 * dL_dc + A2 * dL_db;
+            // W[c][r]: W[0]=(V0,V4,V8) W[1]=(V1,V5,V9) W[2]=(V2,V6,V10)
+            const float dJ00 = V[0] * dT00 + V[4] * dT01 + V[8] * dT02;
+            const float dJ02 = V[2] * dT00 + V[6] * dT01 + V[10] * dT02;
+            const float dJ11 = V[1] * dT10 + V[5] * dT11 + V[9] * dT12;
+            const float dJ12 = V[2] * dT10 + V[6] * dT11 + V[10] * dT12;
+            const float tz = 1.f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
+            const float dtx = x_grad_mul * -hx * tz2 * dJ02;
+            const float dty = y_grad_mul * -hy * tz2 * dJ12;
+            const float dtz = -hx * tz2 * dJ00 - hy * tz2 * dJ11 + (2.f * hx * t.x) * tz3 * dJ02 + (2.f * hy * t.y) * tz3 * dJ12;
+            // pose via camera-space mean (clamped t), (:273-288)
+            tau[0] += dtx; tau[1] += dty; tau[2] += dtz;
+            tau[3] += dty * (-t.z) + dtz * t.y;
+            tau[4] += dtx * t.z + dtz * (-t.x);
+            tau[5] += dtx * (-t.y) + dty * t.x;
+            dmean = {V[0] * dtx + V[1] * dty + V[2] * dtz, V[4] * dtx + V[5] * dty + V[6] * dtz,
+                     V[8] * dtx + V[9] * dty + V[10] * dtz};
+            // pose via W (:299-343)
+            {
+                const V3 dWc1 = {J00 * dT00, J11 * dT10, J02 * dT00 + J12 * dT10};
+                const V3 dWc2 = {J00 * dT01, J11 * dT11, J02 * dT01 + J12 * dT11};
+                const V3 dWc3 = {J00 * dT02, J11 * dT12, J02 * dT02 + J12 * dT12};
+                const V3 c1 = {V[0], V[1], V[2]}, c2 = {V[4], V[5], V[6]}, c3v = {V[8], V[9], V[10]};
+                // -skew(c).cols: (0,-cz,cy) (cz,0,-cx) (-cy,cx,0)
+                tau[3] += (-c1.z * dWc1.y + c1.y * dWc1.z) + (-c2.z * dWc2.y + c2.y * dWc2.z) + (-c3v.z * dWc3.y + c3v.y * dWc3.z);
+                tau[4] += (c1.z * dWc1.x - c1.x * dWc1.z) + (c2.z * dWc2.x - c2.x * dWc2.z) + (c3v.z * dWc3.x - c3v.x * dWc3.z);
+                tau[5] += (-c1.y * dWc1.x + c1.x * dWc1.y) + (-c2.y * dWc2.x + c2.x * dWc2.y) + (-c3v.y * dWc3.x + c3v.x * dWc3.y);
+            }
+            // ---- preprocessCUDA backward (:442-538) ----
+            const float mhx = Pm[0] * m.x + Pm[4] * m.y + Pm[8] * m.z + Pm[12];
+            const float mhy = Pm[1] * m.x + Pm[5] * m.y + Pm[9] * m.z + Pm[13];
+            const float mhw = Pm[3] * m.x + Pm[7] * m.y + Pm[11] * m.z + Pm[15];
+            const float m_w = 1.0f / (mhw + 0.0000001f);
+            const float mul1 = mhx * m_w * m_w, mul2 = mhy * m_w * m_w;
+            dmean.x += (Pm[0] * m_w - Pm[3] * mul1) * dm2x + (Pm[1] * m_w - Pm[3] * mul2) * dm2y;
+            dmean.y += (Pm[4] * m_w - Pm[7] * mul1) * dm2x + (Pm[5] * m_w - Pm[7] * mul2) * dm2y;
+            dmean.z += (Pm[8] * m_w - Pm[11] * mul1) * dm2x + (Pm[9] * m_w - Pm[11] * mul2) * dm2y;
+            {
+                const float alpha = m_w, beta = -mhx * m_w * m_w, gamma = -mhy * m_w * m_w;
+                const float ra = __ldg(p.projmatrix_raw), rb = __ldg(p.projmatrix_raw + 5), re = __ldg(p.projmatrix_raw + 11);
+                const V3 pC = {V[0] * m.x + V[4] * m.y + V[8] * m.z + V[12], V[1] * m.x + V[5] * m.y + V[9] * m.z + V[13],
+                               V[2] * m.x + V[6] * m.y + V[10] * m.z + V[14]};
+                const V3 d1 = {alpha * ra, 0.f, beta * re}, d2 = {0.f, alpha * rb, gamma * re};
+                const V3 th1 = cross(pC, d1), th2 = cross(pC, d2);
+                tau[0] += dm2x * d1.x + dm2y * d2.x; tau[1] += dm2x * d1.y + dm2y * d2.y; tau[2] += dm2x * d1.z + dm2y * d2.z;
+                tau[3] += dm2x * th1.x + dm2y * th2.x; tau[4] += dm2x * th1.y + dm2y * th2.y; tau[5] += dm2x * th1.z + dm2y * th2.z;
+                // depth = p_view.z (:514-528)
+                dmean.x += ddepth * V[2]; dmean.y += ddepth * V[6]; dmean.z += ddepth * V[10];
+                tau[2] += ddepth; tau[3] += ddepth * pC.y; tau[4] += -ddepth * pC.x;
+            }
+            // ---- SH backward (:21-145) ----
+            if (p.sh) {
+                const float* __restrict__ sh = p.sh + (size_t)idx * p.M * 3;
+                float* __restrict__ dsh = p.dL_dsh + (size_t)idx * p.M * 3;
+                const uint8_t cb = p.geom.clamped[idx];
+                const V3 dRGB = {(cb & 1) ? 0.f : dcol[0], (cb & 2) ? 0.f : dcol[1], (cb & 4) ? 0.f : dcol[2]};
+                const V3 dir_orig = {m.x - __ldg(p.campos), m.y - __ldg(p.campos + 1), m.z - __ldg(p.campos + 2)};
+                const float il = 1.f / sqrtf(dot(dir_orig, dir_orig));
+                const float x = dir_orig.x * il, y = dir_orig.y * il, z = dir_orig.z * il;
+                auto SH = [&](int k) { return V3{__ldg(sh + 3 * k), __ldg(sh + 3 * k + 1), __ldg(sh + 3 * k + 2)}; };
+                auto put = [&](int k, float w) { dsh[3 * k] = w * dRGB.x; dsh[3 * k + 1] = w * dRGB.y; dsh[3 * k + 2] = w * dRGB.z; };
+                V3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
+                put(0, kSH_C0);
+                if (p.D > 0) {
+                    put(1, -kSH_C1 * y); put(2, kSH_C1 * z); put(3, -kSH_C1 * x);
+                    dx = -kSH_C1 * SH(3); dy = -kSH_C1 * SH(1); dz = kSH_C1 * SH(2);
+                    if (p.D > 1) {
+                        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+                        put(4, kSH_C2[0] * xy); put(5, kSH_C2[1] * yz); put(6, kSH_C2[2] * (2.f * zz - xx - yy));
+                        put(7, kSH_C2[3] * xz); put(8, kSH_C2[4] * (xx - yy));
+                        dx = dx + (kSH_C2[0] * y) * SH(4) + (kSH_C2[2] * 2.f * -x) * SH(6) + (kSH_C2[3] * z) * SH(7) + (kSH_C2[4] * 2.f * x) * SH(8);
+                        dy = dy + (kSH_C2[0] * x) * SH(4) + (kSH_C2[1] * z) * SH(5) + (kSH_C2[2] * 2.f * -y) * SH(6) + (kSH_C2[4] * 2.f * -y) * SH(8);
+                        dz = dz + (kSH_C2[1] * y) * SH(5) + (kSH_C2[2] * 2.f * 2.f * z) * SH(6) + (kSH_C2[3] * x) * SH(7);
+                        if (p.D > 2) {
+                            put(9, kSH_C3[0] * y * (3.f * xx - yy)); put(10, kSH_C3[1] * xy * z);
+                            put(11, kSH_C3[2] * y * (4.f * zz - xx - yy)); put(12, kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
+                            put(13, kSH_C3[4] * x * (4.f * zz - xx - yy)); put(14, kSH_C3[5] * z * (xx - yy));
+                            put(15, kSH_C3[6] * x * (xx - 3.f * yy));
+                            dx = dx + (kSH_C3[0] * 3.f * 2.f * xy) * SH(9) + (kSH_C3[1] * yz) * SH(10) + (kSH_C3[2] * -2.f * xy) * SH(11) +
+                                 (kSH_C3[3] * -3.f * 2.f * xz) * SH(12) + (kSH_C3[4] * (-3.f * xx + 4.f * zz - yy)) * SH(13) +
+                                 (kSH_C3[5] * 2.f * xz) * SH(14) + (kSH_C3[6] * 3.f * (xx - yy)) * SH(15);
+                            dy = dy + (kSH_C3[0] * 3.f * (xx - yy)) * SH(9) + (kSH_C3[1] * xz) * SH(10) +
+                                 (kSH_C3[2] * (-3.f * yy + 4.f * zz - xx)) * SH(11) + (kSH_C3[3] * -3.f * 2.f * yz) * SH(12) +
+                                 (kSH_C3[4] * -2.f * xy) * SH(13) + (kSH_C3[5] * -2.f * yz) * SH(14) + (kSH_C3[6] * -3.f * 2.f * xy) * SH(15);
+                            dz = dz + (kSH_C3[1] * xy) * SH(10) + (kSH_C3[2] * 4.f * 2.f * yz) * SH(11) +
+                                 (kSH_C3[3] * 3.f * (2.f * zz - xx - yy)) * SH(12) + (kSH_C3[4] * 4.f * 2.f * xz) * SH(13) +
+                                 (kSH_C3[5] * (xx - yy)) * SH(14);
+                        }
+                    }
+                }
+                for (int k = (p.D + 1) * (p.D + 1); k < p.M; k++) put(k, 0.f);  // inactive bands
+                const V3 ddir = {dot(dx, dRGB), dot(dy, dRGB), dot(dz, dRGB)};
+                // dnormvdv (auxiliary.h:107-117)
+                const V3 v = dir_orig;
+                const float sum2 = dot(v, v);
+                const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+                const V3 dms = {((sum2 - v.x * v.x) * ddir.x - v.y * v.x * ddir.y - v.z * v.x * ddir.z) * invsum32,
+                                (-v.x * v.y * ddir.x + (sum2 - v.y * v.y) * ddir.y - v.z * v.y * ddir.z) * invsum32,
+                                (-v.x * v.z * ddir.x - v.y * v.z * ddir.y + (sum2 - v.z * v.z) * ddir.z) * invsum32};
+                dmean = dmean + dms;
+                tau[0] -= dms.x; tau[1] -= dms.y; tau[2] -= dms.z;
+            }
+            // ---- cov3D backward (:350-413) ----
+            if (!p.cov3D_precomp) {
+                float M[9];
+#pragma unroll
+                for (int cc = 0; cc < 3; cc++)
+#pragma unroll
+                    for (int rr = 0; rr < 3; rr++) M[3 * cc + rr] = sc[rr] * Rq[3 * cc + rr];
+                // dL_dSigma (symmetric), GLM [c][r]
+                const float S[9] = {dcov[0], 0.5f * dcov[1], 0.5f * dcov[2], 0.5f * dcov[1], dcov[3], 0.5f * dcov[4],
+                                    0.5f * dcov[2], 0.5f * dcov[4], dcov[5]};
+                // dL_dM = 2 * M * dL_dSigma : [c][r] = 2 * sum_k M[k][r] * S[c][k]
+                float dM[9];
+#pragma unroll
+                for (int cc = 0; cc < 3; cc++)
+#pragma unroll
+                    for (int rr = 0; rr < 3; rr++)
+                        dM[3 * cc + rr] = 2.f * (M[rr] * S[3 * cc] + M[3 + rr] * S[3 * cc + 1] + M[6 + rr] * S[3 * cc + 2]);
+                // Rt = R^T, dMt = dM^T ; Rt[i] (column i of R^T) = row i of R ; dMt[i] = row i of dM
+                float dMt[9];  // dMt[3*i + j] = dM[j][i]  (GLM: dMt[i][j])
+#pragma unroll
+                for (int i = 0; i < 3; i++)
+#pragma unroll
+                    for (int j = 0; j < 3; j++) dMt[3 * i + j] = dM[3 * j + i];
+#pragma unroll
+                for (int i = 0; i < 3; i++)
+                    dscale[i] = Rq[i] * dMt[3 * i] + Rq[3 + i] * dMt[3 * i + 1] + Rq[6 + i] * dMt[3 * i + 2];
+#pragma unroll
+                for (int i = 0; i < 3; i++)
+#pragma unroll
+                    for (int j = 0; j < 3; j++) dMt[3 * i + j] *= sc[i];
+                const float r = q4[0], x = q4[1], y = q4[2], z = q4[3];
+#define DMT(i, j) dMt[3 * (i) + (j)]
+                drot[0] = 2 * z * (DMT(0, 1) - DMT(1, 0)) + 2 * y * (DMT(2, 0) - DMT(0, 2)) + 2 * x * (DMT(1, 2) - DMT(2, 1));
+                drot[1] = 2 * y * (DMT(1, 0) + DMT(0, 1)) + 2 * z * (DMT(2, 0) + DMT(0, 2)) + 2 * r * (DMT(1, 2) - DMT(2, 1)) -
+                          4 * x * (DMT(2, 2) + DMT(1, 1));
+                drot[2] = 2 * x * (DMT(1, 0) + DMT(0, 1)) + 2 * r * (DMT(2, 0) - DMT(0, 2)) + 2 * z * (DMT(1, 2) + DMT(2, 1)) -
+                          4 * y * (DMT(2, 2) + DMT(0, 0));
+                drot[3] = 2 * r * (DMT(0, 1) - DMT(1, 0)) + 2 * x * (DMT(2, 0) + DMT(0, 2)) + 2 * y * (DMT(1, 2) + DMT(2, 1)) -
+                          4 * z * (DMT(1, 1) + DMT(0, 0));
+#undef DMT
+            }
+        } else if (p.sh && p.dL_dsh) {
+            float* __restrict__ dsh = p.dL_dsh + (size_t)idx * p.M * 3;
+            for (int k = 0; k < 3 * p.M; k++) dsh[k] = 0.f;
+        }
+        if (p.dL_dmeans3D) { p.dL_dmeans3D[3 * idx] = dmean.x; p.dL_dmeans3D[3 * idx + 1] = dmean.y; p.dL_dmeans3D[3 * idx + 2] = dmean.z; }
+        if (p.dL_dmeans2D) { p.dL_dmeans2D[3 * idx] = dm2x; p.dL_dmeans2D[3 * idx + 1] = dm2y; p.dL_dmeans2D[3 * idx + 2] = 0.f; }
+        if (p.dL_dopacity) p.dL_dopacity[idx] = dop;
+        if (p.dL_dcolors) { p.dL_dcolors[3 * idx] = dcol[0]; p.dL_dcolors[3 * idx + 1] = dcol[1]; p.dL_dcolors[3 * idx + 2] = dcol[2]; }
+        if (p.dL_dcov3D) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * idx + k] = dcov[k];
+        }
+        if (p.dL_dscales) { p.dL_dscales[3 * idx] = dscale[0]; p.dL_dscales[3 * idx + 1] = dscale[1]; p.dL_dscales[3 * idx + 2] = dscale[2]; }
+        if (p.dL_drotations) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) p.dL_drotations[4 * idx + k] = drot[k];
+        }
+    }
+    // ---- pose gradient: warp -> block -> grid, deterministic ----
+    __shared__ float s_part[WGS_PRE_BWD_THREADS / 32][6];
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < 6; i++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) tau[i] += __shfl_xor_sync(0xffffffffu, tau[i], o);
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < 6; i++) s_part[warp][i] = tau[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < WGS_PRE_BWD_THREADS / 32; w++) s += s_part[w][threadIdx.x];
+        p.grad.pose_partials[6 * blockIdx.x + threadIdx.x] = s;
+        __threadfence();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(p.grad.ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        // 6 warps, one per component; lanes stride over the blocks, fixed order
+        if (warp < 6) {
+            double s = 0.0;
+            for (unsigned b = lane; b < gridDim.x; b += 32) s += (double)((volatile float*)p.grad.pose_partials)[6 * b + warp];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane == 0 && p.dL_dtau) p.dL_dtau[warp] = (float)s;
+        }
+        if (threadIdx.x == 0) *p.grad.ticket = 0;
+    }
+}
+
+void launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
+    if (p.P > 0)
+        preprocess_bwd_kernel<<<(p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS, WGS_PRE_BWD_THREADS, 0, s>>>(p);
+}
+
+}  // namespace wgs

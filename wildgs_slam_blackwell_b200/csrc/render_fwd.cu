@@ -1,0 +1,136 @@
+// Forward alpha compositing.  Replaces reference renderCUDA (cuda_rasterizer/forward.cu:263-392).
+//
+// One CTA per 16x16 tile (the binning granularity is part of the bit-exact contract), 8 warps,
+// each warp owning an 8x4 pixel sub-rectangle.  Per batch of 256 sorted instances the CTA
+// gathers the 48-byte Gaussian records into shared memory with cp.async (double buffered, ids
+// prefetched one batch further ahead); every warp then culls the batch against ITS OWN 8x4
+// rectangle (one Gaussian per lane, exact-conservative ellipse/rectangle test, ballot) and
+// only walks the survivors.  The per-pixel arithmetic is the reference's rn-sequence, so
+// colour, depth, opacity, final_T, n_contrib and n_touched are unchanged by the culling.
+#include "common.cuh"
+#include "kernels.h"
+#include "render_common.cuh"
+
+namespace wgs {
+
+__global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__ RenderFwdParams p) {
+    __shared__ FwdStage st[2];
+    if (p.tile.misc[MISC_OVERFLOW]) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const int tx = tile % p.gx, ty = tile / p.gx;
+    const int wx0 = tx * WGS_TILE + (warp & 1) * 8, wy0 = ty * WGS_TILE + (warp >> 1) * 4;
+    const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
+    const bool inside = pxi < p.W && pyi < p.H;
+    const float pixx = (float)pxi, pixy = (float)pyi;
+    // this warp's pixel rectangle (clipped to the image) for culling
+    const float rx0 = (float)wx0, ry0 = (float)wy0;
+    const float rx1 = (float)min(wx0 + 7, p.W - 1), ry1 = (float)min(wy0 + 3, p.H - 1);
+    const bool warp_in_image = wx0 < p.W && wy0 < p.H;
+
+    const uint2 range = p.tile.ranges[tile];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + BATCH - 1) / BATCH;
+    const unsigned long long* __restrict__ list = p.bucket + range.x;
+
+    float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
+    uint32_t last_contributor = 0;
+    bool done = !inside;
+
+    // prologue: ids of batch 0 -> issue gathers; prefetch ids of batch 1
+    uint32_t id_next = 0;
+    if (tid < total) {
+        const uint32_t id = (uint32_t)list[tid];
+        st[0].id[tid] = id;
+        cp_async16(&st[0].rec0[tid], p.geom.rec + 2 * (size_t)id);
+        cp_async16(&st[0].rec1[tid], p.geom.rec + 2 * (size_t)id + 1);
+        cp_async16(&st[0].col[tid], p.geom.col + id);
+    }
+    cp_async_commit();
+    if (BATCH + tid < total) id_next = (uint32_t)list[BATCH + tid];
+
+    for (int r = 0; r < rounds; r++) {
+        const int buf = r & 1;
+        const int count = min(BATCH, total - r * BATCH);
+        cp_async_wait<0>();
+        // all threads done with buffer buf^1 (read in round r-1) and batch r visible
+        if (__syncthreads_and(done)) break;
+        if (r + 1 < rounds) {
+            const int k = (r + 1) * BATCH + tid;
+            if (k < total) {
+                FwdStage& nx = st[buf ^ 1];
+                nx.id[tid] = id_next;
+                cp_async16(&nx.rec0[tid], p.geom.rec + 2 * (size_t)id_next);
+                cp_async16(&nx.rec1[tid], p.geom.rec + 2 * (size_t)id_next + 1);
+                cp_async16(&nx.col[tid], p.geom.col + id_next);
+            }
+            if (k + BATCH < total) id_next = (uint32_t)list[k + BATCH];
+        }
+        cp_async_commit();
+        if (!warp_in_image || __all_sync(0xffffffffu, done)) continue;
+
+        const FwdStage& s = st[buf];
+        for (int c0 = 0; c0 < count; c0 += 32) {
+            const int mine = c0 + lane;
+            bool hit = false;
+            if (mine < count) {
+                const float4 a = s.rec0[mine];
+                const float4 b = s.rec1[mine];
+                hit = reaches_rect(a.x, a.y, a.z, a.w, b.x, b.w, rx0, ry0, rx1, ry1);
+            }
+            unsigned m = __ballot_sync(0xffffffffu, hit);
+            while (m) {
+                const int j = c0 + __ffs(m) - 1;
+                m &= m - 1;
+                const float4 a = s.rec0[j];
+                const float4 b = s.rec1[j];
+                bool contrib = false, touched = false;
+                float alpha = 0.f, test_T = 0.f;
+                if (!done) {
+                    const float dx = SUB(a.x, pixx), dy = SUB(a.y, pixy);
+                    const float power =
+                        FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
+                    if (!(power > 0.f)) {
+                        alpha = fminf(MUL(b.y, expf(power)), 0.99f);
+                        if (!(alpha < 1.0f / 255.0f)) {
+                            test_T = MUL(T, SUB(1.f, alpha));
+                            if (test_T < 0.0001f) done = true;
+                            else contrib = true;
+                        }
+                    }
+                }
+                if (contrib) {
+                    const float4 col = s.col[j];
+                    C0 = FMA(T, MUL(alpha, col.x), C0);
+                    C1 = FMA(T, MUL(alpha, col.y), C1);
+                    C2 = FMA(T, MUL(alpha, col.z), C2);
+                    D = FMA(T, MUL(alpha, b.z), D);
+                    touched = test_T > 0.5f;
+                    T = test_T;
+                    last_contributor = (uint32_t)(r * BATCH + j + 1);
+                }
+                const unsigned tm = __ballot_sync(0xffffffffu, touched);
+                if (tm && lane == 0) atomicAdd(p.n_touched + s.id[j], __popc(tm));
+                if (__all_sync(0xffffffffu, done)) { m = 0; c0 = count; }
+            }
+        }
+    }
+    cp_async_wait<0>();
+    if (inside) {
+        const size_t N = (size_t)p.W * p.H;
+        const size_t pix = (size_t)pyi * p.W + pxi;
+        p.image.final_T[pix] = T;
+        p.image.n_contrib[pix] = last_contributor;
+        p.out_color[pix] = FMA(T, __ldg(p.bg), C0);
+        p.out_color[N + pix] = FMA(T, __ldg(p.bg + 1), C1);
+        p.out_color[2 * N + pix] = FMA(T, __ldg(p.bg + 2), C2);
+        p.out_depth[pix] = D;
+        p.out_opacity[pix] = SUB(1.f, T);
+    }
+}
+
+void launch_render_fwd(const RenderFwdParams& p, cudaStream_t s) {
+    render_fwd_kernel<<<p.gx * p.gy, 256, 0, s>>>(p);
+}
+
+}  // namespace wgs

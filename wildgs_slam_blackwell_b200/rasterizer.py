@@ -1,0 +1,309 @@
+"""Host side of the drop-in: same names, argument order, outputs and error behaviour as the
+reference's thirdparty/diff-gaussian-rasterization-w-pose/diff_gaussian_rasterization/__init__.py
+(:21-46 rasterize_gaussians, :48-171 _RasterizeGaussians, :173-186 settings, :188-244 module),
+calling libwgs_rasterizer.so through ctypes instead of the pybind `_C` module.
+
+PyTorch is used for device memory, streams and autograd plumbing only.
+"""
+import ctypes as C
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    projmatrix_raw: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+def cpu_deep_copy_tuple(input_tuple):
+    return tuple(item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple)
+
+
+# ---- per-device host state: instance-capacity hint and the self-cleaning gradient workspace ----
+_capacity_hint = {}
+_grad_ws = {}
+
+
+def _ptr(t):
+    """Device pointer of a tensor; empty tensor == absent == NULL (reference convention)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32c(t, device):
+    """float32, contiguous, on `device`; empty stays empty."""
+    if t is None:
+        return None
+    if t.numel() == 0:
+        return t
+    if t.dtype != torch.float32 or t.device != device:
+        t = t.to(device=device, dtype=torch.float32)
+    return t.contiguous()
+
+
+def _empty_u8(nbytes, device):
+    return torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+
+
+def _stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _check(rc, what):
+    if rc != _lib.WGS_OK:
+        msg = _lib.last_error()
+        if rc == _lib.WGS_ERR_NO_COLOR_SOURCE:
+            raise RuntimeError("For non-RGB, provide precomputed Gaussian colors! (" + msg + ")")
+        raise RuntimeError(f"{what} failed ({rc}): {msg}")
+
+
+class ForwardState:
+    """What one forward leaves behind for its backward / for the parity exports."""
+    __slots__ = ("args", "geom", "tile", "binning", "image", "num_rendered", "keep")
+
+
+def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, s):
+    """Runs the forward through the C ABI.  Returns (color, radii, depth, opacity, n_touched, state)."""
+    if means3D.ndim != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("wildgs_slam_blackwell_b200: tensors must live on a CUDA (sm_100) device; "
+                           "there is no CPU path")
+    device = means3D.device
+    lib = _lib.load()
+    with torch.cuda.device(device):
+        ctx = _lib.context(device.index if device.index is not None else torch.cuda.current_device())
+        P = means3D.shape[0]
+        H, W = int(s.image_height), int(s.image_width)
+        means3D = _f32c(means3D, device)
+        sh = _f32c(sh, device)
+        colors_precomp = _f32c(colors_precomp, device)
+        opacities = _f32c(opacities, device)
+        scales = _f32c(scales, device)
+        rotations = _f32c(rotations, device)
+        cov3Ds_precomp = _f32c(cov3Ds_precomp, device)
+        bg = _f32c(s.bg, device)
+        view = _f32c(s.viewmatrix, device)
+        proj = _f32c(s.projmatrix, device)
+        campos = _f32c(s.campos, device)
+        M = int(sh.shape[1]) if (sh is not None and sh.numel() != 0) else 0
+
+        color = torch.empty((3, H, W), dtype=torch.float32, device=device)
+        depth = torch.empty((1, H, W), dtype=torch.float32, device=device)
+        opacity = torch.empty((1, H, W), dtype=torch.float32, device=device)
+        radii = torch.empty((P,), dtype=torch.int32, device=device)
+        n_touched = torch.empty((P,), dtype=torch.int32, device=device)
+
+        key = (device.index, W, H)
+        cap = max(_capacity_hint.get(key, 0), 4 * P, 1 << 16)
+        st = ForwardState()
+        a = _lib.ForwardArgs()
+        a.P, a.sh_degree, a.M, a.width, a.height = P, int(s.sh_degree), M, W, H
+        a.tanfovx, a.tanfovy, a.scale_modifier = float(s.tanfovx), float(s.tanfovy), float(s.scale_modifier)
+        a.prefiltered, a.debug = int(bool(s.prefiltered)), int(bool(s.debug))
+        a.background, a.means3D, a.sh, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors_precomp)
+        a.opacities, a.scales, a.rotations, a.cov3D_precomp = _ptr(opacities), _ptr(scales), _ptr(rotations), _ptr(cov3Ds_precomp)
+        a.viewmatrix, a.projmatrix, a.campos = _ptr(view), _ptr(proj), _ptr(campos)
+        a.out_color, a.out_depth, a.out_opacity = color.data_ptr(), depth.data_ptr(), opacity.data_ptr()
+        a.radii, a.n_touched = _ptr(radii), _ptr(n_touched)
+        R = C.c_int64(0)
+        stream = _stream_ptr(device)
+        while True:
+            ws = _lib.workspace_sizes(P, W, H, cap)
+            st.geom = _empty_u8(ws.geom_bytes, device)
+            st.tile = _empty_u8(ws.tile_bytes, device)
+            st.binning = _empty_u8(ws.binning_bytes, device)
+            st.image = _empty_u8(ws.image_bytes, device)
+            a.geom, a.tile, a.binning, a.image = (st.geom.data_ptr(), st.tile.data_ptr(), st.binning.data_ptr(),
+                                                  st.image.data_ptr())
+            a.capacity = cap
+            rc = lib.wgs_forward(ctx, C.byref(a), stream, C.byref(R))
+            if rc == _lib.WGS_ERR_CAPACITY:
+                cap = int(R.value * 1.25) + 1024
+                continue
+            _check(rc, "wgs_forward")
+            break
+        old = _capacity_hint.get(key, 0)
+        if not (R.value * 1.2 <= old <= R.value * 4):
+            _capacity_hint[key] = int(R.value * 1.5)
+        st.args = a
+        st.num_rendered = int(R.value)
+        # keep every tensor the argument block points at alive as long as the state lives
+        st.keep = (bg, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, view, proj, campos,
+                   color, depth, opacity, radii, n_touched)
+    return color, radii, depth, opacity, n_touched, st
+
+
+def _grad_workspace(device, P):
+    key = device.index
+    ent = _grad_ws.get(key)
+    nbytes = _lib.workspace_sizes(P, 16, 16, 0).grad_bytes
+    if ent is None or ent[0] != P:
+        ent = (P, torch.zeros(int(nbytes), dtype=torch.uint8, device=device))  # zero once; kernels re-zero
+        _grad_ws[key] = ent
+    return ent[1]
+
+
+def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii,
+                 grad_out_color, grad_out_depth):
+    """Runs the backward through the C ABI.  Returns dict of gradient tensors (+ 'tau' (6,))."""
+    device = means3D.device
+    lib = _lib.load()
+    with torch.cuda.device(device):
+        ctx = _lib.context(device.index if device.index is not None else torch.cuda.current_device())
+        P = means3D.shape[0]
+        H, W = int(s.image_height), int(s.image_width)
+        fa = st.args
+        M = fa.M
+        use_sh = M > 0 and not fa.colors_precomp
+        grad_out_color = _f32c(grad_out_color, device)
+        grad_out_depth = _f32c(grad_out_depth, device)
+        proj_raw = _f32c(s.projmatrix_raw, device)
+        e = lambda *shape: torch.empty(shape, dtype=torch.float32, device=device)
+        g = dict(means3D=e(P, 3), means2D=e(P, 3), opacity=e(P, 1), tau=e(6))
+        g["sh"] = e(P, M, 3) if use_sh else None
+        g["colors"] = e(P, 3) if fa.colors_precomp else None
+        g["scales"] = e(P, 3) if not fa.cov3D_precomp else None
+        g["rotations"] = e(P, 4) if not fa.cov3D_precomp else None
+        g["cov3D"] = e(P, 6) if fa.cov3D_precomp else None
+        b = _lib.BackwardArgs()
+        b.P, b.sh_degree, b.M, b.width, b.height = P, fa.sh_degree, M, W, H
+        b.tanfovx, b.tanfovy, b.scale_modifier, b.debug = fa.tanfovx, fa.tanfovy, fa.scale_modifier, fa.debug
+        b.background, b.means3D, b.sh, b.colors_precomp = fa.background, fa.means3D, fa.sh, fa.colors_precomp
+        b.scales, b.rotations, b.cov3D_precomp = fa.scales, fa.rotations, fa.cov3D_precomp
+        b.viewmatrix, b.projmatrix, b.projmatrix_raw, b.campos = fa.viewmatrix, fa.projmatrix, _ptr(proj_raw), fa.campos
+        b.radii = _ptr(radii)
+        b.dL_dout_color, b.dL_dout_depth = _ptr(grad_out_color), _ptr(grad_out_depth)
+        b.dL_dmeans3D, b.dL_dmeans2D, b.dL_dopacity = _ptr(g["means3D"]), _ptr(g["means2D"]), _ptr(g["opacity"])
+        b.dL_dsh, b.dL_dcolors = _ptr(g["sh"]), _ptr(g["colors"])
+        b.dL_dscales, b.dL_drotations, b.dL_dcov3D = _ptr(g["scales"]), _ptr(g["rotations"]), _ptr(g["cov3D"])
+        b.dL_dtau = _ptr(g["tau"])
+        b.geom, b.tile, b.binning, b.image = fa.geom, fa.tile, fa.binning, fa.image
+        b.capacity = fa.capacity
+        if P > 0:
+            b.grad = _grad_workspace(device, P).data_ptr()
+        rc = lib.wgs_backward(ctx, C.byref(b), _stream_ptr(device))
+        if rc != _lib.WGS_OK:
+            _grad_ws.pop(device.index, None)  # accumulators may be dirty
+        _check(rc, "wgs_backward")
+    return g
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        theta, rho, raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, theta, rho, raster_settings)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
+                raster_settings):
+        args = (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings)
+        if raster_settings.debug:
+            cpu_args = cpu_deep_copy_tuple(args[:-1] + tuple(raster_settings))
+            try:
+                color, radii, depth, opacity, n_touched, st = forward_raw(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_fw.dump")
+                print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+                raise ex
+        else:
+            color, radii, depth, opacity, n_touched, st = forward_raw(*args)
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = st.num_rendered
+        ctx.state = st
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh)
+        ctx.mark_non_differentiable(radii, n_touched)
+        return color, radii, depth, opacity, n_touched
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_radii, grad_out_depth, grad_out_opacity, grad_n_touched):
+        # grad_out_opacity is ignored exactly like the reference (__init__.py:108-138)
+        s = ctx.raster_settings
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh = ctx.saved_tensors
+        if grad_out_color is None:
+            grad_out_color = torch.zeros((3, s.image_height, s.image_width), device=means3D.device)
+        if grad_out_depth is None:
+            grad_out_depth = torch.zeros((1, s.image_height, s.image_width), device=means3D.device)
+        args = (ctx.state, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii, grad_out_color,
+                grad_out_depth)
+        if s.debug:
+            cpu_args = cpu_deep_copy_tuple(args[2:] + tuple(s))
+            try:
+                g = backward_raw(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_bw.dump")
+                print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+                raise ex
+        else:
+            g = backward_raw(*args)
+        grad_rho = g["tau"][:3].view(1, -1)
+        grad_theta = g["tau"][3:].view(1, -1)
+        return (g["means3D"], g["means2D"], g["sh"], g["colors"], g["opacity"], g["scales"], g["rotations"],
+                g["cov3D"], grad_theta, grad_rho, None)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        # reference: __init__.py:193-202 -> _C.mark_visible (rasterize_points.cu:213-232)
+        with torch.no_grad():
+            s = self.raster_settings
+            if not positions.is_cuda:
+                raise RuntimeError("wildgs_slam_blackwell_b200: positions must be a CUDA tensor")
+            device = positions.device
+            pos = _f32c(positions, device)
+            view, proj = _f32c(s.viewmatrix, device), _f32c(s.projmatrix, device)
+            P = pos.shape[0]
+            visible = torch.zeros((P,), dtype=torch.bool, device=device)
+            if P:
+                with torch.cuda.device(device):
+                    rc = _lib.load().wgs_mark_visible(P, pos.data_ptr(), view.data_ptr(), proj.data_ptr(),
+                                                      visible.data_ptr(), _stream_ptr(device))
+                _check(rc, "wgs_mark_visible")
+        return visible
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None, theta=None, rho=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        if shs is None:
+            shs = torch.Tensor([])
+        if colors_precomp is None:
+            colors_precomp = torch.Tensor([])
+        if scales is None:
+            scales = torch.Tensor([])
+        if rotations is None:
+            rotations = torch.Tensor([])
+        if cov3D_precomp is None:
+            cov3D_precomp = torch.Tensor([])
+        if theta is None:
+            theta = torch.Tensor([])
+        if rho is None:
+            rho = torch.Tensor([])
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                                   theta, rho, raster_settings)
