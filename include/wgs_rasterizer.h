@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define WGS_ABI_VERSION 4
+#define WGS_ABI_VERSION 5
 
 /* status codes (negative = error) */
 #define WGS_OK 0
@@ -170,6 +170,17 @@ int wgs_export_binning(const WgsForwardArgs* args, int64_t num_rendered,
  * clamped (3P bytes).  Entries of culled Gaussians (radii==0) are written as 0. */
 int wgs_export_geometry(const WgsForwardArgs* args, float* depths, float* means2D,
                         float* conic_opacity, float* rgb, uint8_t* clamped, void* cuda_stream);
+
+/* Stage timing for the roofline report (no reference counterpart: the reference has no timers,
+ * SURVEY.md §5).  When enabled, wgs_forward/wgs_backward bracket every stage with CUDA events
+ * on the caller's stream; wgs_stage_times() synchronises on the last event and returns the
+ * device time of each stage of the most recent forward (+ backward) in milliseconds:
+ *   [0] preprocess_fwd  [1] tile_scan  [2] scatter  [3] tile_sort (small+large)
+ *   [4] render_fwd      [5] render_bwd [6] preprocess_bwd   [7] reserved (0)
+ * Stages that did not run since the last call report 0. */
+#define WGS_NUM_STAGES 8
+int wgs_stage_timing(WgsContext* ctx, int enable);
+int wgs_stage_times(WgsContext* ctx, float* ms_out /* WGS_NUM_STAGES floats, host */);
 
 #ifdef __cplusplus
 }

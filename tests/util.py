@@ -89,6 +89,7 @@ def export_state(g, cam, colors=None, cov=None, dev="cuda:0"):
     scales = e if cov is not None else to_dev(g["scales"], dev)
     rots = e if cov is not None else to_dev(g["rotations"], dev)
     covt = e if cov is None else to_dev(cov, dev)
+    # (outputs are held by these names until the exports below have run)
     color, radii, depth, opacity, n_touched, st = rasterizer.forward_raw(
         to_dev(g["means3D"], dev), sh, col, to_dev(g["opacities"], dev), scales, rots, covt, s)
     P = g["means3D"].shape[0]

@@ -5,7 +5,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libwgs_rasterizer.so")
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 WGS_OK = 0
 WGS_ERR_INVALID_ARGUMENT = -1
@@ -52,7 +52,10 @@ class BackwardArgs(C.Structure):
 
 EXPORTS = ("wgs_abi_version", "wgs_last_error", "wgs_context_create", "wgs_context_destroy",
            "wgs_workspace_sizes", "wgs_forward", "wgs_backward", "wgs_mark_visible", "wgs_export_binning",
-           "wgs_export_geometry")
+           "wgs_export_geometry", "wgs_stage_timing", "wgs_stage_times")
+NUM_STAGES = 8
+STAGE_NAMES = ("preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd", "render_bwd", "preprocess_bwd",
+               "reserved")
 
 _lib = None
 _contexts = {}
@@ -79,6 +82,8 @@ def load():
     lib.wgs_mark_visible.argtypes = [C.c_int32, _fp, _fp, _fp, _fp, C.c_void_p]
     lib.wgs_export_binning.argtypes = [C.POINTER(ForwardArgs), C.c_int64, _fp, _fp, _fp, _fp, _fp, C.c_void_p]
     lib.wgs_export_geometry.argtypes = [C.POINTER(ForwardArgs), _fp, _fp, _fp, _fp, _fp, C.c_void_p]
+    lib.wgs_stage_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.wgs_stage_times.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     if lib.wgs_abi_version() != ABI_VERSION:
         raise RuntimeError(f"libwgs_rasterizer.so ABI {lib.wgs_abi_version()} != expected {ABI_VERSION}; rebuild")
     _lib = lib
@@ -107,3 +112,18 @@ def workspace_sizes(P, W, H, capacity):
     if rc != WGS_OK:
         raise RuntimeError(last_error())
     return ws
+
+
+def stage_timing(device_index, enable):
+    rc = load().wgs_stage_timing(context(device_index), int(bool(enable)))
+    if rc != WGS_OK:
+        raise RuntimeError(last_error())
+
+
+def stage_times(device_index):
+    """dict stage name -> ms of the most recent forward(+backward); synchronises."""
+    buf = (C.c_float * NUM_STAGES)()
+    rc = load().wgs_stage_times(context(device_index), buf)
+    if rc != WGS_OK:
+        raise RuntimeError(last_error())
+    return {n: float(buf[i]) for i, n in enumerate(STAGE_NAMES) if n != "reserved"}

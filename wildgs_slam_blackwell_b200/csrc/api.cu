@@ -18,6 +18,10 @@ struct WgsContext {
     unsigned int* host_R = nullptr;  // pinned + mapped
     unsigned int* dev_R = nullptr;   // device alias of host_R
     cudaEvent_t ev_R = nullptr;
+    // stage timing (wgs_stage_timing): fwd boundaries 0..5, bwd boundaries 6..8
+    bool timing = false;
+    bool fwd_timed = false, bwd_timed = false;
+    cudaEvent_t ev_stage[9] = {};
 };
 
 namespace {
@@ -34,6 +38,10 @@ void set_err(const char* what, cudaError_t e) {
         }                                         \
     } while (0)
 // CHECK_CUDA(A, debug) of the reference (auxiliary.h:166-173)
+#define MARK(ctx, i, stream)                                       \
+    do {                                                           \
+        if ((ctx)->timing) CK(cudaEventRecord((ctx)->ev_stage[i], stream)); \
+    } while (0)
 #define STAGE(debug, stream, name)                                 \
     do {                                                           \
         cudaError_t e_ = cudaGetLastError();                       \
@@ -81,6 +89,8 @@ WgsContext* wgs_context_create(int device) {
 void wgs_context_destroy(WgsContext* c) {
     if (!c) return;
     if (c->ev_R) cudaEventDestroy(c->ev_R);
+    for (cudaEvent_t e : c->ev_stage)
+        if (e) cudaEventDestroy(e);
     if (c->host_R) cudaFreeHost(c->host_R);
     delete c;
 }
@@ -151,8 +161,10 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     pp.opacities = a->opacities; pp.scales = a->scales; pp.rotations = a->rotations; pp.cov3D_precomp = a->cov3D_precomp;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
     pp.radii = a->radii; pp.n_touched = a->n_touched; pp.geom = geom; pp.tile = tile;
+    MARK(ctx, 0, s);
     launch_preprocess_fwd(pp, s);
     STAGE(a->debug, s, "preprocess_fwd");
+    MARK(ctx, 1, s);
 
     BinParams bp;
     bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.capacity = a->capacity;
@@ -160,8 +172,12 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     launch_tile_scan(bp, s);
     CK(cudaEventRecord(ctx->ev_R, s));
     STAGE(a->debug, s, "tile_scan");
-    launch_binning(bp, ctx->num_sms, s);
+    MARK(ctx, 2, s);
+    launch_scatter(bp, s);
+    MARK(ctx, 3, s);
+    launch_tile_sorts(bp, ctx->num_sms, s);
     STAGE(a->debug, s, "binning");
+    MARK(ctx, 4, s);
 
     RenderFwdParams rp;
     rp.W = a->width; rp.H = a->height; rp.gx = gx; rp.gy = gy; rp.bg = a->background;
@@ -170,6 +186,8 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     rp.n_touched = a->n_touched;
     launch_render_fwd(rp, s);
     STAGE(a->debug, s, "render_fwd");
+    MARK(ctx, 5, s);
+    ctx->fwd_timed = ctx->timing;
 
     // Everything is enqueued; now wait for R only (the GPU keeps running the later stages).
     CK(cudaEventSynchronize(ctx->ev_R));
@@ -216,8 +234,10 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     rb.W = a->width; rb.H = a->height; rb.gx = gx; rb.gy = gy; rb.bg = a->background;
     rb.geom = geom; rb.tile = tile; rb.image = image; rb.bucket = (const unsigned long long*)a->binning;
     rb.dL_dcolor = a->dL_dout_color; rb.dL_ddepth = a->dL_dout_depth; rb.grad = grad;
+    MARK(ctx, 6, s);
     launch_render_bwd(rb, s);
     STAGE(a->debug, s, "render_bwd");
+    MARK(ctx, 7, s);
 
     PreBwdParams pb;
     pb.P = a->P; pb.D = a->sh_degree; pb.M = a->M; pb.W = a->width; pb.H = a->height;
@@ -234,6 +254,35 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     pb.dL_drotations = a->dL_drotations; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dtau = a->dL_dtau;
     launch_preprocess_bwd(pb, s);
     STAGE(a->debug, s, "preprocess_bwd");
+    MARK(ctx, 8, s);
+    ctx->bwd_timed = ctx->timing;
+    return WGS_OK;
+}
+
+int wgs_stage_timing(WgsContext* ctx, int enable) {
+    if (!ctx) { set_err("wgs_stage_timing: null context", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    if (enable) {
+        for (cudaEvent_t& e : ctx->ev_stage)
+            if (!e) CK(cudaEventCreate(&e));
+    }
+    ctx->timing = enable != 0;
+    ctx->fwd_timed = ctx->bwd_timed = false;
+    return WGS_OK;
+}
+
+int wgs_stage_times(WgsContext* ctx, float* ms) {
+    if (!ctx || !ms) { set_err("wgs_stage_times: null argument", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    for (int i = 0; i < WGS_NUM_STAGES; i++) ms[i] = 0.f;
+    if (ctx->fwd_timed) {
+        CK(cudaEventSynchronize(ctx->ev_stage[5]));
+        for (int i = 0; i < 5; i++) CK(cudaEventElapsedTime(ms + i, ctx->ev_stage[i], ctx->ev_stage[i + 1]));
+    }
+    if (ctx->bwd_timed) {
+        CK(cudaEventSynchronize(ctx->ev_stage[8]));
+        CK(cudaEventElapsedTime(ms + 5, ctx->ev_stage[6], ctx->ev_stage[7]));
+        CK(cudaEventElapsedTime(ms + 6, ctx->ev_stage[7], ctx->ev_stage[8]));
+    }
+    ctx->fwd_timed = ctx->bwd_timed = false;
     return WGS_OK;
 }
 

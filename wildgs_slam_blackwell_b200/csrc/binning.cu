@@ -204,8 +204,11 @@ __global__ void export_geometry_kernel(int P, GeomView g, const int* radii, floa
 
 void launch_tile_scan(const BinParams& p, cudaStream_t s) { tile_scan_kernel<<<1, 1024, 0, s>>>(p); }
 
-void launch_binning(const BinParams& p, int num_sms, cudaStream_t s) {
+void launch_scatter(const BinParams& p, cudaStream_t s) {
     if (p.P > 0) scatter_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p);
+}
+
+void launch_tile_sorts(const BinParams& p, int num_sms, cudaStream_t s) {
     tile_sort_small_kernel<<<p.tiles, SMALL_THREADS, 0, s>>>(p);
     tile_sort_large_kernel<<<num_sms, LARGE_THREADS, LARGE_MAX * 8, s>>>(p);
 }

@@ -62,7 +62,8 @@ struct PreBwdParams {
 void launch_preprocess_fwd(const PreFwdParams& p, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s);
 void launch_tile_scan(const BinParams& p, cudaStream_t s);   // ranges + R
-void launch_binning(const BinParams& p, int num_sms, cudaStream_t s);  // scatter + per-tile sorts
+void launch_scatter(const BinParams& p, cudaStream_t s);
+void launch_tile_sorts(const BinParams& p, int num_sms, cudaStream_t s);
 void launch_render_fwd(const RenderFwdParams& p, cudaStream_t s);
 void launch_render_bwd(const RenderBwdParams& p, cudaStream_t s);
 void launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s);

@@ -144,9 +144,11 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
             _capacity_hint[key] = int(R.value * 1.5)
         st.args = a
         st.num_rendered = int(R.value)
-        # keep every tensor the argument block points at alive as long as the state lives
-        st.keep = (bg, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, view, proj, campos,
-                   color, depth, opacity, radii, n_touched)
+        # Keep every INPUT the argument block points at alive as long as the state lives.  The
+        # outputs are deliberately not held: under autograd they carry grad_fn -> ctx -> state, and
+        # holding them here would close a reference cycle that only the cyclic GC frees (workspaces
+        # would pile up and every forward would hit cudaMalloc).
+        st.keep = (bg, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, view, proj, campos)
     return color, radii, depth, opacity, n_touched, st
 
 
