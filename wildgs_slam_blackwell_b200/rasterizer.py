@@ -229,6 +229,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         else:
             color, radii, depth, opacity, n_touched, st = forward_raw(*args)
         ctx.raster_settings = raster_settings
+        # radii / opacity / n_touched cotangents are never used (reference ignores them too):
+        # do not let autograd zero-fill them
+        ctx.set_materialize_grads(False)
+        ctx.pose_shapes = (theta.shape, rho.shape)
         ctx.num_rendered = st.num_rendered
         ctx.state = st
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh)
@@ -256,8 +260,11 @@ class _RasterizeGaussians(torch.autograd.Function):
                 raise ex
         else:
             g = backward_raw(*args)
-        grad_rho = g["tau"][:3].view(1, -1)
-        grad_theta = g["tau"][3:].view(1, -1)
+        # The reference returns (1,3) for both and lets autograd sum_to_size them onto the leaves;
+        # hand autograd the leaf's own shape when it has 3 elements (same .grad, no reduce kernel).
+        th_shape, rho_shape = ctx.pose_shapes
+        grad_rho = g["tau"][:3].view(rho_shape if len(rho_shape) and rho_shape.numel() == 3 else (1, 3))
+        grad_theta = g["tau"][3:].view(th_shape if len(th_shape) and th_shape.numel() == 3 else (1, 3))
         return (g["means3D"], g["means2D"], g["sh"], g["colors"], g["opacity"], g["scales"], g["rotations"],
                 g["cov3D"], grad_theta, grad_rho, None)
 
