@@ -1,0 +1,106 @@
+"""CPU (no GPU): the C-ABI library builds/loads and exports every symbol include/wgs_rasterizer.h declares;
+the ctypes structs mirror the header; host-side validation behaves like the reference's front-end
+(RAST/diff_gaussian_rasterization/__init__.py:204-228); there is no CPU fallback."""
+import ctypes as C
+import os
+import re
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from wildgs_slam_blackwell_b200 import _lib, rasterizer  # noqa: E402
+
+HEADER = open(os.path.join(ROOT, "include", "wgs_rasterizer.h")).read()
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    declared = set(re.findall(r"\b(wgs_[a-z_]+)\s*\(", HEADER))
+    assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
+    for name in declared:
+        assert hasattr(lib, name), name
+    m = re.search(r"#define WGS_ABI_VERSION (\d+)", HEADER)
+    assert lib.wgs_abi_version() == int(m.group(1)) == _lib.ABI_VERSION
+
+
+def _struct_fields(name):
+    body = re.search(r"typedef struct " + name + r" \{(.*?)\} " + name + ";", HEADER, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        for part in decl.split(","):
+            names.append(re.findall(r"[A-Za-z_0-9]+", part)[-1])
+    return names
+
+
+@pytest.mark.parametrize("cname,cls", [("WgsForwardArgs", _lib.ForwardArgs), ("WgsBackwardArgs", _lib.BackwardArgs),
+                                       ("WgsWorkspaceSizes", _lib.WorkspaceSizes)])
+def test_ctypes_structs_mirror_header(cname, cls):
+    assert _struct_fields(cname) == [f[0] for f in cls._fields_]
+
+
+def test_workspace_sizes_and_argument_errors_without_gpu():
+    ws = _lib.workspace_sizes(300_000, 640, 480, 1_200_000)
+    assert ws.geom_bytes >= 300_000 * 57 and ws.binning_bytes >= 1_200_000 * 8
+    assert ws.image_bytes >= 640 * 480 * 8 and ws.grad_bytes >= 300_000 * 48 and ws.tile_bytes >= 1200 * 20
+    out = _lib.WorkspaceSizes()
+    assert _lib.load().wgs_workspace_sizes(-1, 640, 480, 0, C.byref(out)) == _lib.WGS_ERR_INVALID_ARGUMENT
+    assert b"invalid" in _lib.load().wgs_last_error()
+    assert _lib.load().wgs_forward(None, None, None, None) == _lib.WGS_ERR_INVALID_ARGUMENT
+    assert _lib.load().wgs_backward(None, None, None) == _lib.WGS_ERR_INVALID_ARGUMENT
+    if not torch.cuda.is_available():
+        assert not _lib.load().wgs_context_create(0)          # no device -> null + message, never a fallback
+        assert _lib.last_error()
+
+
+def _settings():
+    z = torch.zeros(4, 4)
+    return rasterizer.GaussianRasterizationSettings(16, 16, 1.0, 1.0, torch.zeros(3), 1.0, z, z, z, 0, torch.zeros(3),
+                                                    False, False)
+
+
+def test_settings_field_order_matches_reference():
+    assert rasterizer.GaussianRasterizationSettings._fields == (
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+        "projmatrix_raw", "sh_degree", "campos", "prefiltered", "debug")
+
+
+def test_front_end_validation_messages():
+    r = rasterizer.GaussianRasterizer(_settings())
+    m = torch.zeros(4, 3)
+    with pytest.raises(Exception, match="Please provide excatly one of either SHs or precomputed colors!"):
+        r(m, m, torch.zeros(4, 1), scales=m, rotations=torch.zeros(4, 4))
+    with pytest.raises(Exception, match="Please provide excatly one"):
+        r(m, m, torch.zeros(4, 1), shs=torch.zeros(4, 1, 3), colors_precomp=m, scales=m, rotations=torch.zeros(4, 4))
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair or precomputed 3D covariance"):
+        r(m, m, torch.zeros(4, 1), shs=torch.zeros(4, 1, 3))
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair"):
+        r(m, m, torch.zeros(4, 1), shs=torch.zeros(4, 1, 3), scales=m, rotations=torch.zeros(4, 4),
+          cov3D_precomp=torch.zeros(4, 6))
+
+
+def test_no_cpu_fallback():
+    r = rasterizer.GaussianRasterizer(_settings())
+    m = torch.zeros(4, 3)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        r(m, m, torch.zeros(4, 1), shs=torch.zeros(4, 1, 3), scales=m, rotations=torch.zeros(4, 4))
+    with pytest.raises(RuntimeError, match="must have dimensions"):
+        rasterizer.forward_raw(torch.zeros(4, 2), None, None, None, None, None, None, _settings())
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        r.markVisible(m)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "wildgs_slam_blackwell_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.replace("the oracle", ""), f
+    assert "oracle" not in open(os.path.join(ROOT, "diff_gaussian_rasterization", "__init__.py")).read()

@@ -1,0 +1,122 @@
+"""CPU, world_size 2 over gloo: the mapping-window host logic (view->rank assignment, gradient bucket,
+allreduce, per-view pose gradients).  The rasterizer itself has no CPU path, so a stand-in
+differentiable "render" produces per-view losses with the same call structure."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from wildgs_slam_blackwell_b200.window import GradBucket, WindowTrainer, assign_views  # noqa: E402
+
+N_VIEWS, P = 5, 37
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _params(seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return {"means3D": torch.randn(P, 3, generator=g).requires_grad_(True),
+            "opacity": torch.rand(P, 1, generator=g).requires_grad_(True),
+            "sh": torch.randn(P, 1, 3, generator=g).requires_grad_(True)}
+
+
+def _make_render(params):
+    poses = [torch.zeros(6, requires_grad=True) for _ in range(N_VIEWS)]
+
+    def render_loss(v):
+        w = torch.linspace(0.5, 1.5, P).view(P, 1) * (v + 1)
+        poses[v].grad = None
+        img = (params["means3D"] * w).sum(1, keepdim=True) * params["opacity"] + params["sh"].view(P, 3).mean(1, keepdim=True)
+        loss = (img ** 2).mean() + (poses[v] * torch.arange(6.0) * (v + 1)).sum() * img.mean().detach()
+        return loss, (lambda: poses[v].grad)
+    return render_loss
+
+
+def _single_process_reference():
+    params = _params()
+    render = _make_render(params)
+    losses, pose = [], []
+    for v in range(N_VIEWS):
+        loss, pg = render(v)
+        loss.backward()
+        losses.append(loss.detach())
+        pose.append(pg().clone())
+    return {k: p.grad.clone() for k, p in params.items()}, torch.stack(losses), torch.stack(pose)
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        params = _params()
+        tr = WindowTrainer(params)
+        render = _make_render(params)
+        costs = {0: 5.0, 1: 1.0, 2: 3.0, 3: 3.0, 4: 2.0}
+        out1 = tr.step(N_VIEWS, render, cost_fn=lambda v: costs[v])
+        g1 = {k: p.grad.clone() for k, p in params.items()}
+        out2 = tr.step(N_VIEWS, render, cost_fn=lambda v: costs[v])   # second step: cost-balanced assignment
+        g2 = {k: p.grad.clone() for k, p in params.items()}
+        torch.save((rank, g1, g2, out1["losses"].clone(), out1["pose_grads"].clone(), out1["assignment"],
+                    out2["assignment"], out2["pose_grads"].clone()), os.path.join(q, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_window_step_world2_matches_single_process(tmp_path):
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, str(tmp_path))) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    res = [torch.load(tmp_path / f"rank{r}.pt") for r in range(2)]
+    ref_g, ref_l, ref_p = _single_process_reference()
+    for rank, g1, g2, losses, pose, a1, a2, pose2 in res:
+        for k in ref_g:
+            torch.testing.assert_close(g1[k], ref_g[k], rtol=1e-5, atol=1e-6)   # sum over ALL views on every rank
+            torch.testing.assert_close(g2[k], ref_g[k], rtol=1e-5, atol=1e-6)   # independent of the assignment
+        torch.testing.assert_close(losses, ref_l, rtol=1e-6, atol=1e-7)
+        torch.testing.assert_close(pose, ref_p, rtol=1e-6, atol=1e-7)           # per view, NOT summed
+        torch.testing.assert_close(pose2, ref_p, rtol=1e-6, atol=1e-7)
+        assert sorted(a1[0] + a1[1]) == list(range(N_VIEWS))
+        assert a1 == [[0, 2, 4], [1, 3]]                       # uniform costs: round-robin by LPT
+        loads = [sum({0: 5.0, 1: 1.0, 2: 3.0, 3: 3.0, 4: 2.0}[v] for v in part) for part in a2]
+        assert max(loads) == 7.0 and sorted(a2[0] + a2[1]) == list(range(N_VIEWS))
+    assert res[0][5] == res[1][5] and res[0][6] == res[1][6]   # every rank computes the same assignment
+
+
+def test_assign_views_properties():
+    assert assign_views([], 4) == [[], [], [], []]
+    assert assign_views([1, 1, 1], 1) == [[0, 1, 2]]
+    a = assign_views([10, 1, 1, 1, 1, 1, 1, 1, 1, 1], 8)      # config 3: 10 keyframes on 8 GPUs
+    assert sorted(sum(a, [])) == list(range(10)) and max(len(x) for x in a) == 2 and a[0] == [0]
+    a16 = assign_views([1.0] * 16, 8)                          # config 5 divides evenly
+    assert all(len(x) == 2 for x in a16)
+
+
+def test_grad_bucket_layout_and_accumulation():
+    params = _params()
+    b = GradBucket(params)
+    assert b.flat.numel() == P * 3 + P + P * 3 and b.nbytes == 4 * b.flat.numel()
+    b.install()
+    (params["means3D"].sum() * 2).backward()
+    (params["means3D"].sum() * 3).backward()                   # accumulates in place into the bucket
+    assert params["means3D"].grad.data_ptr() == b.flat.data_ptr()
+    torch.testing.assert_close(b.flat[:P * 3], torch.full((P * 3,), 5.0))
+    assert not b.flat[P * 3:].any()
+    assert b.matches(params) and not b.matches({"means3D": params["means3D"]})
+    with pytest.raises(TypeError):
+        GradBucket({"x": torch.zeros(3, dtype=torch.float64)})

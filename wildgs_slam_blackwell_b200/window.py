@@ -1,0 +1,118 @@
+"""Multi-GPU mapping window: views sharded over ranks, Gaussian gradients summed with one allreduce.
+
+New capability (the reference renders ONE keyframe per optimiser step on one GPU,
+src/mapper.py:1083-1093, and has no distributed code).  Semantics: the window gradient
+is the sum over views of the per-view gradient the reference would have produced; per-view pose
+gradients (rho/theta of each keyframe) are not summed, they are returned per view to every rank.
+
+One process per GPU (torchrun); Gaussian parameters are replicated; `torch.distributed` (NCCL over
+NVLink on GPUs, gloo in the CPU tests) is the plumbing.  Nothing here touches the rasterizer's
+arithmetic: `render_loss` is whatever the caller renders with (the drop-in GaussianRasterizer).
+"""
+from typing import Callable, Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def assign_views(costs: Sequence[float], world: int) -> List[List[int]]:
+    """Longest-processing-time-first assignment of views to ranks.  `costs[v]` is any per-view cost
+    estimate (the previous step's num_rendered is a good one); ties and equal loads resolve to the
+    lowest rank / lowest view index, so every rank computes the same assignment."""
+    world = max(int(world), 1)
+    order = sorted(range(len(costs)), key=lambda v: (-float(costs[v]), v))
+    load = [0.0] * world
+    out: List[List[int]] = [[] for _ in range(world)]
+    for v in order:
+        r = min(range(world), key=lambda i: (load[i], i))
+        out[r].append(v)
+        load[r] += max(float(costs[v]), 1e-9)
+    for lst in out:
+        lst.sort()
+    return out
+
+
+class GradBucket:
+    """One flat fp32 buffer holding the gradients of all replicated leaves back to back, plus
+    per-leaf views into it.  Installing the views as `.grad` makes autograd accumulate straight into
+    the buffer, so the allreduce needs no packing copy."""
+
+    def __init__(self, params: Dict[str, torch.Tensor]):
+        self.names = list(params)
+        self.params = params
+        n = sum(p.numel() for p in params.values())
+        first = next(iter(params.values()))
+        self.flat = torch.zeros(n, dtype=torch.float32, device=first.device)
+        self.views: Dict[str, torch.Tensor] = {}
+        off = 0
+        for k, p in params.items():
+            if p.dtype != torch.float32:
+                raise TypeError(f"GradBucket: leaf {k} must be float32")
+            self.views[k] = self.flat[off:off + p.numel()].view(p.shape)
+            off += p.numel()
+
+    def matches(self, params: Dict[str, torch.Tensor]) -> bool:
+        return list(params) == self.names and all(params[k].shape == self.views[k].shape and
+                                                  params[k].device == self.flat.device for k in params)
+
+    def install(self):
+        """Zero the buffer and point every leaf's .grad at its slice."""
+        self.flat.zero_()
+        for k, p in self.params.items():
+            p.grad = self.views[k]
+
+    @property
+    def nbytes(self) -> int:
+        return self.flat.numel() * 4
+
+
+class WindowTrainer:
+    """Drives one window step.
+
+        trainer = WindowTrainer(params)                  # params: name -> leaf tensor (requires_grad)
+        out = trainer.step(n_views, render_loss)         # render_loss(v) -> (loss, pose_grad_fn)
+
+    `render_loss(v)` renders view v against the replicated parameters and returns a scalar loss plus
+    either None or a callable returning that view's pose gradient (6,) AFTER backward.  After step():
+    every leaf's .grad holds the gradient summed over ALL views of the window (identical on every
+    rank), `out["losses"]` (n_views,), `out["pose_grads"]` (n_views, 6), `out["assignment"]`.
+    """
+
+    def __init__(self, params: Dict[str, torch.Tensor], group: Optional[dist.ProcessGroup] = None):
+        self.group = group
+        self.distributed = dist.is_available() and dist.is_initialized()
+        self.world = dist.get_world_size(group) if self.distributed else 1
+        self.rank = dist.get_rank(group) if self.distributed else 0
+        self.bucket = GradBucket(params)
+        self.costs: List[float] = []
+
+    def rebind(self, params: Dict[str, torch.Tensor]):
+        """Call after densify/prune changed the number of Gaussians."""
+        if not self.bucket.matches(params):
+            self.bucket = GradBucket(params)
+        else:
+            self.bucket.params = params
+
+    def step(self, n_views: int, render_loss: Callable, cost_fn: Optional[Callable[[int], float]] = None):
+        if len(self.costs) != n_views:
+            self.costs = [1.0] * n_views
+        assignment = assign_views(self.costs, self.world)
+        mine = assignment[self.rank]
+        b = self.bucket
+        b.install()
+        dev = b.flat.device
+        side = torch.zeros(n_views, 8, dtype=torch.float32, device=dev)  # loss, cost, pose grad (6)
+        for v in mine:
+            loss, pose_grad_fn = render_loss(v)
+            loss.backward()
+            side[v, 0] = loss.detach()
+            side[v, 1] = float(cost_fn(v)) if cost_fn is not None else 1.0
+            if pose_grad_fn is not None:
+                side[v, 2:8] = pose_grad_fn().reshape(6)
+        if self.world > 1:
+            work = dist.all_reduce(b.flat, group=self.group, async_op=True)
+            dist.all_reduce(side, group=self.group)
+            work.wait()
+        self.costs = [float(c) for c in side[:, 1].tolist()]
+        return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": assignment,
+                "bucket_bytes": b.nbytes}
