@@ -1,0 +1,205 @@
+"""GPU: behaviour of the drop-in API and the C ABI beyond the golden scenes — edge cases (empty scene,
+capacity overflow + retry, ragged image sizes, markVisible), parity with the CPU oracle on config 1,
+parity with the UNMODIFIED reference (oracle/_ref, when it travelled to the box) at config-2 size, and
+size-independent properties at BASELINE.json's full size."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import util
+from oracle import cpu_oracle
+from oracle.ref_cuda import ref_api
+from wildgs_slam_blackwell_b200 import rasterizer, scenes
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def test_config1_matches_cpu_oracle():
+    g, cams, cots = scenes.make_scene("config1")
+    ours = util.run_ours(g, cams[0], cots[0])
+    o = cpu_oracle.forward_backward(g, cams[0], cots[0], export=True)
+    np.testing.assert_array_equal(ours["radii"], o["radii"])
+    assert int(ours["num_rendered"]) == int(o["num_rendered"])
+    np.testing.assert_array_equal(ours["st_point_list"].view(np.uint32), o["st_point_list"])
+    np.testing.assert_array_equal(ours["st_ranges"].view(np.uint32), o["st_ranges"])
+    np.testing.assert_array_equal(util.bits(ours["st_depths"]), util.bits(o["st_depths"]))
+    assert (ours["st_n_contrib"].view(np.uint32) != o["st_n_contrib"]).mean() < 2e-3     # host expf vs CUDA expf
+    for k in ("color", "depth", "opacity"):
+        bad = np.abs(ours[k] - o[k]) > 1e-4 * np.abs(o[k]) + 1e-6
+        assert bad.mean() < 2e-3, k
+    util.assert_grad_close("tau", ours["g_dL_dtau_sum"], o["dL_dtau"], rtol=2e-3, atol_scale=2e-4)
+    for a, b in (("g_dL_dmeans3D", "g_dL_dmeans3D"), ("g_dL_dopacity", "g_dL_dopacity"), ("g_dL_dscales", "g_dL_dscales"),
+                 ("g_dL_drotations", "g_dL_drotations"), ("g_dL_dsh", "g_dL_dsh")):
+        ref = o[b]
+        bad = np.abs(ours[a] - ref) > 1e-3 * np.abs(ref) + 1e-4 * np.abs(ref).max()
+        assert bad.mean() < 2e-3, a
+
+
+def test_empty_scene_is_background():
+    cam = scenes.make_camera(70, 50, 3, bg=(0.2, 0.4, 0.6))
+    s = util.settings_from_cam(cam, 0)
+    rast = rasterizer.GaussianRasterizer(s)
+    z = lambda *sh: torch.zeros(*sh, device=DEV)
+    color, radii, depth, opacity, n_touched = rast(z(0, 3), z(0, 3), z(0, 1), shs=z(0, 1, 3), scales=z(0, 3), rotations=z(0, 4))
+    for c in range(3):
+        assert torch.all(color[c] == cam["bg"][c])
+    assert not depth.any() and not opacity.any() and radii.numel() == 0 and n_touched.numel() == 0
+
+
+def test_capacity_overflow_retries_and_matches_oracle():
+    g, cams, cots = scenes.make_scene(3000, 200, 120, 0, seed=21)
+    g["scales"] = g["scales"] * 12.0                      # huge splats: R >> 4P and >> the 65536 floor
+    o = cpu_oracle.forward_backward(g, cams[0], cots[0], export=True)
+    assert int(o["num_rendered"]) > max(4 * 3000, 1 << 16)
+    rasterizer._capacity_hint.clear()
+    ours = util.run_ours(g, cams[0], cots[0])
+    assert int(ours["num_rendered"]) == int(o["num_rendered"])
+    np.testing.assert_array_equal(ours["radii"], o["radii"])
+    np.testing.assert_array_equal(ours["st_point_list"].view(np.uint32), o["st_point_list"])
+    util.assert_grad_close("tau", ours["g_dL_dtau_sum"], o["dL_dtau"], rtol=2e-3, atol_scale=2e-4)
+    assert rasterizer._capacity_hint[(0, 200, 120)] >= int(o["num_rendered"])   # next call starts large enough
+
+
+def test_very_long_tile_lists_use_the_large_sort():
+    g, cams, cots = scenes.make_scene(30000, 48, 32, 0, seed=22)              # 6 tiles, > 4096 entries each
+    o = cpu_oracle.forward_backward(g, cams[0], None, export=True)
+    lens = (o["st_ranges"][:, 1] - o["st_ranges"][:, 0])
+    assert lens.max() > 4096
+    ours = util.run_ours(g, cams[0], None)
+    np.testing.assert_array_equal(ours["st_point_list"].view(np.uint32), o["st_point_list"])
+    np.testing.assert_array_equal(ours["st_point_list_keys"].view(np.uint64), o["st_point_list_keys"])
+    np.testing.assert_array_equal(ours["st_ranges"].view(np.uint32), o["st_ranges"])
+
+
+def test_mark_visible_matches_oracle():
+    g, cams, _ = scenes.make_scene(5000, 64, 64, 0, seed=5)
+    s = util.settings_from_cam(cams[0], 0)
+    vis = rasterizer.GaussianRasterizer(s).markVisible(util.to_dev(g["means3D"]))
+    assert vis.dtype == torch.bool
+    np.testing.assert_array_equal(vis.cpu().numpy(), cpu_oracle.mark_visible(g["means3D"], cams[0]["viewmatrix"]))
+
+
+def test_no_workspace_growth_over_steps():
+    g, cams, cots = scenes.make_scene(20000, 320, 240, 0, seed=7)
+    util.run_ours(g, cams[0], cots[0], export=False)
+    torch.cuda.synchronize()
+    base = torch.cuda.memory_allocated()
+    for _ in range(25):
+        util.run_ours(g, cams[0], cots[0], export=False)
+    torch.cuda.synchronize()
+    assert torch.cuda.memory_allocated() <= base + (1 << 20)   # no reference cycle keeps workspaces alive
+
+
+def test_only_depth_or_only_color_cotangent():
+    g, cams, cots = scenes.make_scene(2000, 96, 64, 0, seed=9)
+    s = util.settings_from_cam(cams[0], 0)
+    leaf = lambda a: util.to_dev(a).requires_grad_(True)
+    m3, op, sh, sc, ro = leaf(g["means3D"]), leaf(g["opacities"]), leaf(g["sh"]), leaf(g["scales"]), leaf(g["rotations"])
+    m2 = torch.zeros(2000, 3, device=DEV, requires_grad=True)
+    th, rh = torch.zeros(3, device=DEV, requires_grad=True), torch.zeros(3, device=DEV, requires_grad=True)
+    color, radii, depth, opacity, n_touched = rasterizer.GaussianRasterizer(s)(m3, m2, op, shs=sh, scales=sc, rotations=ro, theta=th, rho=rh)
+    ga = torch.autograd.grad(depth.sum(), [m3, th, rh], retain_graph=True)
+    gb = torch.autograd.grad(color.sum(), [m3, th, rh], retain_graph=True)
+    gc = torch.autograd.grad(color.sum() + depth.sum() + 3.0 * opacity.sum(), [m3, th, rh])   # opacity cotangent is ignored
+    for a, b, c in zip(ga, gb, gc):
+        torch.testing.assert_close(a + b, c, rtol=2e-3, atol=1e-4 * float(c.abs().max()))
+    assert th.grad is None and tuple(gc[1].shape) == (3,) and not radii.requires_grad and not n_touched.requires_grad
+
+
+# ------------------------------- BASELINE.json full size (config 2) -------------------------------
+@pytest.fixture(scope="module")
+def config2():
+    g, cams, cots = scenes.make_scene("config2")
+    ours = util.run_ours(g, cams[0], cots[0])
+    return g, cams[0], cots[0], ours
+
+
+def test_config2_structural_properties(config2):
+    g, cam, cot, o = config2
+    R = int(o["num_rendered"])
+    ranges = o["st_ranges"].view(np.uint32).astype(np.int64)
+    lens = ranges[:, 1] - ranges[:, 0]
+    nz = lens > 0
+    assert lens.sum() == R                                           # ranges partition [0, R)
+    assert np.array_equal(ranges[nz][1:, 0], ranges[nz][:-1, 1]) and ranges[nz][0, 0] == 0 and ranges[nz][-1, 1] == R
+    keys = o["st_point_list_keys"].view(np.uint64)
+    assert np.all(keys[1:] >= keys[:-1])                             # globally sorted (tile | depth)
+    tile_of = (keys >> np.uint64(32)).astype(np.int64)
+    assert np.array_equal(np.repeat(np.arange(len(lens)), lens), tile_of)
+    ids = o["st_point_list"].view(np.uint32).astype(np.int64)
+    eq = keys[1:] == keys[:-1]
+    assert np.all(ids[1:][eq] > ids[:-1][eq])                        # stable: ties keep ascending id
+    depth_bits = (keys & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    assert np.array_equal(depth_bits, util.bits(o["st_depths"])[ids])
+    # every instance belongs to its Gaussian's tile rectangle count: sum over Gaussians == R
+    vis = o["radii"] > 0
+    assert np.array_equal(np.bincount(ids, minlength=len(vis)) > 0, vis)
+    gx = (cam["width"] + 15) // 16
+    ncon = o["st_n_contrib"].view(np.uint32).reshape(cam["height"], cam["width"])
+    tile_len = lens.reshape(-1, gx)
+    assert np.all(ncon <= np.repeat(np.repeat(tile_len, 16, 0), 16, 1)[:cam["height"], :cam["width"]])
+    T = o["st_final_T"].reshape(cam["height"], cam["width"])
+    np.testing.assert_allclose(o["opacity"][0], 1.0 - T, rtol=0, atol=1e-7)
+    assert np.all((T >= 1e-4 * 0.01) & (T <= 1.0))
+
+
+def test_config2_forward_is_deterministic_and_backward_is_linear(config2):
+    g, cam, cot, o = config2
+    o2 = util.run_ours(g, cam, (2.0 * cot[0], 2.0 * cot[1]), export=False)
+    for k in ("color", "depth", "opacity", "radii", "n_touched"):
+        np.testing.assert_array_equal(o[k], o2[k])                   # bitwise repeatable forward
+    for k in ("g_dL_dmeans3D", "g_dL_dopacity", "g_dL_dsh", "g_dL_dscales", "g_dL_drotations", "g_dL_dtau_sum"):
+        util.assert_grad_close(k, o2[k], 2.0 * o[k], rtol=1e-3, atol_scale=1e-4)   # linear in the cotangents
+
+
+@pytest.mark.skipif(not ref_api.available(), reason="oracle/_ref/libref_rasterizer.so not built")
+def test_config2_matches_unmodified_reference(config2):
+    g, cam, cot, o = config2
+    gt, ct = ref_api.to_cuda(g, DEV), ref_api.to_cuda(cam, DEV)
+    ref = ref_api.RefRasterizer()
+    out = ref.forward(gt, ct)
+    st = ref.export_state()
+    gr = ref.backward(torch.from_numpy(cot[0]).to(DEV), torch.from_numpy(cot[1]).to(DEV))
+    n = lambda t: t.cpu().numpy()
+    np.testing.assert_array_equal(o["radii"], n(out["radii"]))
+    assert int(o["num_rendered"]) == int(out["num_rendered"])
+    np.testing.assert_array_equal(o["st_point_list_keys"].view(np.uint64), n(st["point_list_keys"]).view(np.uint64))
+    np.testing.assert_array_equal(o["st_point_list"], n(st["point_list"]))
+    np.testing.assert_array_equal(o["st_ranges"], n(st["ranges"]))
+    np.testing.assert_array_equal(o["st_n_contrib"], n(st["n_contrib"]))
+    np.testing.assert_array_equal(o["n_touched"], n(out["n_touched"]))
+    np.testing.assert_array_equal(util.bits(o["st_final_T"]), util.bits(n(st["final_T"])))
+    for k in ("color", "depth", "opacity"):
+        np.testing.assert_allclose(o[k], n(out[k]), rtol=1e-4, atol=1e-7, err_msg=k)
+    util.assert_grad_close("means3D", o["g_dL_dmeans3D"], n(gr["dL_dmeans3D"]))
+    util.assert_grad_close("means2D", o["g_dL_dmeans2D"], n(gr["dL_dmeans2D"]))
+    util.assert_grad_close("opacity", o["g_dL_dopacity"], n(gr["dL_dopacity"]))
+    util.assert_grad_close("sh", o["g_dL_dsh"], n(gr["dL_dsh"]))
+    util.assert_grad_close("scales", o["g_dL_dscales"], n(gr["dL_dscales"]))
+    util.assert_grad_close("rotations", o["g_dL_drotations"], n(gr["dL_drotations"]))
+    util.assert_grad_close("tau", o["g_dL_dtau_sum"], n(gr["dL_dtau_sum"]))
+
+
+@pytest.mark.skipif(not ref_api.available(), reason="oracle/_ref/libref_rasterizer.so not built")
+def test_config4_shape_sh3_1080p_matches_reference():
+    """config 4's shape (SH degree 3, 1920x1080) at a Gaussian count that keeps the test short."""
+    g, cams, cots = scenes.make_scene(400_000, 1920, 1080, 3, seed=1004)
+    cam, cot = cams[0], cots[0]
+    o = util.run_ours(g, cam, cot)
+    gt, ct = ref_api.to_cuda(g, DEV), ref_api.to_cuda(cam, DEV)
+    ref = ref_api.RefRasterizer()
+    out = ref.forward(gt, ct)
+    st = ref.export_state()
+    gr = ref.backward(torch.from_numpy(cot[0]).to(DEV), torch.from_numpy(cot[1]).to(DEV))
+    n = lambda t: t.cpu().numpy()
+    np.testing.assert_array_equal(o["radii"], n(out["radii"]))
+    np.testing.assert_array_equal(o["st_point_list"], n(st["point_list"]))
+    np.testing.assert_array_equal(o["st_n_contrib"], n(st["n_contrib"]))
+    np.testing.assert_allclose(o["color"], n(out["color"]), rtol=1e-4, atol=1e-7)
+    util.assert_grad_close("sh", o["g_dL_dsh"], n(gr["dL_dsh"]))
+    util.assert_grad_close("means3D", o["g_dL_dmeans3D"], n(gr["dL_dmeans3D"]))
+    util.assert_grad_close("tau", o["g_dL_dtau_sum"], n(gr["dL_dtau_sum"]))
