@@ -9,8 +9,9 @@
 //   binning: bucket[capacity] u64 = depth_bits<<32 | gaussian_id, grouped by tile, sorted
 //            ascending inside each tile  (== the reference's stable (tile|depth) radix order)
 //   image  : final_T[N] f32, n_contrib[N] u32
-//   grad   : acc[3i..3i+2] float4 x3 per Gaussian (dmean2D.xy, dconic.xyw, dopacity, dcolor.rgb,
-//            ddepth, 2 pad) -- zero between backward passes; pose partials; ticket
+//   grad   : acc[3i..3i+2] float4 x3 per Gaussian (dmean2D.xy, dconic.xyw -- both without their
+//            constant factors, see preprocess_bwd --, dopacity, dcolor.rgb, ddepth, 2 pad)
+//            -- zero between backward passes; pose partials; ticket
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>

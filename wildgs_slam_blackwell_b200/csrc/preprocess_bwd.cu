@@ -54,8 +54,10 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
             const float4 z4 = make_float4(0, 0, 0, 0);
             p.grad.acc[3 * idx] = z4; p.grad.acc[3 * idx + 1] = z4; p.grad.acc[3 * idx + 2] = z4;
         }
-        const float dm2x = g0.x, dm2y = g0.y;              // dL/dmean2D (NDC-scaled)
-        const float dcx = g0.z, dcy = g0.w, dcz = g1.x;    // dL/dconic (x, y, w)
+        // render_bwd accumulates without the per-pixel constants (backward.cu:643-644,752-756);
+        // apply them once here: ddelx_dx = W/2, ddely_dy = H/2, and the -1/2 of the conic terms
+        const float dm2x = -0.5f * p.W * g0.x, dm2y = -0.5f * p.H * g0.y;   // dL/dmean2D (NDC-scaled)
+        const float dcx = -0.5f * g0.z, dcy = -0.5f * g0.w, dcz = -0.5f * g1.x;  // dL/dconic (x, y, w)
         const float dop = g1.y;
         const float dcol[3] = {g1.z, g1.w, g2.x};
         const float ddepth = g2.y;

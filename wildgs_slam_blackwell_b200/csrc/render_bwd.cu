@@ -3,50 +3,85 @@
 //
 // Same decomposition as the forward (CTA = 16x16 tile, warp = 8x4 pixels, cp.async-staged
 // batches, per-warp ellipse/rectangle culling), traversed back to front starting at the
-// tile's last contributor.  The reference reduces every (tile, Gaussian) pair with a 256-wide
-// shared-memory tree (9 block barriers) and a contended shared atomic; here the ten per-pixel
-// gradient terms are reduced inside the warp with a 12-shuffle reduce-scatter butterfly, after
-// which ten lanes each own one total and issue one RED.ADD.F32 into the 48-byte per-Gaussian
-// accumulator record -- no block barrier per pair at all.
+// tile's last contributor.  The kernel is FP32-issue bound (ncu: 77 % issue utilisation), so
+// the design minimises instructions per (warp, Gaussian) pair:
+//  * the four per-channel "accum_rec" recurrences of the reference (backward.cu:709-722)
+//    collapse into ONE scalar recurrence on x = c.dL_dpixel + depth*dL_ddepth (they are linear);
+//  * constant factors (0.5*W, 0.5*H, -0.5) are applied once per Gaussian in preprocess_bwd,
+//    not once per pixel here;
+//  * the reference's 256-wide shared-memory tree + 9 block barriers per list entry becomes a
+//    warp-private shared-memory transpose: every lane stores its 10 terms, and once GROUP
+//    Gaussians are pending, 10*GROUP lanes each sum one 32-float row (8 LDS.128, conflict-free
+//    at a 36-float row pitch) and issue one RED.ADD.F32 into the 48-byte accumulator record.
+//    No block barrier per pair at all.
+// ex2.approx / rcp.approx are used (tolerance on gradients is rtol 1e-3; the forward, which is
+// bit-exact, is untouched).
 #include "common.cuh"
 #include "kernels.h"
 #include "render_common.cuh"
 
 namespace wgs {
 
-// Reduce-scatter N per-lane values across the 32 lanes of a warp: after the call lane L holds
-// in v[0] the warp-wide sum of original value index 5*b4 + 3*b3 + 2*b2 + b1 (b_k = bit k of
-// L) -- see owner_index() -- using 5+3+2+1+1 = 12 shuffles instead of 10*5 = 50.
-template <int N, int OFFSET>
-__device__ __forceinline__ void reduce_scatter(float (&v)[10], int lane) {
-    if constexpr (N == 1) {
-#pragma unroll
-        for (int o = OFFSET; o > 0; o >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], o);
+constexpr int BB = 128;    // list entries staged per batch
+constexpr int GROUP = 3;   // Gaussians per shared-memory reduction
+constexpr int ROW = 36;    // floats per reduction row (32 + pad: 144 B pitch, 16-B aligned, conflict-free)
+
+struct __align__(16) BwdStage {
+    float4 rec0[BB];  // x, y, conic.x, conic.y
+    float4 rec1[BB];  // conic.z, opacity, depth, ln(255*opacity)
+    float4 col[BB];   // r, g, b, -
+    uint32_t id[BB];
+};
+
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// threads 0..127 copy rec0/rec1 of slot tid, threads 128..255 copy col + id of slot tid-128
+__device__ __forceinline__ void bwd_gather(BwdStage& st, int tid, uint32_t id, const GeomView& g) {
+    const int slot = tid & (BB - 1);
+    if (tid < BB) {
+        cp_async16(&st.rec0[slot], g.rec + 2 * (size_t)id);
+        cp_async16(&st.rec1[slot], g.rec + 2 * (size_t)id + 1);
     } else {
-        constexpr int M = (N + 1) / 2;
-        const bool up = (lane & OFFSET) != 0;
-#pragma unroll
-        for (int i = 0; i < M; i++) {
-            const float lo = v[i];
-            const float hi = (i + M < N) ? v[i + M] : 0.f;
-            const float send = up ? lo : hi;
-            const float keep = up ? hi : lo;
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, OFFSET);
-        }
-        reduce_scatter<M, OFFSET / 2>(v, lane);
+        cp_async16(&st.col[slot], g.col + id);
+        st.id[slot] = id;
     }
 }
 
-// value index owned by a lane after reduce_scatter<10,16>, or -1
-__device__ __forceinline__ int owner_index(int lane) {
-    const int b4 = (lane >> 4) & 1, b3 = (lane >> 3) & 1, b2 = (lane >> 2) & 1, b1 = (lane >> 1) & 1;
-    const int s2 = 2 * b2 + b1, s3 = 3 * b3 + s2;
-    if ((lane & 1) || s2 >= 3 || s3 >= 5) return -1;
-    return 5 * b4 + s3;
+// Sum the pending rows of this warp and add them to the per-Gaussian accumulators.
+__device__ __forceinline__ void flush_group(const float (*red)[ROW], const uint32_t* rid, int n, int lane,
+                                            float* __restrict__ acc) {
+    __syncwarp();
+    if (lane < 10 * n) {
+        const float4* r4 = reinterpret_cast<const float4*>(red[lane]);
+        float4 s0 = r4[0], s1 = r4[1], s2 = r4[2], s3 = r4[3];
+        const float4 t0 = r4[4], t1 = r4[5], t2 = r4[6], t3 = r4[7];
+        s0.x += t0.x; s0.y += t0.y; s0.z += t0.z; s0.w += t0.w;
+        s1.x += t1.x; s1.y += t1.y; s1.z += t1.z; s1.w += t1.w;
+        s2.x += t2.x; s2.y += t2.y; s2.z += t2.z; s2.w += t2.w;
+        s3.x += t3.x; s3.y += t3.y; s3.z += t3.z; s3.w += t3.w;
+        s0.x += s1.x; s0.y += s1.y; s0.z += s1.z; s0.w += s1.w;
+        s2.x += s3.x; s2.y += s3.y; s2.z += s3.z; s2.w += s3.w;
+        s0.x += s2.x; s0.y += s2.y; s0.z += s2.z; s0.w += s2.w;
+        const float sum = (s0.x + s0.y) + (s0.z + s0.w);
+        const int g = lane / 10, i = lane - 10 * g;
+        atomicAdd(acc + 12 * (size_t)rid[g] + i, sum);
+    }
+    __syncwarp();
 }
 
-__global__ void __launch_bounds__(256) render_bwd_kernel(const __grid_constant__ RenderBwdParams p) {
-    __shared__ FwdStage st[2];
+__global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constant__ RenderBwdParams p) {
+    __shared__ BwdStage st[2];
+    __shared__ __align__(16) float red[8][10 * GROUP][ROW];
+    __shared__ uint32_t rid[8][4];
     __shared__ uint32_t s_hi;
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -72,7 +107,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const __grid_constant__
     __syncthreads();
     const int hi = (int)s_hi;  // entries [hi, total) contributed to no pixel of this tile
     if (hi == 0) return;
-    const int rounds = (hi + BATCH - 1) / BATCH;
+    const int rounds = (hi + BB - 1) / BB;
 
     const float T_final = inside ? p.image.final_T[pix] : 0.f;
     float T = T_final;
@@ -81,36 +116,38 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const __grid_constant__
         dpx = __ldg(p.dL_dcolor + pix); dpy = __ldg(p.dL_dcolor + N + pix); dpz = __ldg(p.dL_dcolor + 2 * N + pix);
         dpd = __ldg(p.dL_ddepth + pix);
     }
-    const float bg_dot = __ldg(p.bg) * dpx + __ldg(p.bg + 1) * dpy + __ldg(p.bg + 2) * dpz;
-    const float ddelx_dx = 0.5f * p.W, ddely_dy = 0.5f * p.H;
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f;
-    float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f;
-    const int own = owner_index(lane);
+    // T_final * (bg . dL_dpixel): the background term of dL_dalpha (backward.cu:733-738)
+    const float tfbg = T_final * (__ldg(p.bg) * dpx + __ldg(p.bg + 1) * dpy + __ldg(p.bg + 2) * dpz);
+    float last_alpha = 0.f, last_x = 0.f, A = 0.f;
     float* __restrict__ acc = (float*)p.grad.acc;
+    const float (*wred)[ROW] = red[warp];
+    float* const wcol = &red[warp][0][lane];  // this lane's column
+    int pending = 0;
 
-    // round r holds list entries k = hi - (r+1)*BATCH + slot, slot in [0, BATCH)
+    // round r holds list entries k = hi - (r+1)*BB + slot, slot in [0, BB)
+    const int slot = tid & (BB - 1);
     uint32_t id_next = 0;
     {
-        const int k = hi - BATCH + tid;
-        if (k >= 0) stage_gather(st[0], tid, (uint32_t)list[k], p.geom);
+        const int k = hi - BB + slot;
+        if (k >= 0) bwd_gather(st[0], tid, (uint32_t)list[k], p.geom);
         cp_async_commit();
-        if (k - BATCH >= 0) id_next = (uint32_t)list[k - BATCH];
+        if (k - BB >= 0) id_next = (uint32_t)list[k - BB];
     }
     for (int r = 0; r < rounds; r++) {
         const int buf = r & 1;
-        const int base = hi - (r + 1) * BATCH;
+        const int base = hi - (r + 1) * BB;
         cp_async_wait<0>();
         __syncthreads();
         if (r + 1 < rounds) {
-            const int k = base - BATCH + tid;
-            if (k >= 0) stage_gather(st[buf ^ 1], tid, id_next, p.geom);
-            if (k - BATCH >= 0) id_next = (uint32_t)list[k - BATCH];
+            const int k = base - BB + slot;
+            if (k >= 0) bwd_gather(st[buf ^ 1], tid, id_next, p.geom);
+            if (k - BB >= 0) id_next = (uint32_t)list[k - BB];
         }
         cp_async_commit();
         if (base >= warp_last) continue;  // whole batch lies behind this warp's last contributor
 
-        const FwdStage& s = st[buf];
-        for (int c0 = BATCH - 32; c0 >= 0; c0 -= 32) {
+        const BwdStage& s = st[buf];
+        for (int c0 = BB - 32; c0 >= 0; c0 -= 32) {
             const int mine = c0 + lane;
             const int kmine = base + mine;
             bool hit = false;
@@ -127,57 +164,53 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const __grid_constant__
                 const int k = base + j;
                 const float4 a = s.rec0[j];
                 const float4 b = s.rec1[j];
-                float v[10];
-#pragma unroll
-                for (int i = 0; i < 10; i++) v[i] = 0.f;
+                float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f, v8 = 0.f, v9 = 0.f;
                 bool active = false;
                 if (k < last_contributor) {
-                    const float dx = SUB(a.x, pixx), dy = SUB(a.y, pixy);
-                    const float power =
-                        FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
+                    const float dx = a.x - pixx, dy = a.y - pixy;
+                    // same expression as the forward so that skip decisions agree
+                    const float power = FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
                     if (!(power > 0.f)) {
-                        const float G = expf(power);
-                        const float alpha = fminf(MUL(b.y, G), 0.99f);
+                        const float G = ex2_approx(power * 1.4426950408889634f);
+                        const float alpha = fminf(b.y * G, 0.99f);
                         if (!(alpha < 1.0f / 255.0f)) {
                             active = true;
                             const float4 col = s.col[j];
-                            const float inv = __frcp_rn(1.f - alpha);
-                            T = T * inv;
-                            const float dch = alpha * T;
-                            const float om = 1.f - last_alpha;
-                            ar0 = last_alpha * lc0 + om * ar0; lc0 = col.x;
-                            ar1 = last_alpha * lc1 + om * ar1; lc1 = col.y;
-                            ar2 = last_alpha * lc2 + om * ar2; lc2 = col.z;
-                            ard = last_alpha * ld + om * ard;  ld = b.z;
-                            float dL_dalpha = (col.x - ar0) * dpx + (col.y - ar1) * dpy + (col.z - ar2) * dpz +
-                                              (b.z - ard) * dpd;
-                            dL_dalpha *= T;
+                            const float inv = rcp_approx(1.f - alpha);
+                            T *= inv;
+                            const float x = fmaf(col.x, dpx, fmaf(col.y, dpy, fmaf(col.z, dpz, b.z * dpd)));
+                            A = fmaf(last_alpha, last_x - A, A);
+                            last_x = x;
                             last_alpha = alpha;
-                            dL_dalpha += (-T_final * inv) * bg_dot;
-                            const float dL_dG = b.y * dL_dalpha;
-                            const float gdx = G * dx, gdy = G * dy;
-                            const float dG_ddelx = -gdx * a.z - gdy * a.w;
-                            const float dG_ddely = -gdy * b.x - gdx * a.w;
-                            v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                            v[1] = dL_dG * dG_ddely * ddely_dy;
-                            v[2] = -0.5f * gdx * dx * dL_dG;
-                            v[3] = -0.5f * gdx * dy * dL_dG;
-                            v[4] = -0.5f * gdy * dy * dL_dG;
-                            v[5] = G * dL_dalpha;
-                            v[6] = dch * dpx;
-                            v[7] = dch * dpy;
-                            v[8] = dch * dpz;
-                            v[9] = dch * dpd;
+                            const float dLa = fmaf(-tfbg, inv, (x - A) * T);  // dL/dalpha
+                            const float dch = alpha * T;
+                            const float t = b.y * dLa;                       // dL/dG
+                            const float aa = G * dx * t, bb = G * dy * t;
+                            v0 = fmaf(aa, a.z, bb * a.w);   // -> dL/dmean2D.x after * -(W/2)
+                            v1 = fmaf(bb, b.x, aa * a.w);   // -> dL/dmean2D.y after * -(H/2)
+                            v2 = aa * dx;                   // -> dL/dconic.x after * -1/2
+                            v3 = aa * dy;                   // -> dL/dconic.y after * -1/2
+                            v4 = bb * dy;                   // -> dL/dconic.w after * -1/2
+                            v5 = G * dLa;                   // dL/dopacity
+                            v6 = dch * dpx; v7 = dch * dpy; v8 = dch * dpz;  // dL/dcolor
+                            v9 = dch * dpd;                 // dL/ddepth
                         }
                     }
                 }
                 if (__any_sync(0xffffffffu, active)) {
-                    reduce_scatter<10, 16>(v, lane);
-                    if (own >= 0) atomicAdd(acc + 12 * (size_t)s.id[j] + own, v[0]);
+                    float* c = wcol + pending * (10 * ROW);
+                    c[0 * ROW] = v0; c[1 * ROW] = v1; c[2 * ROW] = v2; c[3 * ROW] = v3; c[4 * ROW] = v4;
+                    c[5 * ROW] = v5; c[6 * ROW] = v6; c[7 * ROW] = v7; c[8 * ROW] = v8; c[9 * ROW] = v9;
+                    if (lane == 0) rid[warp][pending] = s.id[j];
+                    if (++pending == GROUP) {
+                        flush_group(wred, rid[warp], GROUP, lane, acc);
+                        pending = 0;
+                    }
                 }
             }
         }
     }
+    if (pending) flush_group(wred, rid[warp], pending, lane, acc);
     cp_async_wait<0>();
 }
 
