@@ -57,11 +57,11 @@ __device__ __forceinline__ void bwd_gather(BwdStage& st, int tid, uint32_t id, c
 }
 
 // Sum the pending rows of this warp and add them to the per-Gaussian accumulators.
-__device__ __forceinline__ void flush_group(const float (*red)[ROW], const uint32_t* rid, int n, int lane,
+__device__ __forceinline__ void flush_group(const float* my_row, uint32_t rid, int n, int lane, int sub,
                                             float* __restrict__ acc) {
     __syncwarp();
     if (lane < 10 * n) {
-        const float4* r4 = reinterpret_cast<const float4*>(red[lane]);
+        const float4* r4 = reinterpret_cast<const float4*>(my_row);
         float4 s0 = r4[0], s1 = r4[1], s2 = r4[2], s3 = r4[3];
         const float4 t0 = r4[4], t1 = r4[5], t2 = r4[6], t3 = r4[7];
         s0.x += t0.x; s0.y += t0.y; s0.z += t0.z; s0.w += t0.w;
@@ -72,8 +72,7 @@ __device__ __forceinline__ void flush_group(const float (*red)[ROW], const uint3
         s2.x += s3.x; s2.y += s3.y; s2.z += s3.z; s2.w += s3.w;
         s0.x += s2.x; s0.y += s2.y; s0.z += s2.z; s0.w += s2.w;
         const float sum = (s0.x + s0.y) + (s0.z + s0.w);
-        const int g = lane / 10, i = lane - 10 * g;
-        atomicAdd(acc + 12 * (size_t)rid[g] + i, sum);
+        atomicAdd(acc + 12 * (size_t)rid + sub, sum);
     }
     __syncwarp();
 }
@@ -81,7 +80,6 @@ __device__ __forceinline__ void flush_group(const float (*red)[ROW], const uint3
 __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constant__ RenderBwdParams p) {
     __shared__ BwdStage st[2];
     __shared__ __align__(16) float red[8][10 * GROUP][ROW];
-    __shared__ uint32_t rid[8][4];
     __shared__ uint32_t s_hi;
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -120,8 +118,12 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
     const float tfbg = T_final * (__ldg(p.bg) * dpx + __ldg(p.bg + 1) * dpy + __ldg(p.bg + 2) * dpz);
     float last_alpha = 0.f, last_x = 0.f, A = 0.f;
     float* __restrict__ acc = (float*)p.grad.acc;
-    const float (*wred)[ROW] = red[warp];
-    float* const wcol = &red[warp][0][lane];  // this lane's column
+    // shared-window address of this lane's column (written per Gaussian); kept as a 32-bit register
+    unsigned wcol;
+    asm volatile("mov.u32 %0, %1;" : "=r"(wcol) : "r"((unsigned)__cvta_generic_to_shared(&red[warp][0][lane])));
+    const float* const wrow = &red[warp][lane < 10 * GROUP ? lane : 0][0];  // this lane's row (summed at flush)
+    const int my_g = lane / 10, my_sub = lane - 10 * my_g;  // which pending Gaussian / term this lane flushes
+    uint32_t my_id = 0;                              // id of pending Gaussian my_g
     int pending = 0;
 
     // round r holds list entries k = hi - (r+1)*BB + slot, slot in [0, BB)
@@ -198,19 +200,24 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
                     }
                 }
                 if (__any_sync(0xffffffffu, active)) {
-                    float* c = wcol + pending * (10 * ROW);
-                    c[0 * ROW] = v0; c[1 * ROW] = v1; c[2 * ROW] = v2; c[3 * ROW] = v3; c[4 * ROW] = v4;
-                    c[5 * ROW] = v5; c[6 * ROW] = v6; c[7 * ROW] = v7; c[8 * ROW] = v8; c[9 * ROW] = v9;
-                    if (lane == 0) rid[warp][pending] = s.id[j];
+                    const unsigned c = wcol + pending * (10 * ROW * 4);
+                    asm volatile(
+                        "st.shared.f32 [%0], %1;\n\tst.shared.f32 [%0+144], %2;\n\tst.shared.f32 [%0+288], %3;\n\t"
+                        "st.shared.f32 [%0+432], %4;\n\tst.shared.f32 [%0+576], %5;\n\tst.shared.f32 [%0+720], %6;\n\t"
+                        "st.shared.f32 [%0+864], %7;\n\tst.shared.f32 [%0+1008], %8;\n\tst.shared.f32 [%0+1152], %9;\n\t"
+                        "st.shared.f32 [%0+1296], %10;\n" ::"r"(c), "f"(v0), "f"(v1), "f"(v2), "f"(v3), "f"(v4), "f"(v5),
+                        "f"(v6), "f"(v7), "f"(v8), "f"(v9) : "memory");
+                    const uint32_t gid = s.id[j];
+                    if (pending == my_g) my_id = gid;
                     if (++pending == GROUP) {
-                        flush_group(wred, rid[warp], GROUP, lane, acc);
+                        flush_group(wrow, my_id, GROUP, lane, my_sub, acc);
                         pending = 0;
                     }
                 }
             }
         }
     }
-    if (pending) flush_group(wred, rid[warp], pending, lane, acc);
+    if (pending) flush_group(wrow, my_id, pending, lane, my_sub, acc);
     cp_async_wait<0>();
 }
 
