@@ -39,7 +39,7 @@ typedef struct WgsContext WgsContext; /* per-device: pinned readback word, event
 /* Workspace byte sizes for a problem of P Gaussians, W x H pixels and room for
  * `capacity` (Gaussian,tile) instances.  Replaces required<GeometryState/BinningState/
  * ImageState>() (RAST/cuda_rasterizer/rasterizer_impl.h:64-72, rasterizer_impl.cu:155-194).
- * geom: 57 B/Gaussian; tile: 20 B/tile; binning: 8 B/instance; image: 8 B/pixel;
+ * geom: 57 B/Gaussian; tile: 268 B/tile (up to 32 privatised histogram + cursor copies); binning: 8 B/instance; image: 8 B/pixel;
  * grad: 48 B/Gaussian + pose partials (the reference: 79 B/Gaussian, 24 B/instance + CUB
  * temporaries, 16 B/pixel, and eleven zero-filled gradient tensors per backward). */
 typedef struct WgsWorkspaceSizes {

@@ -152,7 +152,7 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
 
     PreFwdParams pp;
     pp.P = a->P; pp.D = a->sh_degree; pp.M = a->M; pp.W = a->width; pp.H = a->height; pp.gx = gx; pp.gy = gy;
-    pp.prefiltered = a->prefiltered;
+    pp.prefiltered = a->prefiltered; pp.copies = hist_copies((size_t)tiles);
     pp.tanfovx = a->tanfovx; pp.tanfovy = a->tanfovy;
     pp.focal_y = a->height / (2.0f * a->tanfovy);  // rasterizer_impl.cu:225-226
     pp.focal_x = a->width / (2.0f * a->tanfovx);
@@ -167,7 +167,7 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     MARK(ctx, 1, s);
 
     BinParams bp;
-    bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.capacity = a->capacity;
+    bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.copies = hist_copies((size_t)tiles); bp.capacity = a->capacity;
     bp.geom = geom; bp.tile = tile; bp.bucket = (unsigned long long*)a->binning; bp.host_R = ctx->dev_R;
     launch_tile_scan(bp, s);
     CK(cudaEventRecord(ctx->ev_R, s));
@@ -307,7 +307,7 @@ int wgs_export_binning(const WgsForwardArgs* a, int64_t num_rendered, uint64_t* 
     }
     const int gx = (a->width + 15) / 16, gy = (a->height + 15) / 16, tiles = gx * gy;
     BinParams bp;
-    bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.capacity = a->capacity;
+    bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.copies = hist_copies((size_t)tiles); bp.capacity = a->capacity;
     bp.geom = geom_view(a->geom, (size_t)(a->P > 0 ? a->P : 1));
     bp.tile = tile_view(a->tile, (size_t)tiles);
     bp.bucket = (unsigned long long*)a->binning; bp.host_R = nullptr;

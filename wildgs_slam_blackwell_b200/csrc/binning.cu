@@ -27,7 +27,10 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__
     uint32_t carry = 0;
     for (int base = 0; base < p.tiles; base += 1024) {
         const int t = base + tid;
-        const uint32_t c = t < p.tiles ? p.tile.count[t] : 0u;
+        uint32_t c = 0;
+        if (t < p.tiles) {
+            for (int k = 0; k < p.copies; k++) c += p.tile.count[(size_t)k * p.tiles + t];
+        }
         uint32_t v = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -49,7 +52,11 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__
         const uint32_t excl = carry + (warp ? warp_sums[warp - 1] : 0u) + v - c;
         if (t < p.tiles) {
             p.tile.ranges[t] = make_uint2(excl, excl + c);
-            p.tile.cursor[t] = excl;
+            uint32_t run = excl;  // copy k of this tile scatters into [run_k, run_k + count_k)
+            for (int k = 0; k < p.copies; k++) {
+                p.tile.cursor[(size_t)k * p.tiles + t] = run;
+                run += p.tile.count[(size_t)k * p.tiles + t];
+            }
             if (c > (uint32_t)SMALL_MAX) p.tile.large_list[atomicAdd(p.tile.misc + MISC_N_LARGE, 1u)] = t;
         }
         carry += warp_sums[31];
@@ -81,10 +88,11 @@ __global__ void __launch_bounds__(256) scatter_kernel(const __grid_constant__ Bi
     }
     const uint32_t w = x1 - x0, n = w * (y1 - y0);
     const bool wide = n > 32;
+    uint32_t* __restrict__ cursor = p.tile.cursor + (size_t)(blockIdx.x % p.copies) * p.tiles;
     if (n && !wide) {
         for (uint32_t y = y0; y < y1; y++)
             for (uint32_t x = x0; x < x1; x++) {
-                const uint32_t slot = atomicAdd(p.tile.cursor + y * p.gx + x, 1u);
+                const uint32_t slot = atomicAdd(cursor + y * p.gx + x, 1u);
                 if ((long long)slot < p.capacity) p.bucket[slot] = key;
             }
     }
@@ -96,7 +104,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(const __grid_constant__ Bi
         const uint32_t sw = __shfl_sync(0xffffffffu, w, src), sn = __shfl_sync(0xffffffffu, n, src);
         const unsigned long long skey = __shfl_sync(0xffffffffu, key, src);
         for (uint32_t i = lane; i < sn; i += 32) {
-            const uint32_t slot = atomicAdd(p.tile.cursor + (sy0 + i / sw) * p.gx + sx0 + i % sw, 1u);
+            const uint32_t slot = atomicAdd(cursor + (sy0 + i / sw) * p.gx + sx0 + i % sw, 1u);
             if ((long long)slot < p.capacity) p.bucket[slot] = skey;
         }
     }

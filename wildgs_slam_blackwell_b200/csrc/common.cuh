@@ -18,6 +18,11 @@
 
 #define WGS_TILE 16            // BLOCK_X == BLOCK_Y == 16 (reference config.h:14-16)
 #define WGS_TILE_PIX 256
+// The per-tile instance histogram / scatter cursors are privatised into up to this many copies
+// (copy = blockIdx.x % copies in preprocess_fwd and scatter, which share their block mapping):
+// same-line L2 atomics serialise, and 1200 counters are only 38 cache lines.  The copy count
+// actually used is hist_copies(tiles): fewer copies when there are many tiles already.
+#define WGS_HIST_COPIES 32
 
 // Round-to-nearest primitives that nvcc never re-associates or contracts.  The forward path
 // is written in these so that it reproduces, bit for bit, the instruction sequence nvcc 12.9
@@ -49,8 +54,8 @@ struct GeomView {
 };
 
 struct TileView {
-    uint32_t* count;
-    uint32_t* cursor;
+    uint32_t* count;   // [WGS_HIST_COPIES][tiles]
+    uint32_t* cursor;  // [WGS_HIST_COPIES][tiles]
     uint2* ranges;
     uint32_t* misc;
     uint32_t* large_list;  // tile ids whose segment is too long for the small sort kernel
@@ -68,6 +73,11 @@ struct GradView {
 };
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+__host__ __device__ inline int hist_copies(size_t tiles) {
+    int k = WGS_HIST_COPIES;
+    while (k > 1 && (size_t)k * tiles > 65536) k >>= 1;
+    return k;
+}
 
 __host__ __device__ inline size_t geom_bytes(size_t P) {
     return align_up(P * 32) + align_up(P * 16) + align_up(P * 8) + align_up(P);
@@ -82,16 +92,18 @@ __host__ __device__ inline GeomView geom_view(void* base, size_t P) {
     return g;
 }
 // count[] and misc[] are adjacent so that one memset clears both at the start of a forward
-__host__ __device__ inline size_t tile_clear_bytes(size_t tiles) { return align_up(tiles * 4) + align_up(MISC_WORDS * 4); }
+__host__ __device__ inline size_t tile_clear_bytes(size_t tiles) {
+    return align_up(WGS_HIST_COPIES * tiles * 4) + align_up(MISC_WORDS * 4);
+}
 __host__ __device__ inline size_t tile_bytes(size_t tiles) {
-    return tile_clear_bytes(tiles) + 2 * align_up(tiles * 4) + align_up(tiles * 8);
+    return tile_clear_bytes(tiles) + align_up(WGS_HIST_COPIES * tiles * 4) + align_up(tiles * 4) + align_up(tiles * 8);
 }
 __host__ __device__ inline TileView tile_view(void* base, size_t tiles) {
     char* p = (char*)base;
     TileView t;
-    t.count = (uint32_t*)p; p += align_up(tiles * 4);
+    t.count = (uint32_t*)p; p += align_up(WGS_HIST_COPIES * tiles * 4);
     t.misc = (uint32_t*)p; p += align_up(MISC_WORDS * 4);
-    t.cursor = (uint32_t*)p; p += align_up(tiles * 4);
+    t.cursor = (uint32_t*)p; p += align_up(WGS_HIST_COPIES * tiles * 4);
     t.large_list = (uint32_t*)p; p += align_up(tiles * 4);
     t.ranges = (uint2*)p;
     return t;

@@ -6,7 +6,7 @@
 namespace wgs {
 
 struct PreFwdParams {
-    int P, D, M, W, H, gx, gy, prefiltered;
+    int P, D, M, W, H, gx, gy, prefiltered, copies;
     float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
     const float *means3D, *sh, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
     const float *viewmatrix, *projmatrix, *campos;
@@ -17,7 +17,7 @@ struct PreFwdParams {
 };
 
 struct BinParams {
-    int P, gx, gy, tiles;
+    int P, gx, gy, tiles, copies;
     long long capacity;
     GeomView geom;
     TileView tile;

@@ -188,9 +188,10 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
     // Tile histogram: one RED per (Gaussian, tile).  Wide rectangles are spread over the warp.
     const uint32_t w = x1 - x0, n = w * (y1 - y0);
     const bool wide = n > 32;
+    uint32_t* __restrict__ count = p.tile.count + (size_t)(blockIdx.x % p.copies) * (p.gx * p.gy);
     if (visible && !wide) {
         for (uint32_t y = y0; y < y1; y++)
-            for (uint32_t x = x0; x < x1; x++) atomicAdd(p.tile.count + y * p.gx + x, 1u);
+            for (uint32_t x = x0; x < x1; x++) atomicAdd(count + y * p.gx + x, 1u);
     }
     unsigned m = __ballot_sync(0xffffffffu, wide);
     while (m) {
@@ -198,7 +199,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
         m &= m - 1;
         const uint32_t sx0 = __shfl_sync(0xffffffffu, x0, src), sy0 = __shfl_sync(0xffffffffu, y0, src);
         const uint32_t sw = __shfl_sync(0xffffffffu, w, src), sn = __shfl_sync(0xffffffffu, n, src);
-        for (uint32_t i = lane; i < sn; i += 32) atomicAdd(p.tile.count + (sy0 + i / sw) * p.gx + sx0 + i % sw, 1u);
+        for (uint32_t i = lane; i < sn; i += 32) atomicAdd(count + (sy0 + i / sw) * p.gx + sx0 + i % sw, 1u);
     }
 }
 
