@@ -117,6 +117,22 @@ def load_impl(impl):
     return mod
 
 
+class _Set:
+    """One set of device-resident step inputs (+ the autograd leaves / rasterizer bound to them)."""
+
+    def __init__(self, wl, mod, dev):
+        self.d = {k: v.to(dev) for k, v in wl.host.items()}
+        self.leaves = [self.d[k].requires_grad_(True) for k in ("means3D", "sh", "opacities", "scales", "rotations")]
+        self.settings = mod.GaussianRasterizationSettings(
+            image_height=wl.H, image_width=wl.W, tanfovx=wl.cam["tanfovx"], tanfovy=wl.cam["tanfovy"],
+            bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=self.d["viewmatrix"],
+            projmatrix=self.d["projmatrix"], projmatrix_raw=torch.from_numpy(wl.cam["projmatrix_raw"]).to(dev),
+            sh_degree=wl.deg, campos=self.d["campos"], prefiltered=False, debug=False)
+        self.rast = mod.GaussianRasterizer(self.settings)
+        self.copy_done = torch.cuda.Event()
+        self.compute_done = torch.cuda.Event()
+
+
 class Workload:
     """One view of the scene on one device, driven through the public API of `mod`."""
 
@@ -136,57 +152,72 @@ class Workload:
                          viewmatrix=pin(self.cam["viewmatrix"]), projmatrix=pin(self.cam["projmatrix"]),
                          campos=pin(self.cam["campos"]),
                          target_color=pin(rng.uniform(0, 1, (3, H, W))), target_depth=pin(rng.uniform(0.5, 6, (1, H, W))))
-        self.d = {k: v.to(dev) for k, v in self.host.items()}
-        self.leaves = [self.d[k].requires_grad_(True) for k in ("means3D", "sh", "opacities", "scales", "rotations")]
+        # two input sets: the e2e loop copies step i+1's inputs (copy stream) while step i computes
+        self.sets = [_Set(self, mod, dev), _Set(self, mod, dev)]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.e2e_i = 0
+        main = self.sets[0]
+        self.d, self.leaves, self.settings, self.rast = main.d, main.leaves, main.settings, main.rast
         self.means2D = torch.zeros(P, 3, device=dev, requires_grad=True)
         self.theta = torch.zeros(3, device=dev, requires_grad=True)
         self.rho = torch.zeros(3, device=dev, requires_grad=True)
         self.dc, self.dd = torch.from_numpy(dc).to(dev), torch.from_numpy(dd).to(dev)
-        self.settings = mod.GaussianRasterizationSettings(
-            image_height=H, image_width=W, tanfovx=self.cam["tanfovx"], tanfovy=self.cam["tanfovy"],
-            bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=self.d["viewmatrix"],
-            projmatrix=self.d["projmatrix"], projmatrix_raw=torch.from_numpy(self.cam["projmatrix_raw"]).to(dev),
-            sh_degree=deg, campos=self.d["campos"], prefiltered=False, debug=False)
-        self.rast = mod.GaussianRasterizer(self.settings)
         self.out_host = torch.zeros(7, dtype=torch.float32).pin_memory()
         self.h2d_bytes = sum(v.numel() * 4 for v in self.host.values())
         self.d2h_bytes = 7 * 4
         self.bucket_floats = sum(t.numel() for t in self.leaves)
 
-    def _zero_grads(self):
-        for t in self.leaves + [self.means2D, self.theta, self.rho]:
+    def _zero_grads(self, leaves):
+        for t in leaves + [self.means2D, self.theta, self.rho]:
             t.grad = None
 
-    def _forward(self):
-        m3, sh, op, sc, ro = self.leaves
-        return self.rast(m3, self.means2D, op, shs=sh, colors_precomp=None, scales=sc, rotations=ro,
-                         cov3D_precomp=None, theta=self.theta, rho=self.rho)
+    def _forward(self, st):
+        m3, sh, op, sc, ro = st.leaves
+        return st.rast(m3, self.means2D, op, shs=sh, colors_precomp=None, scales=sc, rotations=ro,
+                       cov3D_precomp=None, theta=self.theta, rho=self.rho)
 
     def step_resident(self, world):
         """fwd+bwd, inputs and cotangents resident in HBM (+ gradient allreduce when sharded)."""
-        self._zero_grads()
-        color, radii, depth, opacity, n_touched = self._forward()
+        st = self.sets[0]
+        self._zero_grads(st.leaves)
+        color, radii, depth, opacity, n_touched = self._forward(st)
         torch.autograd.backward([color, depth], [self.dc, self.dd])
         if world > 1:
-            bucket = torch.cat([t.grad.reshape(-1) for t in self.leaves])
+            bucket = torch.cat([t.grad.reshape(-1) for t in st.leaves])
             dist.all_reduce(bucket)
             return bucket
         return None
 
-    def step_e2e(self, world):
-        """Host buffers in, loss + pose gradient out; all copies inside the timed region."""
-        with torch.no_grad():
+    def prefetch(self, i):
+        """Enqueue the H2D copy of step i's inputs (all of them, from pinned memory) on the copy stream."""
+        st = self.sets[i % 2]
+        with torch.cuda.stream(self.copy_stream), torch.no_grad():
+            self.copy_stream.wait_event(st.compute_done)      # the step that last used this set has finished
             for k, h in self.host.items():
-                self.d[k].copy_(h, non_blocking=True)
-        self._zero_grads()
-        color, radii, depth, opacity, n_touched = self._forward()
-        loss = (color - self.d["target_color"]).abs().mean() + (depth - self.d["target_depth"]).abs().mean()
+                st.d[k].copy_(h, non_blocking=True)
+            st.copy_done.record(self.copy_stream)
+
+    def step_e2e(self, world):
+        """Host buffers in, loss + pose gradient out.  Every step's inputs cross PCIe inside the timed
+        region; the copy for step i+1 is issued at the start of step i so that it overlaps compute."""
+        i = self.e2e_i
+        self.e2e_i += 1
+        st = self.sets[i % 2]
+        if i == 0:
+            self.prefetch(0)
+        cur = torch.cuda.current_stream()
+        cur.wait_event(st.copy_done)
+        self.prefetch(i + 1)
+        self._zero_grads(st.leaves)
+        color, radii, depth, opacity, n_touched = self._forward(st)
+        loss = (color - st.d["target_color"]).abs().mean() + (depth - st.d["target_depth"]).abs().mean()
         loss.backward()
         if world > 1:
-            bucket = torch.cat([t.grad.reshape(-1) for t in self.leaves])
+            bucket = torch.cat([t.grad.reshape(-1) for t in st.leaves])
             dist.all_reduce(bucket)
         res = torch.cat([loss.detach().reshape(1), self.rho.grad.reshape(-1), self.theta.grad.reshape(-1)])
         self.out_host.copy_(res, non_blocking=True)
+        st.compute_done.record(cur)
 
 
 def timed_loop(fn, steps, warmup, flush, world):
@@ -341,7 +372,8 @@ def main():
     if not a.no_e2e:
         e2e_ms, _ = timed_loop(lambda: wl.step_e2e(world), a.steps, a.warmup, flush, world)
         e2e = {"value": round(frames / (e2e_ms * 1e-3), 3), "unit": "frames/s", "h2d_bytes_per_step": wl.h2d_bytes,
-               "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": round(e2e_ms / a.steps, 4)}
+               "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": round(e2e_ms / a.steps, 4),
+               "pipelining": "inputs of step i+1 copied on a second stream during step i (double-buffered)"}
 
     roof = stages = counts = None
     if a.impl == "ours" and rank == 0:

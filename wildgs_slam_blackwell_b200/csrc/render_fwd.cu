@@ -13,6 +13,48 @@
 
 namespace wgs {
 
+// Walk the survivors (bit mask m) of one 32-entry chunk front to back for this lane's pixel.
+// The arithmetic is the reference's rn-sequence (forward.cu:336-380).
+template <bool TOUCH>
+__device__ __forceinline__ void walk_survivors(const FwdStage& s, unsigned m, int c0, int round_base, float pixx,
+                                               float pixy, float& T, float& C0, float& C1, float& C2, float& D,
+                                               uint32_t& last_contributor, bool& done, int lane,
+                                               int* __restrict__ n_touched) {
+    while (m) {
+        const int j = c0 + __ffs(m) - 1;
+        m &= m - 1;
+        const float4 a = s.rec0[j];
+        const float4 b = s.rec1[j];
+        bool touched = false;
+        if (!done) {
+            const float dx = SUB(a.x, pixx), dy = SUB(a.y, pixy);
+            const float power = FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
+            if (!(power > 0.f)) {
+                const float alpha = fminf(MUL(b.y, expf(power)), 0.99f);
+                if (!(alpha < 1.0f / 255.0f)) {
+                    const float test_T = MUL(T, SUB(1.f, alpha));
+                    if (test_T < 0.0001f) {
+                        done = true;
+                    } else {
+                        const float4 col = s.col[j];
+                        C0 = FMA(T, MUL(alpha, col.x), C0);
+                        C1 = FMA(T, MUL(alpha, col.y), C1);
+                        C2 = FMA(T, MUL(alpha, col.z), C2);
+                        D = FMA(T, MUL(alpha, b.z), D);
+                        if (TOUCH) touched = test_T > 0.5f;
+                        T = test_T;
+                        last_contributor = (uint32_t)(round_base + j + 1);
+                    }
+                }
+            }
+        }
+        if (TOUCH) {
+            const unsigned tm = __ballot_sync(0xffffffffu, touched);
+            if (tm && lane == 0) atomicAdd(n_touched + s.id[j], __popc(tm));
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__ RenderFwdParams p) {
     __shared__ FwdStage st[2];
     if (p.tile.misc[MISC_OVERFLOW]) return;
@@ -79,40 +121,15 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
                 hit = reaches_rect(a.x, a.y, a.z, a.w, b.x, b.w, rx0, ry0, rx1, ry1);
             }
             unsigned m = __ballot_sync(0xffffffffu, hit);
-            while (m) {
-                const int j = c0 + __ffs(m) - 1;
-                m &= m - 1;
-                const float4 a = s.rec0[j];
-                const float4 b = s.rec1[j];
-                bool contrib = false, touched = false;
-                float alpha = 0.f, test_T = 0.f;
-                if (!done) {
-                    const float dx = SUB(a.x, pixx), dy = SUB(a.y, pixy);
-                    const float power =
-                        FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
-                    if (!(power > 0.f)) {
-                        alpha = fminf(MUL(b.y, expf(power)), 0.99f);
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            test_T = MUL(T, SUB(1.f, alpha));
-                            if (test_T < 0.0001f) done = true;
-                            else contrib = true;
-                        }
-                    }
-                }
-                if (contrib) {
-                    const float4 col = s.col[j];
-                    C0 = FMA(T, MUL(alpha, col.x), C0);
-                    C1 = FMA(T, MUL(alpha, col.y), C1);
-                    C2 = FMA(T, MUL(alpha, col.z), C2);
-                    D = FMA(T, MUL(alpha, b.z), D);
-                    touched = test_T > 0.5f;
-                    T = test_T;
-                    last_contributor = (uint32_t)(r * BATCH + j + 1);
-                }
-                const unsigned tm = __ballot_sync(0xffffffffu, touched);
-                if (tm && lane == 0) atomicAdd(p.n_touched + s.id[j], __popc(tm));
-                if (__all_sync(0xffffffffu, done)) { m = 0; c0 = count; }
-            }
+            // T only decreases: once no pixel of the warp has T > 0.5, n_touched cannot change any more
+            // (forward.cu:369-371 needs test_T > 0.5), and the cheaper loop without its vote is used.
+            if (__any_sync(0xffffffffu, !done && T > 0.5f))
+                walk_survivors<true>(s, m, c0, r * BATCH, pixx, pixy, T, C0, C1, C2, D, last_contributor, done, lane,
+                                     p.n_touched);
+            else
+                walk_survivors<false>(s, m, c0, r * BATCH, pixx, pixy, T, C0, C1, C2, D, last_contributor, done, lane,
+                                      p.n_touched);
+            if (__all_sync(0xffffffffu, done)) break;
         }
     }
     cp_async_wait<0>();
