@@ -21,16 +21,19 @@ constexpr int LARGE_MAX = 24576;   // 192 KB of keys, 1024-thread CTA, 1 CTA/SM
 constexpr int SMALL_THREADS = 512;
 constexpr int LARGE_THREADS = 1024;
 
+// K = number of privatised histogram copies (compile-time so that all K loads are in flight at once)
+template <int K>
 __global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__ BinParams p) {
     __shared__ uint32_t warp_sums[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint32_t carry = 0;
     for (int base = 0; base < p.tiles; base += 1024) {
         const int t = base + tid;
-        uint32_t c = 0;
-        if (t < p.tiles) {
-            for (int k = 0; k < p.copies; k++) c += p.tile.count[(size_t)k * p.tiles + t];
-        }
+        uint32_t c = 0, ck[K];
+#pragma unroll
+        for (int k = 0; k < K; k++) ck[k] = t < p.tiles ? __ldcg(p.tile.count + (size_t)k * p.tiles + t) : 0u;
+#pragma unroll
+        for (int k = 0; k < K; k++) c += ck[k];
         uint32_t v = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -53,9 +56,10 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__
         if (t < p.tiles) {
             p.tile.ranges[t] = make_uint2(excl, excl + c);
             uint32_t run = excl;  // copy k of this tile scatters into [run_k, run_k + count_k)
-            for (int k = 0; k < p.copies; k++) {
+#pragma unroll
+            for (int k = 0; k < K; k++) {
                 p.tile.cursor[(size_t)k * p.tiles + t] = run;
-                run += p.tile.count[(size_t)k * p.tiles + t];
+                run += ck[k];
             }
             if (c > (uint32_t)SMALL_MAX) p.tile.large_list[atomicAdd(p.tile.misc + MISC_N_LARGE, 1u)] = t;
         }
@@ -141,16 +145,119 @@ __device__ __forceinline__ void bitonic_sort(unsigned long long* a, int n, int t
     }
 }
 
+// One CTA sorts one tile segment of up to SMALL_MAX entries.  Depth keys inside a tile are spread
+// over a range, so instead of a comparison network the segment is bucketed: a monotone linear map
+// of the depth bits between the tile's min and max onto NB buckets (shared-memory histogram whose
+// atomicAdd return value is the entry's rank inside its bucket), an exclusive scan of the
+// histogram, a scatter into shared memory, and an insertion sort inside every bucket that
+// received more than one entry (full 64-bit compare, so equal depths end up in ascending-id
+// order exactly like the reference's stable radix sort).  Expected bucket occupancy is < 1 for
+// the typical tile and <= 4 at SMALL_MAX; a pathological depth distribution (some bucket holding
+// more than BUCKET_LIMIT entries) falls back to the bitonic network on the same buffer.
+constexpr int NB = 1024;
+constexpr int BUCKET_LIMIT = 32;
+constexpr int EPT = SMALL_MAX / SMALL_THREADS;  // entries per thread
+
 __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __grid_constant__ BinParams p) {
-    __shared__ unsigned long long keys[SMALL_MAX];
+    __shared__ unsigned long long out[SMALL_MAX];
+    __shared__ uint32_t hist[NB];
+    __shared__ uint32_t wsum[SMALL_THREADS / 32];
+    __shared__ uint32_t s_min, s_max, s_maxcnt;
     const uint2 r = p.tile.ranges[blockIdx.x];
     const int n = (int)(r.y - r.x);
     if (n < 2 || n > SMALL_MAX || p.tile.misc[MISC_OVERFLOW]) return;
     unsigned long long* seg = p.bucket + r.x;
-    for (int i = threadIdx.x; i < n; i += SMALL_THREADS) keys[i] = seg[i];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    unsigned long long key[EPT];
+    uint32_t lo = 0xffffffffu, hi = 0u;
+#pragma unroll
+    for (int e = 0; e < EPT; e++) {
+        const int i = tid + e * SMALL_THREADS;
+        if (i < n) {
+            key[e] = seg[i];
+            const uint32_t d = (uint32_t)(key[e] >> 32);
+            lo = min(lo, d);
+            hi = max(hi, d);
+        }
+    }
+    for (int i = tid; i < NB; i += SMALL_THREADS) hist[i] = 0;
+    if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; }
     __syncthreads();
-    bitonic_sort(keys, n, threadIdx.x, SMALL_THREADS);
-    for (int i = threadIdx.x; i < n; i += SMALL_THREADS) seg[i] = keys[i];
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
+    if (lane == 0) { atomicMin(&s_min, lo); atomicMax(&s_max, hi); }
+    __syncthreads();
+    const uint32_t kmin = s_min;
+    const float scale = (float)NB / ((float)(s_max - kmin) + 1.0f);
+    uint32_t br[EPT];  // bucket << 12 | rank inside the bucket
+#pragma unroll
+    for (int e = 0; e < EPT; e++) {
+        const int i = tid + e * SMALL_THREADS;
+        if (i < n) {
+            const uint32_t d = (uint32_t)(key[e] >> 32);
+            // monotone non-decreasing in d: u32->f32 conversion, positive scale, truncation, clamp
+            const uint32_t bkt = min((uint32_t)((float)(d - kmin) * scale), (uint32_t)(NB - 1));
+            br[e] = (bkt << 12) | atomicAdd(&hist[bkt], 1u);
+        }
+    }
+    __syncthreads();
+    // exclusive scan of the histogram in place (2 buckets per thread) + largest bucket
+    {
+        static_assert(NB == 2 * SMALL_THREADS, "scan assumes two buckets per thread");
+        const uint32_t c0 = hist[2 * tid], c1 = hist[2 * tid + 1];
+        uint32_t v = c0 + c1;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += u;
+        }
+        if (lane == 31) wsum[warp] = v;
+        const uint32_t mx = __reduce_max_sync(0xffffffffu, max(c0, c1));
+        if (lane == 0) atomicMax(&s_maxcnt, mx);
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = lane < SMALL_THREADS / 32 ? wsum[lane] : 0u;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += u;
+            }
+            if (lane < SMALL_THREADS / 32) wsum[lane] = w;
+        }
+        __syncthreads();
+        const uint32_t excl = (warp ? wsum[warp - 1] : 0u) + v - (c0 + c1);
+        hist[2 * tid] = excl;
+        hist[2 * tid + 1] = excl + c0;
+    }
+    __syncthreads();
+    if (s_maxcnt > (uint32_t)BUCKET_LIMIT) {
+#pragma unroll
+        for (int e = 0; e < EPT; e++) {
+            const int i = tid + e * SMALL_THREADS;
+            if (i < n) out[i] = key[e];
+        }
+        __syncthreads();
+        bitonic_sort(out, n, tid, SMALL_THREADS);
+    } else {
+#pragma unroll
+        for (int e = 0; e < EPT; e++) {
+            const int i = tid + e * SMALL_THREADS;
+            if (i < n) out[hist[br[e] >> 12] + (br[e] & 0xfffu)] = key[e];
+        }
+        __syncthreads();
+        for (int bkt = tid; bkt < NB; bkt += SMALL_THREADS) {
+            const int s0 = (int)hist[bkt], e0 = bkt + 1 < NB ? (int)hist[bkt + 1] : n;
+            for (int i = s0 + 1; i < e0; i++) {  // insertion sort of out[s0, e0)
+                const unsigned long long k = out[i];
+                int j = i - 1;
+                while (j >= s0 && out[j] > k) { out[j + 1] = out[j]; j--; }
+                out[j + 1] = k;
+            }
+        }
+        __syncthreads();
+    }
+    for (int i = tid; i < n; i += SMALL_THREADS) seg[i] = out[i];
 }
 
 __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __grid_constant__ BinParams p) {
@@ -210,7 +317,16 @@ __global__ void export_geometry_kernel(int P, GeomView g, const int* radii, floa
     if (clamped) { clamped[3 * i] = cb & 1; clamped[3 * i + 1] = (cb >> 1) & 1; clamped[3 * i + 2] = (cb >> 2) & 1; }
 }
 
-void launch_tile_scan(const BinParams& p, cudaStream_t s) { tile_scan_kernel<<<1, 1024, 0, s>>>(p); }
+void launch_tile_scan(const BinParams& p, cudaStream_t s) {
+    switch (p.copies) {
+        case 32: tile_scan_kernel<32><<<1, 1024, 0, s>>>(p); break;
+        case 16: tile_scan_kernel<16><<<1, 1024, 0, s>>>(p); break;
+        case 8: tile_scan_kernel<8><<<1, 1024, 0, s>>>(p); break;
+        case 4: tile_scan_kernel<4><<<1, 1024, 0, s>>>(p); break;
+        case 2: tile_scan_kernel<2><<<1, 1024, 0, s>>>(p); break;
+        default: tile_scan_kernel<1><<<1, 1024, 0, s>>>(p); break;
+    }
+}
 
 void launch_scatter(const BinParams& p, cudaStream_t s) {
     if (p.P > 0) scatter_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p);

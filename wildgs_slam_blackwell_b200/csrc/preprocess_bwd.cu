@@ -47,10 +47,24 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
     const int idx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
     float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (idx < p.P) {
-        const bool vis = p.radii[idx] > 0;
-        float4 g0 = make_float4(0, 0, 0, 0), g1 = g0, g2 = g0;
+        // Issue every load this Gaussian can need before looking at radii, so that the latencies
+        // overlap (the kernel is latency-bound: 108 registers, 2 CTAs/SM).  Accumulator records of
+        // culled Gaussians are never written, so they read as zero.
+        const int rad = __ldg(p.radii + idx);
+        float4 g0 = __ldcg(p.grad.acc + 3 * idx), g1 = __ldcg(p.grad.acc + 3 * idx + 1), g2 = __ldcg(p.grad.acc + 3 * idx + 2);
+        const V3 m = {__ldg(p.means3D + 3 * idx), __ldg(p.means3D + 3 * idx + 1), __ldg(p.means3D + 3 * idx + 2)};
+        float s3[3] = {0.f, 0.f, 0.f}, q4[4] = {1.f, 0.f, 0.f, 0.f}, c3[6];
+        if (p.cov3D_precomp) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) c3[k] = __ldg(p.cov3D_precomp + 6 * idx + k);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 3; k++) s3[k] = __ldg(p.scales + 3 * idx + k);
+#pragma unroll
+            for (int k = 0; k < 4; k++) q4[k] = __ldg(p.rotations + 4 * idx + k);
+        }
+        const bool vis = rad > 0;
         if (vis) {
-            g0 = p.grad.acc[3 * idx]; g1 = p.grad.acc[3 * idx + 1]; g2 = p.grad.acc[3 * idx + 2];
             const float4 z4 = make_float4(0, 0, 0, 0);
             p.grad.acc[3 * idx] = z4; p.grad.acc[3 * idx + 1] = z4; p.grad.acc[3 * idx + 2] = z4;
         }
@@ -67,17 +81,8 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
         if (vis) {
             const float* __restrict__ V = p.viewmatrix;
             const float* __restrict__ Pm = p.projmatrix;
-            const V3 m = {__ldg(p.means3D + 3 * idx), __ldg(p.means3D + 3 * idx + 1), __ldg(p.means3D + 3 * idx + 2)};
-            float c3[6], Rq[9], sc[3], q4[4];
-            if (p.cov3D_precomp) {
-#pragma unroll
-                for (int k = 0; k < 6; k++) c3[k] = __ldg(p.cov3D_precomp + 6 * idx + k);
-            } else {
-                const float s3[3] = {__ldg(p.scales + 3 * idx), __ldg(p.scales + 3 * idx + 1), __ldg(p.scales + 3 * idx + 2)};
-#pragma unroll
-                for (int k = 0; k < 4; k++) q4[k] = __ldg(p.rotations + 4 * idx + k);
-                cov3d_natural(s3, p.scale_modifier, q4, c3, Rq, sc);
-            }
+            float Rq[9], sc[3];
+            if (!p.cov3D_precomp) cov3d_natural(s3, p.scale_modifier, q4, c3, Rq, sc);
             // ---- computeCov2DCUDA (backward.cu:150-346) ----
             V3 t = {V[0] * m.x + V[4] * m.y + V[8] * m.z + V[12], V[1] * m.x + V[5] * m.y + V[9] * m.z + V[13],
                     V[2] * m.x + V[6] * m.y + V[10] * m.z + V[14]};
