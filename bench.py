@@ -166,6 +166,27 @@ class Workload:
         self.h2d_bytes = sum(v.numel() * 4 for v in self.host.values())
         self.d2h_bytes = 7 * 4
         self.bucket_floats = sum(t.numel() for t in self.leaves)
+        # multi-GPU: the backward kernel writes the Gaussian gradients straight into one flat bucket
+        # (rasterizer.grad_sink) that NCCL then sums in place -- no packing copy
+        self.bucket = torch.zeros(self.bucket_floats, dtype=torch.float32, device=dev)
+        self.sink = None
+        if hasattr(mod, "grad_sink"):
+            views, off = {}, 0
+            for name, t in zip(("means3D", "sh", "opacity", "scales", "rotations"), self.leaves):
+                views[name] = self.bucket[off:off + t.numel()].view(t.shape)
+                off += t.numel()
+            self.sink = mod.grad_sink(views)
+
+    def _backward(self, world, fn):
+        if world > 1 and self.sink is not None:
+            with self.sink:
+                fn()
+            dist.all_reduce(self.bucket)
+        else:
+            fn()
+            if world > 1:
+                st = self.sets[0]
+                dist.all_reduce(torch.cat([t.grad.reshape(-1) for t in st.leaves]))
 
     def _zero_grads(self, leaves):
         for t in leaves + [self.means2D, self.theta, self.rho]:
@@ -181,12 +202,7 @@ class Workload:
         st = self.sets[0]
         self._zero_grads(st.leaves)
         color, radii, depth, opacity, n_touched = self._forward(st)
-        torch.autograd.backward([color, depth], [self.dc, self.dd])
-        if world > 1:
-            bucket = torch.cat([t.grad.reshape(-1) for t in st.leaves])
-            dist.all_reduce(bucket)
-            return bucket
-        return None
+        self._backward(world, lambda: torch.autograd.backward([color, depth], [self.dc, self.dd]))
 
     def prefetch(self, i):
         """Enqueue the H2D copy of step i's inputs (all of them, from pinned memory) on the copy stream."""
@@ -211,10 +227,7 @@ class Workload:
         self._zero_grads(st.leaves)
         color, radii, depth, opacity, n_touched = self._forward(st)
         loss = (color - st.d["target_color"]).abs().mean() + (depth - st.d["target_depth"]).abs().mean()
-        loss.backward()
-        if world > 1:
-            bucket = torch.cat([t.grad.reshape(-1) for t in st.leaves])
-            dist.all_reduce(bucket)
+        self._backward(world, loss.backward)
         res = torch.cat([loss.detach().reshape(1), self.rho.grad.reshape(-1), self.theta.grad.reshape(-1)])
         self.out_host.copy_(res, non_blocking=True)
         st.compute_done.record(cur)

@@ -11,6 +11,7 @@ from wildgs_slam_blackwell_b200.rasterizer import (  # noqa: F401
     rasterize_gaussians,
     _RasterizeGaussians,
     cpu_deep_copy_tuple,
+    grad_sink,
 )
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]

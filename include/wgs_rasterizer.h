@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define WGS_ABI_VERSION 5
+#define WGS_ABI_VERSION 6
 
 /* status codes (negative = error) */
 #define WGS_OK 0
@@ -97,6 +97,8 @@ typedef struct WgsBackwardArgs {
   int32_t P, sh_degree, M, width, height;
   float tanfovx, tanfovy, scale_modifier;
   int32_t debug;
+  int32_t accumulate; /* 0: gradient outputs are overwritten; 1: added to (lets a keyframe window sum the
+                         per-view Gaussian gradients in place; dL_dtau is always overwritten) */
   const float* background;
   const float* means3D;
   const float* sh;
@@ -112,7 +114,7 @@ typedef struct WgsBackwardArgs {
   /* cotangents (device); dL_dopacity-image is ignored like the reference (__init__.py:108) */
   const float* dL_dout_color;  /* (3,H,W) */
   const float* dL_dout_depth;  /* (1,H,W) */
-  /* gradient outputs (device, caller-allocated, need NOT be pre-zeroed; any may be null) */
+  /* gradient outputs (device, caller-allocated, need NOT be pre-zeroed unless accumulate; any may be null) */
   float* dL_dmeans3D;   /* (P,3) */
   float* dL_dmeans2D;   /* (P,3), z = 0 */
   float* dL_dsh;        /* (P,M,3)   (sh path) */

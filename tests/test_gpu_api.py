@@ -203,3 +203,39 @@ def test_config4_shape_sh3_1080p_matches_reference():
     util.assert_grad_close("sh", o["g_dL_dsh"], n(gr["dL_dsh"]))
     util.assert_grad_close("means3D", o["g_dL_dmeans3D"], n(gr["dL_dmeans3D"]))
     util.assert_grad_close("tau", o["g_dL_dtau_sum"], n(gr["dL_dtau_sum"]))
+
+
+def test_grad_sink_writes_and_accumulates_in_place():
+    """rasterizer.grad_sink (used by the mapping window): gradients land in caller buffers, autograd gets
+    None for them, accumulate=True adds; pose gradients still flow through autograd."""
+    g, cams, cots = scenes.make_scene(3000, 128, 96, 0, seed=31)
+    base = util.run_ours(g, cams[0], cots[0], export=False)
+    s = util.settings_from_cam(cams[0], 0)
+    leaf = lambda a: util.to_dev(a).requires_grad_(True)
+    m3, op, sh, sc, ro = leaf(g["means3D"]), leaf(g["opacities"]), leaf(g["sh"]), leaf(g["scales"]), leaf(g["rotations"])
+    m2 = torch.zeros(3000, 3, device=DEV, requires_grad=True)
+    th, rh = torch.zeros(3, device=DEV, requires_grad=True), torch.zeros(3, device=DEV, requires_grad=True)
+    flat = torch.full((3000 * 14,), 7.0, device=DEV)             # garbage: first pass must overwrite
+    bufs, off = {}, 0
+    for name, t in (("means3D", m3), ("sh", sh), ("opacity", op), ("scales", sc), ("rotations", ro)):
+        bufs[name] = flat[off:off + t.numel()].view(t.shape)
+        off += t.numel()
+    dc, dd = util.to_dev(cots[0][0]), util.to_dev(cots[0][1])
+    rast = rasterizer.GaussianRasterizer(s)
+    for k in range(2):
+        color, radii, depth, opacity, n_touched = rast(m3, m2, op, shs=sh, scales=sc, rotations=ro, theta=th, rho=rh)
+        with rasterizer.grad_sink(bufs, accumulate=k > 0):
+            ((color * dc).sum() + (depth * dd).sum()).backward()
+        assert m3.grad is None and sh.grad is None and op.grad is None
+        mult = float(k + 1)
+        util.assert_grad_close("means3D", bufs["means3D"].cpu().numpy(), mult * base["g_dL_dmeans3D"])
+        util.assert_grad_close("sh", bufs["sh"].cpu().numpy(), mult * base["g_dL_dsh"])
+        util.assert_grad_close("opacity", bufs["opacity"].cpu().numpy(), mult * base["g_dL_dopacity"])
+        util.assert_grad_close("scales", bufs["scales"].cpu().numpy(), mult * base["g_dL_dscales"])
+        util.assert_grad_close("rotations", bufs["rotations"].cpu().numpy(), mult * base["g_dL_drotations"])
+    tau = np.concatenate([rh.grad.cpu().numpy().reshape(-1), th.grad.cpu().numpy().reshape(-1)])
+    util.assert_grad_close("tau", tau, 2.0 * base["g_dL_dtau_sum"])       # autograd accumulated the two passes
+    with pytest.raises(RuntimeError, match="grad_sink buffer"):
+        color, *_ = rast(m3, m2, op, shs=sh, scales=sc, rotations=ro, theta=th, rho=rh)
+        with rasterizer.grad_sink({"means3D": torch.zeros(5, 3, device=DEV)}):
+            color.sum().backward()

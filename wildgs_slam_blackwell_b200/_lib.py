@@ -5,7 +5,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libwgs_rasterizer.so")
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 WGS_OK = 0
 WGS_ERR_INVALID_ARGUMENT = -1
@@ -39,6 +39,7 @@ class BackwardArgs(C.Structure):
     _fields_ = [
         ("P", C.c_int32), ("sh_degree", C.c_int32), ("M", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
         ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float), ("debug", C.c_int32),
+        ("accumulate", C.c_int32),
         ("background", _fp), ("means3D", _fp), ("sh", _fp), ("colors_precomp", _fp), ("scales", _fp),
         ("rotations", _fp), ("cov3D_precomp", _fp), ("viewmatrix", _fp), ("projmatrix", _fp),
         ("projmatrix_raw", _fp), ("campos", _fp), ("radii", _fp),

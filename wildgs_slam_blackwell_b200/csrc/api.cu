@@ -240,7 +240,7 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     MARK(ctx, 7, s);
 
     PreBwdParams pb;
-    pb.P = a->P; pb.D = a->sh_degree; pb.M = a->M; pb.W = a->width; pb.H = a->height;
+    pb.P = a->P; pb.D = a->sh_degree; pb.M = a->M; pb.W = a->width; pb.H = a->height; pb.accumulate = a->accumulate;
     pb.tanfovx = a->tanfovx; pb.tanfovy = a->tanfovy;
     pb.focal_y = a->height / (2.0f * a->tanfovy);
     pb.focal_x = a->width / (2.0f * a->tanfovx);

@@ -48,7 +48,7 @@ struct RenderBwdParams {
 };
 
 struct PreBwdParams {
-    int P, D, M, W, H;
+    int P, D, M, W, H, accumulate;
     float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
     const float *means3D, *sh, *colors_precomp, *scales, *rotations, *cov3D_precomp;
     const float *viewmatrix, *projmatrix, *projmatrix_raw, *campos;

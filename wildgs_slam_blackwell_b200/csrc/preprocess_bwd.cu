@@ -21,6 +21,11 @@ __device__ __forceinline__ V3 cross(V3 a, V3 b) {
     return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
 }
 
+// gradient store: overwrite, or add to what the buffer holds (WgsBackwardArgs::accumulate)
+__device__ __forceinline__ void gput(float* __restrict__ ptr, size_t i, float v, bool acc) {
+    ptr[i] = acc ? ptr[i] + v : v;
+}
+
 __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const float* q4, float c[6], float R[9],
                                               float s[3]) {
     // R[3*col + row] as GLM stores it (reference computeCov3D, forward.cu:120-154)
@@ -45,6 +50,7 @@ __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const 
 
 __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
     const int idx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
+    const bool accm = p.accumulate != 0;
     float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (idx < p.P) {
         // Issue every load this Gaussian can need before looking at radii, so that the latencies
@@ -183,7 +189,9 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
                 const float il = 1.f / sqrtf(dot(dir_orig, dir_orig));
                 const float x = dir_orig.x * il, y = dir_orig.y * il, z = dir_orig.z * il;
                 auto SH = [&](int k) { return V3{__ldg(sh + 3 * k), __ldg(sh + 3 * k + 1), __ldg(sh + 3 * k + 2)}; };
-                auto put = [&](int k, float w) { dsh[3 * k] = w * dRGB.x; dsh[3 * k + 1] = w * dRGB.y; dsh[3 * k + 2] = w * dRGB.z; };
+                auto put = [&](int k, float w) {
+                    gput(dsh, 3 * k, w * dRGB.x, accm); gput(dsh, 3 * k + 1, w * dRGB.y, accm); gput(dsh, 3 * k + 2, w * dRGB.z, accm);
+                };
                 V3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
                 put(0, kSH_C0);
                 if (p.D > 0) {
@@ -268,20 +276,21 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
             }
         } else if (p.sh && p.dL_dsh) {
             float* __restrict__ dsh = p.dL_dsh + (size_t)idx * p.M * 3;
-            for (int k = 0; k < 3 * p.M; k++) dsh[k] = 0.f;
+            if (!accm)
+                for (int k = 0; k < 3 * p.M; k++) dsh[k] = 0.f;
         }
-        if (p.dL_dmeans3D) { p.dL_dmeans3D[3 * idx] = dmean.x; p.dL_dmeans3D[3 * idx + 1] = dmean.y; p.dL_dmeans3D[3 * idx + 2] = dmean.z; }
-        if (p.dL_dmeans2D) { p.dL_dmeans2D[3 * idx] = dm2x; p.dL_dmeans2D[3 * idx + 1] = dm2y; p.dL_dmeans2D[3 * idx + 2] = 0.f; }
-        if (p.dL_dopacity) p.dL_dopacity[idx] = dop;
-        if (p.dL_dcolors) { p.dL_dcolors[3 * idx] = dcol[0]; p.dL_dcolors[3 * idx + 1] = dcol[1]; p.dL_dcolors[3 * idx + 2] = dcol[2]; }
+        if (p.dL_dmeans3D) { gput(p.dL_dmeans3D, 3 * idx, dmean.x, accm); gput(p.dL_dmeans3D, 3 * idx + 1, dmean.y, accm); gput(p.dL_dmeans3D, 3 * idx + 2, dmean.z, accm); }
+        if (p.dL_dmeans2D) { gput(p.dL_dmeans2D, 3 * idx, dm2x, accm); gput(p.dL_dmeans2D, 3 * idx + 1, dm2y, accm); gput(p.dL_dmeans2D, 3 * idx + 2, 0.f, accm); }
+        if (p.dL_dopacity) gput(p.dL_dopacity, idx, dop, accm);
+        if (p.dL_dcolors) { gput(p.dL_dcolors, 3 * idx, dcol[0], accm); gput(p.dL_dcolors, 3 * idx + 1, dcol[1], accm); gput(p.dL_dcolors, 3 * idx + 2, dcol[2], accm); }
         if (p.dL_dcov3D) {
 #pragma unroll
-            for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * idx + k] = dcov[k];
+            for (int k = 0; k < 6; k++) gput(p.dL_dcov3D, 6 * idx + k, dcov[k], accm);
         }
-        if (p.dL_dscales) { p.dL_dscales[3 * idx] = dscale[0]; p.dL_dscales[3 * idx + 1] = dscale[1]; p.dL_dscales[3 * idx + 2] = dscale[2]; }
+        if (p.dL_dscales) { gput(p.dL_dscales, 3 * idx, dscale[0], accm); gput(p.dL_dscales, 3 * idx + 1, dscale[1], accm); gput(p.dL_dscales, 3 * idx + 2, dscale[2], accm); }
         if (p.dL_drotations) {
 #pragma unroll
-            for (int k = 0; k < 4; k++) p.dL_drotations[4 * idx + k] = drot[k];
+            for (int k = 0; k < 4; k++) gput(p.dL_drotations, 4 * idx + k, drot[k], accm);
         }
     }
     // ---- pose gradient: warp -> block -> grid, deterministic ----

@@ -162,8 +162,34 @@ def _grad_workspace(device, P):
     return ent[1]
 
 
+class grad_sink:
+    """Context manager (new capability, used by the multi-GPU mapping window): while active, the
+    backward writes the Gaussian-parameter gradients straight into the caller's buffers
+    (`buffers`: any of 'means3D', 'sh', 'colors', 'opacity', 'scales', 'rotations', 'cov3D' ->
+    float32 CUDA tensor of the gradient's shape, e.g. slices of one flat allreduce bucket) and
+    autograd receives None for them; with accumulate=True the kernel adds to the buffers instead
+    of overwriting, so a window of views sums in place.  Pose gradients still flow through autograd.
+
+        with grad_sink(bucket_views, accumulate=(k > 0)):
+            loss_k.backward()
+    """
+    _active = None
+
+    def __init__(self, buffers, accumulate=False):
+        self.buffers, self.accumulate = dict(buffers), bool(accumulate)
+
+    def __enter__(self):
+        self._prev = grad_sink._active
+        grad_sink._active = self
+        return self
+
+    def __exit__(self, *exc):
+        grad_sink._active = self._prev
+        return False
+
+
 def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii,
-                 grad_out_color, grad_out_depth):
+                 grad_out_color, grad_out_depth, sink=None):
     """Runs the backward through the C ABI.  Returns dict of gradient tensors (+ 'tau' (6,))."""
     device = means3D.device
     lib = _lib.load()
@@ -177,16 +203,29 @@ def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_p
         grad_out_color = _f32c(grad_out_color, device)
         grad_out_depth = _f32c(grad_out_depth, device)
         proj_raw = _f32c(s.projmatrix_raw, device)
-        e = lambda *shape: torch.empty(shape, dtype=torch.float32, device=device)
-        g = dict(means3D=e(P, 3), means2D=e(P, 3), opacity=e(P, 1), tau=e(6))
-        g["sh"] = e(P, M, 3) if use_sh else None
-        g["colors"] = e(P, 3) if fa.colors_precomp else None
-        g["scales"] = e(P, 3) if not fa.cov3D_precomp else None
-        g["rotations"] = e(P, 4) if not fa.cov3D_precomp else None
-        g["cov3D"] = e(P, 6) if fa.cov3D_precomp else None
+        def e(name, *shape):
+            if sink is not None and name in sink.buffers:
+                t = sink.buffers[name]
+                if (tuple(t.shape) != shape or t.dtype != torch.float32 or t.device != device or
+                        not t.is_contiguous()):
+                    raise RuntimeError(f"grad_sink buffer '{name}' must be a contiguous float32 {shape} tensor on {device}")
+                return t
+            if sink is not None and sink.accumulate and name not in ("means2D", "tau"):
+                raise RuntimeError(f"grad_sink(accumulate=True) needs a buffer for '{name}'")
+            return torch.empty(shape, dtype=torch.float32, device=device)
+        g = dict(means3D=e("means3D", P, 3), means2D=None, opacity=e("opacity", P, 1), tau=e("tau", 6))
+        # dL_dmeans2D only feeds densification statistics; in accumulate mode it is skipped (null)
+        if sink is None or not sink.accumulate or "means2D" in sink.buffers:
+            g["means2D"] = e("means2D", P, 3)
+        g["sh"] = e("sh", P, M, 3) if use_sh else None
+        g["colors"] = e("colors", P, 3) if fa.colors_precomp else None
+        g["scales"] = e("scales", P, 3) if not fa.cov3D_precomp else None
+        g["rotations"] = e("rotations", P, 4) if not fa.cov3D_precomp else None
+        g["cov3D"] = e("cov3D", P, 6) if fa.cov3D_precomp else None
         b = _lib.BackwardArgs()
         b.P, b.sh_degree, b.M, b.width, b.height = P, fa.sh_degree, M, W, H
         b.tanfovx, b.tanfovy, b.scale_modifier, b.debug = fa.tanfovx, fa.tanfovy, fa.scale_modifier, fa.debug
+        b.accumulate = int(sink is not None and sink.accumulate)
         b.background, b.means3D, b.sh, b.colors_precomp = fa.background, fa.means3D, fa.sh, fa.colors_precomp
         b.scales, b.rotations, b.cov3D_precomp = fa.scales, fa.rotations, fa.cov3D_precomp
         b.viewmatrix, b.projmatrix, b.projmatrix_raw, b.campos = fa.viewmatrix, fa.projmatrix, _ptr(proj_raw), fa.campos
@@ -248,10 +287,11 @@ class _RasterizeGaussians(torch.autograd.Function):
             grad_out_color = torch.zeros((3, s.image_height, s.image_width), device=means3D.device)
         if grad_out_depth is None:
             grad_out_depth = torch.zeros((1, s.image_height, s.image_width), device=means3D.device)
+        sink = grad_sink._active
         args = (ctx.state, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii, grad_out_color,
-                grad_out_depth)
+                grad_out_depth, sink)
         if s.debug:
-            cpu_args = cpu_deep_copy_tuple(args[2:] + tuple(s))
+            cpu_args = cpu_deep_copy_tuple(args[2:-1] + tuple(s))
             try:
                 g = backward_raw(*args)
             except Exception as ex:
@@ -265,6 +305,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         th_shape, rho_shape = ctx.pose_shapes
         grad_rho = g["tau"][:3].view(rho_shape if len(rho_shape) and rho_shape.numel() == 3 else (1, 3))
         grad_theta = g["tau"][3:].view(th_shape if len(th_shape) and th_shape.numel() == 3 else (1, 3))
+        if sink is not None:   # sunk gradients do not go through autograd
+            for k in sink.buffers:
+                g[k] = None
         return (g["means3D"], g["means2D"], g["sh"], g["colors"], g["opacity"], g["scales"], g["rotations"],
                 g["cov3D"], grad_theta, grad_rho, None)
 

@@ -55,9 +55,10 @@ class GradBucket:
         return list(params) == self.names and all(params[k].shape == self.views[k].shape and
                                                   params[k].device == self.flat.device for k in params)
 
-    def install(self):
-        """Zero the buffer and point every leaf's .grad at its slice."""
-        self.flat.zero_()
+    def install(self, zero=True):
+        """Point every leaf's .grad at its slice (optionally zeroing the buffer first)."""
+        if zero:
+            self.flat.zero_()
         for k, p in self.params.items():
             p.grad = self.views[k]
 
@@ -78,7 +79,14 @@ class WindowTrainer:
     rank), `out["losses"]` (n_views,), `out["pose_grads"]` (n_views, 6), `out["assignment"]`.
     """
 
-    def __init__(self, params: Dict[str, torch.Tensor], group: Optional[dist.ProcessGroup] = None):
+    def __init__(self, params: Dict[str, torch.Tensor], group: Optional[dist.ProcessGroup] = None,
+                 sink_names: Optional[Dict[str, str]] = None):
+        """`sink_names` (optional): leaf name -> rasterizer gradient name ('means3D', 'sh', 'opacity',
+        'scales', 'rotations', ...).  When given, the rasterizer's backward kernel writes / accumulates
+        straight into the bucket (rasterizer.grad_sink) instead of autograd allocating per-view
+        gradient tensors and adding them; requires that the leaves are passed to the rasterizer
+        unmodified (no activation in between)."""
+        self.sink_names = sink_names
         self.group = group
         self.distributed = dist.is_available() and dist.is_initialized()
         self.world = dist.get_world_size(group) if self.distributed else 1
@@ -99,16 +107,29 @@ class WindowTrainer:
         assignment = assign_views(self.costs, self.world)
         mine = assignment[self.rank]
         b = self.bucket
-        b.install()
+        use_sink = self.sink_names is not None and len(mine) > 0
+        if use_sink:
+            from . import rasterizer
+            sink_bufs = {g: b.views[k] for k, g in self.sink_names.items()}
+            for p in b.params.values():
+                p.grad = None
+        else:
+            b.install()
         dev = b.flat.device
         side = torch.zeros(n_views, 8, dtype=torch.float32, device=dev)  # loss, cost, pose grad (6)
-        for v in mine:
+        for n_done, v in enumerate(mine):
             loss, pose_grad_fn = render_loss(v)
-            loss.backward()
+            if use_sink:
+                with rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0):
+                    loss.backward()
+            else:
+                loss.backward()
             side[v, 0] = loss.detach()
             side[v, 1] = float(cost_fn(v)) if cost_fn is not None else 1.0
             if pose_grad_fn is not None:
                 side[v, 2:8] = pose_grad_fn().reshape(6)
+        if use_sink:
+            b.install(zero=False)
         if self.world > 1:
             work = dist.all_reduce(b.flat, group=self.group, async_op=True)
             dist.all_reduce(side, group=self.group)
