@@ -239,3 +239,36 @@ def test_grad_sink_writes_and_accumulates_in_place():
         color, *_ = rast(m3, m2, op, shs=sh, scales=sc, rotations=ro, theta=th, rho=rh)
         with rasterizer.grad_sink({"means3D": torch.zeros(5, 3, device=DEV)}):
             color.sum().backward()
+
+
+def test_window_trainer_sums_views_with_and_without_sink():
+    """WindowTrainer on one GPU, 3 views: bucket == sum over views of the single-view gradients,
+    whether autograd accumulates (.grad views) or the backward kernel accumulates (grad_sink)."""
+    from wildgs_slam_blackwell_b200.window import WindowTrainer
+    g, cams, cots = scenes.make_scene(4000, 160, 112, 0, seed=41, n_views=3)
+    singles = [util.run_ours(g, cams[k], cots[k], export=False) for k in range(3)]
+    want = {n: sum(s[key] for s in singles) for n, key in (("means3D", "g_dL_dmeans3D"), ("sh", "g_dL_dsh"),
+            ("opacities", "g_dL_dopacity"), ("scales", "g_dL_dscales"), ("rotations", "g_dL_drotations"))}
+    for sink in (None, {"means3D": "means3D", "sh": "sh", "opacities": "opacity", "scales": "scales",
+                        "rotations": "rotations"}):
+        params = {k: util.to_dev(g[k]).requires_grad_(True) for k in ("means3D", "sh", "opacities", "scales", "rotations")}
+        tr = WindowTrainer(params, sink_names=sink)
+        m2 = torch.zeros(4000, 3, device=DEV, requires_grad=True)
+        poses = [(torch.zeros(3, device=DEV, requires_grad=True), torch.zeros(3, device=DEV, requires_grad=True)) for _ in range(3)]
+
+        def render_loss(v):
+            th, rh = poses[v]
+            th.grad = rh.grad = None
+            rast = rasterizer.GaussianRasterizer(util.settings_from_cam(cams[v], 0))
+            color, radii, depth, opacity, n_touched = rast(params["means3D"], m2, params["opacities"], shs=params["sh"],
+                                                           scales=params["scales"], rotations=params["rotations"], theta=th, rho=rh)
+            loss = (color * util.to_dev(cots[v][0])).sum() + (depth * util.to_dev(cots[v][1])).sum()
+            return loss, (lambda: torch.cat([rh.grad.reshape(-1), th.grad.reshape(-1)]))
+        for _ in range(2):                      # second step re-uses the bucket: must not carry over
+            out = tr.step(3, render_loss)
+        for n in want:
+            assert params[n].grad.data_ptr() == tr.bucket.views[n].data_ptr()
+            util.assert_grad_close(n, params[n].grad.cpu().numpy(), want[n])
+        for v in range(3):
+            util.assert_grad_close(f"tau{v}", out["pose_grads"][v].cpu().numpy(), singles[v]["g_dL_dtau_sum"])
+        assert out["assignment"] == [[0, 1, 2]]
