@@ -272,3 +272,14 @@ def test_window_trainer_sums_views_with_and_without_sink():
         for v in range(3):
             util.assert_grad_close(f"tau{v}", out["pose_grads"][v].cpu().numpy(), singles[v]["g_dL_dtau_sum"])
         assert out["assignment"] == [[0, 1, 2]]
+
+
+def test_more_than_8192_tiles_uses_single_block_scan():
+    """2048x1100 = 8832 tiles: beyond the 8-CTA cluster scan, exercises the fallback scan kernel."""
+    g, cams, cots = scenes.make_scene(20000, 2048, 1100, 0, seed=51)
+    o = cpu_oracle.forward_backward(g, cams[0], None, export=True)
+    ours = util.run_ours(g, cams[0], None)
+    assert int(ours["num_rendered"]) == int(o["num_rendered"])
+    np.testing.assert_array_equal(ours["st_ranges"].view(np.uint32), o["st_ranges"])
+    np.testing.assert_array_equal(ours["st_point_list"].view(np.uint32), o["st_point_list"])
+    np.testing.assert_array_equal(ours["radii"], o["radii"])

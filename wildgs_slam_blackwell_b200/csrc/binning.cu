@@ -11,8 +11,12 @@
 // Because gaussian ids are unique inside a tile, ordering by (depth_bits, id) is a total order
 // and equals the order the reference's STABLE radix sort produces (ties keep emission order =
 // ascending id), so sorted ids, keys and ranges are bit-identical.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 #include "kernels.h"
+
+namespace cg = cooperative_groups;
 
 namespace wgs {
 
@@ -69,11 +73,74 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__
     if (tid == 0) {
         p.tile.misc[MISC_NUM_RENDERED] = carry;
         p.tile.misc[MISC_OVERFLOW] = (long long)carry > p.capacity;
-        if (p.host_R) {
-            *(volatile unsigned int*)p.host_R = carry;
-            __threadfence_system();
-        }
+        if (p.host_R) *(volatile unsigned int*)p.host_R = carry;
     }
+}
+
+// Same scan on one 8-CTA thread-block cluster (tiles <= 8 * 1024): every CTA sums the K copies of
+// its contiguous slice of tiles (one tile per thread), scans the slice, publishes the slice total
+// in its shared memory, and after one cluster barrier reads the totals of the lower-ranked CTAs
+// through distributed shared memory.  Replaces ~12 us of single-SM latency by ~5 us.
+constexpr int SCAN_CLUSTER = 8;
+template <int K>
+__global__ void __cluster_dims__(SCAN_CLUSTER, 1, 1) __launch_bounds__(1024)
+    tile_scan_cluster_kernel(const __grid_constant__ BinParams p) {
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t s_total;
+    cg::cluster_group cluster = cg::this_cluster();
+    const int crank = (int)cluster.block_rank();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int chunk = (p.tiles + SCAN_CLUSTER - 1) / SCAN_CLUSTER;  // <= 1024
+    const int t = crank * chunk + tid;
+    const bool valid = tid < chunk && t < p.tiles;
+    uint32_t c = 0, ck[K];
+#pragma unroll
+    for (int k = 0; k < K; k++) ck[k] = valid ? __ldcg(p.tile.count + (size_t)k * p.tiles + t) : 0u;
+#pragma unroll
+    for (int k = 0; k < K; k++) c += ck[k];
+    uint32_t v = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += u;
+    }
+    if (lane == 31) warp_sums[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t s = warp_sums[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, s, o);
+            if (lane >= o) s += u;
+        }
+        warp_sums[lane] = s;
+        if (lane == 31) s_total = s;
+    }
+    cluster.sync();  // also a CTA barrier: warp_sums / s_total of every CTA are visible
+    uint32_t base = 0, total = 0;
+#pragma unroll
+    for (int r = 0; r < SCAN_CLUSTER; r++) {
+        const uint32_t tr = *cluster.map_shared_rank(&s_total, r);
+        if (r < crank) base += tr;
+        total += tr;
+    }
+    const uint32_t excl = base + (warp ? warp_sums[warp - 1] : 0u) + v - c;
+    if (valid) {
+        p.tile.ranges[t] = make_uint2(excl, excl + c);
+        uint32_t run = excl;
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            p.tile.cursor[(size_t)k * p.tiles + t] = run;
+            run += ck[k];
+        }
+        if (c > (uint32_t)SMALL_MAX) p.tile.large_list[atomicAdd(p.tile.misc + MISC_N_LARGE, 1u)] = t;
+    }
+    if (crank == 0 && tid == 0) {
+        p.tile.misc[MISC_NUM_RENDERED] = total;
+        p.tile.misc[MISC_OVERFLOW] = (long long)total > p.capacity;
+        if (p.host_R) *(volatile unsigned int*)p.host_R = total;
+    }
+    cluster.sync();  // no CTA may exit while its shared memory can still be read remotely
 }
 
 // duplicateWithKeys (rasterizer_impl.cu:70-111), tile digit already consumed
@@ -318,6 +385,17 @@ __global__ void export_geometry_kernel(int P, GeomView g, const int* radii, floa
 }
 
 void launch_tile_scan(const BinParams& p, cudaStream_t s) {
+    if (p.tiles <= SCAN_CLUSTER * 1024) {
+        switch (p.copies) {
+            case 32: tile_scan_cluster_kernel<32><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
+            case 16: tile_scan_cluster_kernel<16><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
+            case 8: tile_scan_cluster_kernel<8><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
+            case 4: tile_scan_cluster_kernel<4><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
+            case 2: tile_scan_cluster_kernel<2><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
+            default: tile_scan_cluster_kernel<1><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
+        }
+        return;
+    }
     switch (p.copies) {
         case 32: tile_scan_kernel<32><<<1, 1024, 0, s>>>(p); break;
         case 16: tile_scan_kernel<16><<<1, 1024, 0, s>>>(p); break;
