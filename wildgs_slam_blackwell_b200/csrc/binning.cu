@@ -161,11 +161,19 @@ __global__ void __launch_bounds__(256) scatter_kernel(const __grid_constant__ Bi
     const bool wide = n > 32;
     uint32_t* __restrict__ cursor = p.tile.cursor + (size_t)(blockIdx.x % p.copies) * p.tiles;
     if (n && !wide) {
-        for (uint32_t y = y0; y < y1; y++)
-            for (uint32_t x = x0; x < x1; x++) {
-                const uint32_t slot = atomicAdd(cursor + y * p.gx + x, 1u);
-                if ((long long)slot < p.capacity) p.bucket[slot] = key;
+        // four cursor atomics in flight before their dependent stores (the kernel is bound by the
+        // round trip of the returning atomics, not by their number)
+        for (uint32_t i = 0; i < n; i += 4) {
+            uint32_t slot[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint32_t q = i + j;
+                if (q < n) slot[j] = atomicAdd(cursor + (y0 + q / w) * p.gx + x0 + q % w, 1u);
             }
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (i + j < n && (long long)slot[j] < p.capacity) p.bucket[slot[j]] = key;
+        }
     }
     unsigned m = __ballot_sync(0xffffffffu, wide);
     while (m) {
