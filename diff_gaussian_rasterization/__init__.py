@@ -12,6 +12,7 @@ from wildgs_slam_blackwell_b200.rasterizer import (  # noqa: F401
     _RasterizeGaussians,
     cpu_deep_copy_tuple,
     grad_sink,
+    tile_rows,
 )
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define WGS_ABI_VERSION 6
+#define WGS_ABI_VERSION 7
 
 /* status codes (negative = error) */
 #define WGS_OK 0
@@ -87,6 +87,13 @@ typedef struct WgsForwardArgs {
   void* binning;
   void* image;
   int64_t capacity;   /* instance capacity the binning workspace was sized for */
+  /* Tile-row strip [tile_row_begin, tile_row_end) to render (rows of 16 pixels; both 0 = whole image).
+   * New capability for sub-frame sharding of a keyframe window across GPUs (no reference
+   * counterpart): only the strip's tiles are binned and composited, only the strip's pixels of the
+   * outputs are written, radii keep their whole-image meaning, n_touched counts the strip's pixels.
+   * Images, n_touched and (in the backward) all gradients of the strips of a partition of the image sum
+   * to the whole-image results. */
+  int32_t tile_row_begin, tile_row_end;
 } WgsForwardArgs;
 
 /* Arguments of the backward pass.  Replaces RasterizeGaussiansBackwardCUDA
@@ -131,6 +138,7 @@ typedef struct WgsBackwardArgs {
   const void* image;
   void* grad;           /* accumulators; must be zero before the FIRST backward that uses it (kernels re-zero it) */
   int64_t capacity;
+  int32_t tile_row_begin, tile_row_end; /* must equal the matching forward's */
 } WgsBackwardArgs;
 
 /* library / device */

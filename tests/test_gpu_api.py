@@ -283,3 +283,40 @@ def test_more_than_8192_tiles_uses_single_block_scan():
     np.testing.assert_array_equal(ours["st_ranges"].view(np.uint32), o["st_ranges"])
     np.testing.assert_array_equal(ours["st_point_list"].view(np.uint32), o["st_point_list"])
     np.testing.assert_array_equal(ours["radii"], o["radii"])
+
+
+def test_tile_row_strips_sum_to_the_whole_image():
+    """rasterizer.tile_rows: strips of a partition of the image reproduce the whole-image forward bitwise
+    inside their rows, and their n_touched / gradients (incl. pose) sum to the whole-image results."""
+    g, cams, cots = scenes.make_scene(6000, 200, 150, 1, seed=61)     # 13 x 10 tiles, ragged edges
+    cam, cot = cams[0], cots[0]
+    full = util.run_ours(g, cam, cot, export=False)
+    s = util.settings_from_cam(cam, 1)
+    dc, dd = util.to_dev(cot[0]), util.to_dev(cot[1])
+    acc = None
+    for r0, r1 in ((0, 3), (3, 4), (4, 10)):
+        leaf = lambda a: util.to_dev(a).requires_grad_(True)
+        m3, op, sh, sc, ro = leaf(g["means3D"]), leaf(g["opacities"]), leaf(g["sh"]), leaf(g["scales"]), leaf(g["rotations"])
+        m2 = torch.zeros(6000, 3, device=DEV, requires_grad=True)
+        th, rh = torch.zeros(3, device=DEV, requires_grad=True), torch.zeros(3, device=DEV, requires_grad=True)
+        with rasterizer.tile_rows(r0, r1):
+            color, radii, depth, opacity, n_touched = rasterizer.GaussianRasterizer(s)(
+                m3, m2, op, shs=sh, scales=sc, rotations=ro, theta=th, rho=rh)
+        ((color * dc).sum() + (depth * dd).sum()).backward()          # backward outside the context: strip is remembered
+        y0, y1 = r0 * 16, min(r1 * 16, 150)
+        c = color.detach().cpu().numpy()
+        np.testing.assert_array_equal(c[:, y0:y1], full["color"][:, y0:y1])
+        assert not c[:, :y0].any() and not c[:, y1:].any()
+        np.testing.assert_array_equal(depth.detach().cpu().numpy()[:, y0:y1], full["depth"][:, y0:y1])
+        np.testing.assert_array_equal(radii.cpu().numpy(), full["radii"])
+        part = dict(n_touched=n_touched.cpu().numpy().astype(np.int64), m3=m3.grad.cpu().numpy(), op=op.grad.cpu().numpy(),
+                    sh=sh.grad.cpu().numpy(), sc=sc.grad.cpu().numpy(), ro=ro.grad.cpu().numpy(), m2=m2.grad.cpu().numpy(),
+                    tau=np.concatenate([rh.grad.cpu().numpy().reshape(-1), th.grad.cpu().numpy().reshape(-1)]))
+        acc = part if acc is None else {k: acc[k] + part[k] for k in acc}
+    np.testing.assert_array_equal(acc["n_touched"], full["n_touched"])
+    for k, ref in (("m3", "g_dL_dmeans3D"), ("op", "g_dL_dopacity"), ("sh", "g_dL_dsh"), ("sc", "g_dL_dscales"),
+                   ("ro", "g_dL_drotations"), ("m2", "g_dL_dmeans2D"), ("tau", "g_dL_dtau_sum")):
+        util.assert_grad_close(k, acc[k], full[ref])
+    with pytest.raises(RuntimeError, match="tile_rows"):
+        with rasterizer.tile_rows(4, 11):
+            rasterizer.GaussianRasterizer(s)(m3, m2, op, shs=sh, scales=sc, rotations=ro, theta=th, rho=rh)

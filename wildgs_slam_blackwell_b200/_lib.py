@@ -5,7 +5,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libwgs_rasterizer.so")
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 WGS_OK = 0
 WGS_ERR_INVALID_ARGUMENT = -1
@@ -31,7 +31,7 @@ class ForwardArgs(C.Structure):
         ("campos", _fp),
         ("out_color", _fp), ("out_depth", _fp), ("out_opacity", _fp), ("radii", _fp), ("n_touched", _fp),
         ("geom", _fp), ("tile", _fp), ("binning", _fp), ("image", _fp),
-        ("capacity", C.c_int64),
+        ("capacity", C.c_int64), ("tile_row_begin", C.c_int32), ("tile_row_end", C.c_int32),
     ]
 
 
@@ -47,7 +47,7 @@ class BackwardArgs(C.Structure):
         ("dL_dmeans3D", _fp), ("dL_dmeans2D", _fp), ("dL_dsh", _fp), ("dL_dcolors", _fp), ("dL_dopacity", _fp),
         ("dL_dscales", _fp), ("dL_drotations", _fp), ("dL_dcov3D", _fp), ("dL_dtau", _fp),
         ("geom", _fp), ("tile", _fp), ("binning", _fp), ("image", _fp), ("grad", _fp),
-        ("capacity", C.c_int64),
+        ("capacity", C.c_int64), ("tile_row_begin", C.c_int32), ("tile_row_end", C.c_int32),
     ]
 
 

@@ -53,6 +53,13 @@ void set_err(const char* what, cudaError_t e) {
     } while (0)
 
 bool aligned256(const void* p) { return ((uintptr_t)p & 255u) == 0; }
+// tile-row strip of a call: (0,0) means the whole image; returns false if out of range
+bool strip_rows(int begin, int end, int gy, int* r0, int* r1) {
+    if (begin == 0 && end == 0) { *r0 = 0; *r1 = gy; return true; }
+    if (begin < 0 || end <= begin || end > gy) return false;
+    *r0 = begin; *r1 = end;
+    return true;
+}
 }  // namespace
 
 extern "C" {
@@ -143,6 +150,11 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
         }
     }
     const int gx = (a->width + 15) / 16, gy = (a->height + 15) / 16, tiles = gx * gy;
+    int row0, row1;
+    if (!strip_rows(a->tile_row_begin, a->tile_row_end, gy, &row0, &row1)) {
+        set_err("wgs_forward: tile_row_begin/end out of range", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
     const size_t Pn = (size_t)(a->P > 0 ? a->P : 1);
     GeomView geom = geom_view(a->geom, Pn);
     TileView tile = tile_view(a->tile, (size_t)tiles);
@@ -152,7 +164,7 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
 
     PreFwdParams pp;
     pp.P = a->P; pp.D = a->sh_degree; pp.M = a->M; pp.W = a->width; pp.H = a->height; pp.gx = gx; pp.gy = gy;
-    pp.prefiltered = a->prefiltered; pp.copies = hist_copies((size_t)tiles);
+    pp.prefiltered = a->prefiltered; pp.copies = hist_copies((size_t)tiles); pp.row0 = row0; pp.row1 = row1;
     pp.tanfovx = a->tanfovx; pp.tanfovy = a->tanfovy;
     pp.focal_y = a->height / (2.0f * a->tanfovy);  // rasterizer_impl.cu:225-226
     pp.focal_x = a->width / (2.0f * a->tanfovx);
@@ -181,6 +193,7 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
 
     RenderFwdParams rp;
     rp.W = a->width; rp.H = a->height; rp.gx = gx; rp.gy = gy; rp.bg = a->background;
+    rp.tile0 = row0 * gx; rp.ntiles = (row1 - row0) * gx;
     rp.geom = geom; rp.tile = tile; rp.image = image; rp.bucket = bp.bucket;
     rp.out_color = a->out_color; rp.out_depth = a->out_depth; rp.out_opacity = a->out_opacity;
     rp.n_touched = a->n_touched;
@@ -222,6 +235,11 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
         set_err("wgs_backward: provide scales+rotations or cov3D_precomp", cudaSuccess);
         return WGS_ERR_INVALID_ARGUMENT;
     }
+    int row0, row1;
+    if (!strip_rows(a->tile_row_begin, a->tile_row_end, (a->height + 15) / 16, &row0, &row1)) {
+        set_err("wgs_backward: tile_row_begin/end out of range", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
     const bool use_sh = a->sh && !a->colors_precomp;
     if (use_sh && !a->dL_dsh) { set_err("wgs_backward: dL_dsh is required on the SH path", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
     const int gx = (a->width + 15) / 16, gy = (a->height + 15) / 16, tiles = gx * gy;
@@ -232,6 +250,7 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
 
     RenderBwdParams rb;
     rb.W = a->width; rb.H = a->height; rb.gx = gx; rb.gy = gy; rb.bg = a->background;
+    rb.tile0 = row0 * gx; rb.ntiles = (row1 - row0) * gx;
     rb.geom = geom; rb.tile = tile; rb.image = image; rb.bucket = (const unsigned long long*)a->binning;
     rb.dL_dcolor = a->dL_dout_color; rb.dL_ddepth = a->dL_dout_depth; rb.grad = grad;
     MARK(ctx, 6, s);

@@ -7,6 +7,7 @@ namespace wgs {
 
 struct PreFwdParams {
     int P, D, M, W, H, gx, gy, prefiltered, copies;
+    int row0, row1;  // tile-row strip to bin (whole image: 0, gy)
     float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
     const float *means3D, *sh, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
     const float *viewmatrix, *projmatrix, *campos;
@@ -27,6 +28,7 @@ struct BinParams {
 
 struct RenderFwdParams {
     int W, H, gx, gy;
+    int tile0, ntiles;  // first tile and number of tiles of the strip (whole image: 0, gx*gy)
     const float* bg;
     GeomView geom;
     TileView tile;
@@ -38,6 +40,7 @@ struct RenderFwdParams {
 
 struct RenderBwdParams {
     int W, H, gx, gy;
+    int tile0, ntiles;
     const float* bg;
     GeomView geom;
     TileView tile;

@@ -69,7 +69,8 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
 #pragma unroll
             for (int k = 0; k < 4; k++) q4[k] = __ldg(p.rotations + 4 * idx + k);
         }
-        const bool vis = rad > 0;
+        const uint2 rect = __ldg(p.geom.rect + idx);
+        const bool vis = rad > 0 && rect.x != rect.y;  // rect is empty outside the rendered strip
         if (vis) {
             const float4 z4 = make_float4(0, 0, 0, 0);
             p.grad.acc[3 * idx] = z4; p.grad.acc[3 * idx + 1] = z4; p.grad.acc[3 * idx + 2] = z4;

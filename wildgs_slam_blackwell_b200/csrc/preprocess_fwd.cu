@@ -160,7 +160,12 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
                 mx = ndc2pix(projx, p.W); my = ndc2pix(projy, p.H);
                 const int r = (int)rad_f;
                 get_rect(mx, my, r, p.gx, p.gy, x0, y0, x1, y1);
-                if ((x1 - x0) * (y1 - y0) != 0) { visible = true; radius = r; }
+                if ((x1 - x0) * (y1 - y0) != 0) {
+                    radius = r;  // whole-image meaning (forward.cu:238-239), also in strip mode
+                    y0 = max(y0, (uint32_t)p.row0);
+                    y1 = min(y1, (uint32_t)p.row1);
+                    visible = y1 > y0;  // touches the strip being rendered
+                }
             }
         }
         p.radii[idx] = radius;

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
     __shared__ uint32_t s_hi;
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
+    const int tile = p.tile0 + blockIdx.x;
     const int tx = tile % p.gx, ty = tile / p.gx;
     const int wx0 = tx * WGS_TILE + (warp & 1) * 8, wy0 = ty * WGS_TILE + (warp >> 1) * 4;
     const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
 }
 
 void launch_render_bwd(const RenderBwdParams& p, cudaStream_t s) {
-    render_bwd_kernel<<<p.gx * p.gy, 256, 0, s>>>(p);
+    render_bwd_kernel<<<p.ntiles, 256, 0, s>>>(p);
 }
 
 }  // namespace wgs

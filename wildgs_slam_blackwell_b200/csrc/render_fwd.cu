@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
     __shared__ FwdStage st[2];
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
+    const int tile = p.tile0 + blockIdx.x;
     const int tx = tile % p.gx, ty = tile / p.gx;
     const int wx0 = tx * WGS_TILE + (warp & 1) * 8, wy0 = ty * WGS_TILE + (warp >> 1) * 4;
     const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
 }
 
 void launch_render_fwd(const RenderFwdParams& p, cudaStream_t s) {
-    render_fwd_kernel<<<p.gx * p.gy, 256, 0, s>>>(p);
+    render_fwd_kernel<<<p.ntiles, 256, 0, s>>>(p);
 }
 
 }  // namespace wgs

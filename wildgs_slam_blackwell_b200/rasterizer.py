@@ -104,9 +104,11 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
         campos = _f32c(s.campos, device)
         M = int(sh.shape[1]) if (sh is not None and sh.numel() != 0) else 0
 
-        color = torch.empty((3, H, W), dtype=torch.float32, device=device)
-        depth = torch.empty((1, H, W), dtype=torch.float32, device=device)
-        opacity = torch.empty((1, H, W), dtype=torch.float32, device=device)
+        strip = tile_rows._active
+        new_img = torch.zeros if strip is not None else torch.empty   # outside a strip nothing is written
+        color = new_img((3, H, W), dtype=torch.float32, device=device)
+        depth = new_img((1, H, W), dtype=torch.float32, device=device)
+        opacity = new_img((1, H, W), dtype=torch.float32, device=device)
         radii = torch.empty((P,), dtype=torch.int32, device=device)
         n_touched = torch.empty((P,), dtype=torch.int32, device=device)
 
@@ -122,6 +124,10 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
         a.viewmatrix, a.projmatrix, a.campos = _ptr(view), _ptr(proj), _ptr(campos)
         a.out_color, a.out_depth, a.out_opacity = color.data_ptr(), depth.data_ptr(), opacity.data_ptr()
         a.radii, a.n_touched = _ptr(radii), _ptr(n_touched)
+        if strip is not None:
+            if not (0 <= strip.begin < strip.end <= (H + 15) // 16):
+                raise RuntimeError(f"tile_rows({strip.begin}, {strip.end}) outside the {(H + 15) // 16} tile rows")
+            a.tile_row_begin, a.tile_row_end = strip.begin, strip.end
         R = C.c_int64(0)
         stream = _stream_ptr(device)
         while True:
@@ -160,6 +166,30 @@ def _grad_workspace(device, P):
         ent = (P, torch.zeros(int(nbytes), dtype=torch.uint8, device=device))  # zero once; kernels re-zero
         _grad_ws[key] = ent
     return ent[1]
+
+
+class tile_rows:
+    """Context manager (new capability: sub-frame sharding of a keyframe window): forwards issued
+    while active render only tile rows [begin, end) (rows of 16 pixels).  Output images have the full
+    (H, W) shape and are ZERO outside the strip, so images, n_touched and -- after backward --
+    every gradient of the strips of a partition sum to the whole-image results; radii keep their
+    whole-image meaning.  The matching backward uses the same strip automatically.
+
+        with tile_rows(0, 15):  color_top, *_ = rasterizer(...)
+    """
+    _active = None
+
+    def __init__(self, begin, end):
+        self.begin, self.end = int(begin), int(end)
+
+    def __enter__(self):
+        self._prev = tile_rows._active
+        tile_rows._active = self
+        return self
+
+    def __exit__(self, *exc):
+        tile_rows._active = self._prev
+        return False
 
 
 class grad_sink:
@@ -237,6 +267,7 @@ def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_p
         b.dL_dtau = _ptr(g["tau"])
         b.geom, b.tile, b.binning, b.image = fa.geom, fa.tile, fa.binning, fa.image
         b.capacity = fa.capacity
+        b.tile_row_begin, b.tile_row_end = fa.tile_row_begin, fa.tile_row_end
         if P > 0:
             b.grad = _grad_workspace(device, P).data_ptr()
         rc = lib.wgs_backward(ctx, C.byref(b), _stream_ptr(device))
