@@ -85,6 +85,7 @@ WgsContext* wgs_context_create(int device) {
     if (e == cudaSuccess) e = cudaHostGetDevicePointer((void**)&c->dev_R, c->host_R, 0);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_R, cudaEventDisableTiming);
     if (e == cudaSuccess) e = (cudaError_t)configure_binning();
+    if (e == cudaSuccess) e = (cudaError_t)configure_render_bwd();
     if (e != cudaSuccess) {
         set_err("wgs_context_create", e);
         delete c;

@@ -59,6 +59,7 @@ struct TileView {
     uint2* ranges;
     uint32_t* misc;
     uint32_t* large_list;  // tile ids whose segment is too long for the small sort kernel
+    uint32_t* order;       // tile ids, longest segment first (block -> tile map of the compositing kernels)
 };
 
 struct ImageView {
@@ -96,7 +97,7 @@ __host__ __device__ inline size_t tile_clear_bytes(size_t tiles) {
     return align_up(WGS_HIST_COPIES * tiles * 4) + align_up(MISC_WORDS * 4);
 }
 __host__ __device__ inline size_t tile_bytes(size_t tiles) {
-    return tile_clear_bytes(tiles) + align_up(WGS_HIST_COPIES * tiles * 4) + align_up(tiles * 4) + align_up(tiles * 8);
+    return tile_clear_bytes(tiles) + align_up(WGS_HIST_COPIES * tiles * 4) + 2 * align_up(tiles * 4) + align_up(tiles * 8);
 }
 __host__ __device__ inline TileView tile_view(void* base, size_t tiles) {
     char* p = (char*)base;
@@ -105,6 +106,7 @@ __host__ __device__ inline TileView tile_view(void* base, size_t tiles) {
     t.misc = (uint32_t*)p; p += align_up(MISC_WORDS * 4);
     t.cursor = (uint32_t*)p; p += align_up(WGS_HIST_COPIES * tiles * 4);
     t.large_list = (uint32_t*)p; p += align_up(tiles * 4);
+    t.order = (uint32_t*)p; p += align_up(tiles * 4);
     t.ranges = (uint2*)p;
     return t;
 }

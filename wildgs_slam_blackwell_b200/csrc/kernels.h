@@ -76,5 +76,6 @@ void launch_export_binning(const BinParams& p, const ImageView& image, int W, in
 void launch_export_geometry(int P, const GeomView& g, const int* radii, float* depths, float* means2D,
                             float* conic_opacity, float* rgb, uint8_t* clamped, cudaStream_t s);
 int configure_binning();  // one-time cudaFuncSetAttribute calls; returns cudaError_t
+int configure_render_bwd();
 
 }  // namespace wgs

@@ -3,7 +3,8 @@
 // (:21-145), the cov3D backward (:350-413) and the torch.sum over the (P,6) dL_dtau buffer in
 // diff_gaussian_rasterization/__init__.py:152-154.
 //
-// Each thread consumes (and re-zeroes) the 48-byte accumulator record render_bwd filled,
+// Each thread consumes (and re-zeroes) the 48-byte accumulator record render_bwd filled
+// (pixel moments of G*dL/dalpha, colour and depth sums),
 // recomputes the forward intermediates it needs (cov3D, T = W*J) instead of reading a stored
 // copy, writes every per-Gaussian output exactly once (so outputs need no pre-zeroing), and
 // the six pose-gradient terms are reduced warp -> block -> grid (per-block partials, last
@@ -70,16 +71,23 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
             for (int k = 0; k < 4; k++) q4[k] = __ldg(p.rotations + 4 * idx + k);
         }
         const uint2 rect = __ldg(p.geom.rect + idx);
+        const float4 ra = __ldcg(p.geom.rec + 2 * idx), rb = __ldcg(p.geom.rec + 2 * idx + 1);
         const bool vis = rad > 0 && rect.x != rect.y;  // rect is empty outside the rendered strip
         if (vis) {
             const float4 z4 = make_float4(0, 0, 0, 0);
             p.grad.acc[3 * idx] = z4; p.grad.acc[3 * idx + 1] = z4; p.grad.acc[3 * idx + 2] = z4;
         }
-        // render_bwd accumulates without the per-pixel constants (backward.cu:643-644,752-756);
-        // apply them once here: ddelx_dx = W/2, ddely_dy = H/2, and the -1/2 of the conic terms
-        const float dm2x = -0.5f * p.W * g0.x, dm2y = -0.5f * p.H * g0.y;   // dL/dmean2D (NDC-scaled)
-        const float dcx = -0.5f * g0.z, dcy = -0.5f * g0.w, dcz = -0.5f * g1.x;  // dL/dconic (x, y, w)
-        const float dop = g1.y;
+        // render_bwd accumulates the moments of w = G*dL/dalpha over the pixels, d = mean2D - pixel:
+        //   g0 = (S w, S w dx, S w dy, S w dx^2), g1.xy = (S w dx dy, S w dy^2).
+        // With dL/dG = opacity * dL/dalpha (backward.cu:741-742) the reference's per-pixel terms
+        // (backward.cu:744-757) sum to: dL/dmean2D = -(W/2, H/2) * o * (conic.x Sx + conic.y Sy,
+        // conic.y Sx + conic.z Sy), dL/dconic = -1/2 * o * (Sxx, Sxy, Syy), dL/dopacity = S w.
+        // Records of culled Gaussians are zero, but their geom record is stale: gate on vis.
+        const float o = vis ? rb.y : 0.f, kx = vis ? ra.z : 0.f, ky = vis ? ra.w : 0.f, kz = vis ? rb.x : 0.f;
+        const float dm2x = -0.5f * p.W * o * (kx * g0.y + ky * g0.z);   // dL/dmean2D (NDC-scaled)
+        const float dm2y = -0.5f * p.H * o * (ky * g0.y + kz * g0.z);
+        const float dcx = -0.5f * o * g0.w, dcy = -0.5f * o * g1.x, dcz = -0.5f * o * g1.y;  // dL/dconic (x, y, w)
+        const float dop = g0.x;
         const float dcol[3] = {g1.z, g1.w, g2.x};
         const float ddepth = g2.y;
         V3 dmean = {0.f, 0.f, 0.f};

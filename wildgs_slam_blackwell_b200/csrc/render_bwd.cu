@@ -3,17 +3,27 @@
 //
 // Same decomposition as the forward (CTA = 16x16 tile, warp = 8x4 pixels, cp.async-staged
 // batches, per-warp ellipse/rectangle culling), traversed back to front starting at the
-// tile's last contributor.  The kernel is FP32-issue bound (ncu: 77 % issue utilisation), so
-// the design minimises instructions per (warp, Gaussian) pair:
+// tile's last contributor.  The kernel is FP32-issue bound, so the design minimises
+// instructions per (warp, Gaussian) pair:
 //  * the four per-channel "accum_rec" recurrences of the reference (backward.cu:709-722)
 //    collapse into ONE scalar recurrence on x = c.dL_dpixel + depth*dL_ddepth (they are linear);
-//  * constant factors (0.5*W, 0.5*H, -0.5) are applied once per Gaussian in preprocess_bwd,
-//    not once per pixel here;
-//  * the reference's 256-wide shared-memory tree + 9 block barriers per list entry becomes a
-//    warp-private shared-memory transpose: every lane stores its 10 terms, and once GROUP
-//    Gaussians are pending, 10*GROUP lanes each sum one 32-float row (8 LDS.128, conflict-free
-//    at a 36-float row pitch) and issue one RED.ADD.F32 into the 48-byte accumulator record.
-//    No block barrier per pair at all.
+//  * every per-Gaussian gradient of the reference (backward.cu:724-757) is a sum over pixels of
+//    one of TWO per-pixel scalars times a factor that does not depend on the Gaussian:
+//        w = G * dL/dalpha      -> dL/dopacity = S[w],   and with d = mean2D - pixel
+//                                  dL/dmean2D, dL/dconic  from the moments S[w d_x], S[w d_y],
+//                                  S[w d_x^2], S[w d_x d_y], S[w d_y^2]   (conic, opacity and the
+//                                  constants 0.5*W, 0.5*H, -0.5 are applied once per Gaussian in
+//                                  preprocess_bwd)
+//        c = alpha * T          -> dL/dcolor = S[c dL_dpixel.rgb], dL/ddepth = S[c dL_ddepth]
+//    and d = (mean2D - warp origin) - (lane_x, lane_y), so inside a warp the ten sums are the
+//    product  [16 pending Gaussians x 32 lanes] * [32 lanes x 10]  with a matrix that is CONSTANT
+//    for the warp (1, u, v, u^2, uv, v^2 of the lane coordinates; the lane's pixel cotangents).
+//    The reference's 256-wide shared-memory tree + 9 block barriers per list entry therefore
+//    becomes: 2 STS per (lane, Gaussian), and per 16 Gaussians 8 ldmatrix + 16 mma.sync
+//    (m16n8k8 TF32, operands split hi/lo so the products carry ~21 mantissa bits, fp32
+//    accumulate), a 6-shuffle conversion from lane moments to d-moments and 4 vector REDs.
+//    This is the one place of the path where a dense contraction exists; it is tiny (1 mma per
+//    pair), the point is to take ~40 instructions per pair off the FP32/LSU issue slots.
 // ex2.approx / rcp.approx are used (tolerance on gradients is rtol 1e-3; the forward, which is
 // bit-exact, is untouched).
 #include "common.cuh"
@@ -22,15 +32,28 @@
 
 namespace wgs {
 
-constexpr int BB = 128;    // list entries staged per batch
-constexpr int GROUP = 3;   // Gaussians per shared-memory reduction
-constexpr int ROW = 36;    // floats per reduction row (32 + pad: 144 B pitch, 16-B aligned, conflict-free)
+constexpr int BB = 128;  // list entries staged per batch
+constexpr int MG = 16;   // pending Gaussians per tensor-core reduction (the M of m16n8k8)
+constexpr int VP = 36;   // floats per pending row (32 lanes + pad: 144-B pitch keeps ldmatrix conflict-free)
 
 struct __align__(16) BwdStage {
     float4 rec0[BB];  // x, y, conic.x, conic.y
     float4 rec1[BB];  // conic.z, opacity, depth, ln(255*opacity)
     float4 col[BB];   // r, g, b, -
     uint32_t id[BB];
+};
+
+// per-warp staging of the pending (Gaussian, lane) scalars
+struct __align__(16) WarpRed {
+    float w[MG][VP];   // G * dL/dalpha
+    float c[MG][VP];   // alpha * T
+    float4 cst[MG];    // {gaussian id (bits), mean2D.x - warp x0, mean2D.y - warp y0, -}
+};
+
+struct __align__(16) BwdSmem {
+    BwdStage st[2];
+    WarpRed red[8];
+    uint32_t hi;
 };
 
 __device__ __forceinline__ float rcp_approx(float x) {
@@ -42,6 +65,26 @@ __device__ __forceinline__ float ex2_approx(float x) {
     float r;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
+}
+__device__ __forceinline__ void ldsm4(unsigned addr, unsigned (&r)[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const unsigned (&a)[4], unsigned b0, unsigned b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void red_add_v2(float* addr, float x, float y) {
+    asm volatile("red.relaxed.gpu.global.add.v2.f32 [%0], {%1, %2};\n" ::"l"(addr), "f"(x), "f"(y) : "memory");
+}
+// tf32 keeps the upper 19 bits; hi + lo reproduces v to ~21 mantissa bits
+__device__ __forceinline__ void split_tf32(const unsigned (&v)[4], unsigned (&h)[4], unsigned (&l)[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        h[i] = v[i] & 0xffffe000u;
+        l[i] = __float_as_uint(__uint_as_float(v[i]) - __uint_as_float(h[i]));
+    }
 }
 
 // threads 0..127 copy rec0/rec1 of slot tid, threads 128..255 copy col + id of slot tid-128
@@ -56,34 +99,66 @@ __device__ __forceinline__ void bwd_gather(BwdStage& st, int tid, uint32_t id, c
     }
 }
 
-// Sum the pending rows of this warp and add them to the per-Gaussian accumulators.
-__device__ __forceinline__ void flush_group(const float* my_row, uint32_t rid, int n, int lane, int sub,
-                                            float* __restrict__ acc) {
+// Reduce the n (<= MG) pending Gaussians of this warp over its 32 lanes on the tensor pipe and add
+// the ten sums of each to its accumulator record:
+//   [S w, S w dx, S w dy, S w dx^2 | S w dx dy, S w dy^2, dcolor.r, dcolor.g | dcolor.b, ddepth, -, -]
+// bw: B fragments of the lane-moment matrix (columns 1,u,v,u^2,uv,v^2,0,0); bc: B fragments of the
+// cotangent matrix (columns dp.r,dp.g,dp.b,dp.depth hi parts, then their four lo parts).
+__device__ __forceinline__ void flush_pending(const WarpRed& wr, unsigned lm_addr, int n, int lane,
+                                              const unsigned (&bw)[4][2], const unsigned (&bc)[4][2],
+                                              float* __restrict__ acc) {
     __syncwarp();
-    if (lane < 10 * n) {
-        const float4* r4 = reinterpret_cast<const float4*>(my_row);
-        float4 s0 = r4[0], s1 = r4[1], s2 = r4[2], s3 = r4[3];
-        const float4 t0 = r4[4], t1 = r4[5], t2 = r4[6], t3 = r4[7];
-        s0.x += t0.x; s0.y += t0.y; s0.z += t0.z; s0.w += t0.w;
-        s1.x += t1.x; s1.y += t1.y; s1.z += t1.z; s1.w += t1.w;
-        s2.x += t2.x; s2.y += t2.y; s2.z += t2.z; s2.w += t2.w;
-        s3.x += t3.x; s3.y += t3.y; s3.z += t3.z; s3.w += t3.w;
-        s0.x += s1.x; s0.y += s1.y; s0.z += s1.z; s0.w += s1.w;
-        s2.x += s3.x; s2.y += s3.y; s2.z += s3.z; s2.w += s3.w;
-        s0.x += s2.x; s0.y += s2.y; s0.z += s2.z; s0.w += s2.w;
-        const float sum = (s0.x + s0.y) + (s0.z + s0.w);
-        atomicAdd(acc + 12 * (size_t)rid + sub, sum);
+    float mw[4] = {0.f, 0.f, 0.f, 0.f}, mc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int s = 0; s < 4; s++) {  // k-step s = pixel row s of the warp's 8x4 rectangle
+        unsigned a[4], h[4], l[4];
+        ldsm4(lm_addr + 32 * s, a);
+        split_tf32(a, h, l);
+        mma_tf32(mw, h, bw[s][0], bw[s][1]);
+        mma_tf32(mw, l, bw[s][0], bw[s][1]);
+        ldsm4(lm_addr + MG * VP * 4 + 32 * s, a);
+        split_tf32(a, h, l);
+        mma_tf32(mc, h, bc[s][0], bc[s][1]);
+        mma_tf32(mc, l, bc[s][0], bc[s][1]);
+    }
+    // D fragment: lane (q = lane/4, t = lane%4) holds columns 2t, 2t+1 of rows q (regs 0,1) and q+8 (regs 2,3)
+    const int q = lane >> 2, t = lane & 3, qb = lane & ~3;
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const int row = q + 8 * half;
+        const float c0 = mw[2 * half], c1 = mw[2 * half + 1];
+        const float S0 = __shfl_sync(0xffffffffu, c0, qb), Su = __shfl_sync(0xffffffffu, c1, qb);
+        const float Sv = __shfl_sync(0xffffffffu, c0, qb + 1), Suu = __shfl_sync(0xffffffffu, c1, qb + 1);
+        const float Suv = __shfl_sync(0xffffffffu, c0, qb + 2), Svv = __shfl_sync(0xffffffffu, c1, qb + 2);
+        // cotangent sums: hi columns (t = 0,1) + lo columns (t = 2,3)
+        const float d0 = mc[2 * half] + __shfl_down_sync(0xffffffffu, mc[2 * half], 2);
+        const float d1 = mc[2 * half + 1] + __shfl_down_sync(0xffffffffu, mc[2 * half + 1], 2);
+        const float4 k = wr.cst[row];
+        // d = (e, f) - (u, v): lane moments -> moments of d
+        const float e = k.y, f = k.z;
+        const float Sx = fmaf(e, S0, -Su), Sy = fmaf(f, S0, -Sv);
+        const float Sxx = fmaf(e, Sx - Su, Suu);
+        const float Sxy = fmaf(f, Sx, fmaf(-e, Sv, Suv));
+        const float Syy = fmaf(f, Sy - Sv, Svv);
+        const float o0 = t == 0 ? S0 : (t == 1 ? Sy : Sxy);
+        const float o1 = t == 0 ? Sx : (t == 1 ? Sxx : Syy);
+        float* rec = acc + 12 * (size_t)__float_as_uint(k.x);
+        if (row < n) {
+            if (t < 3) red_add_v2(rec + 2 * t, o0, o1);
+            if (t < 2) red_add_v2(rec + 6 + 2 * t, d0, d1);
+        }
     }
     __syncwarp();
 }
 
 __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constant__ RenderBwdParams p) {
-    __shared__ BwdStage st[2];
-    __shared__ __align__(16) float red[8][10 * GROUP][ROW];
-    __shared__ uint32_t s_hi;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = p.tile0 + blockIdx.x;
+    // longest tiles first (tile_scan's order); a tile-row strip skips the tiles outside it
+    const int tile = (int)p.tile.order[blockIdx.x];
+    if (tile < p.tile0 || tile >= p.tile0 + p.ntiles) return;
     const int tx = tile % p.gx, ty = tile / p.gx;
     const int wx0 = tx * WGS_TILE + (warp & 1) * 8, wy0 = ty * WGS_TILE + (warp >> 1) * 4;
     const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
@@ -99,11 +174,11 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
 
     const int last_contributor = inside ? (int)p.image.n_contrib[pix] : 0;
     const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
-    if (tid == 0) s_hi = 0;
+    if (tid == 0) sm.hi = 0;
     __syncthreads();
-    if (lane == 0 && warp_last) atomicMax(&s_hi, (uint32_t)warp_last);
+    if (lane == 0 && warp_last) atomicMax(&sm.hi, (uint32_t)warp_last);
     __syncthreads();
-    const int hi = (int)s_hi;  // entries [hi, total) contributed to no pixel of this tile
+    const int hi = (int)sm.hi;  // entries [hi, total) contributed to no pixel of this tile
     if (hi == 0) return;
     const int rounds = (hi + BB - 1) / BB;
 
@@ -118,12 +193,41 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
     const float tfbg = T_final * (__ldg(p.bg) * dpx + __ldg(p.bg + 1) * dpy + __ldg(p.bg + 2) * dpz);
     float last_alpha = 0.f, last_x = 0.f, A = 0.f;
     float* __restrict__ acc = (float*)p.grad.acc;
-    // shared-window address of this lane's column (written per Gaussian); kept as a 32-bit register
-    unsigned wcol;
-    asm volatile("mov.u32 %0, %1;" : "=r"(wcol) : "r"((unsigned)__cvta_generic_to_shared(&red[warp][0][lane])));
-    const float* const wrow = &red[warp][lane < 10 * GROUP ? lane : 0][0];  // this lane's row (summed at flush)
-    const int my_g = lane / 10, my_sub = lane - 10 * my_g;  // which pending Gaussian / term this lane flushes
-    uint32_t my_id = 0;                              // id of pending Gaussian my_g
+
+    WarpRed& wr = sm.red[warp];
+    // ---- constant B fragments of this warp (b0: k = t, b1: k = t + 4 of k-step s; column n = q) ----
+    unsigned bw[4][2], bc[4][2];
+    {
+        const int q = lane >> 2, t = lane & 3;
+        // cotangents of all 32 lanes, hi/lo split, as an 8 x 32 table in the (still unused) w rows
+        {
+            const float v4[4] = {dpx, dpy, dpz, dpd};
+#pragma unroll
+            for (int n = 0; n < 4; n++) {
+                const float h = __uint_as_float(__float_as_uint(v4[n]) & 0xffffe000u);
+                wr.w[n][lane] = h;
+                wr.w[n + 4][lane] = v4[n] - h;
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int s = 0; s < 4; s++) {
+#pragma unroll
+            for (int b = 0; b < 2; b++) {
+                const int u = t + 4 * b, v = s;  // lane coordinates of pixel lane j = 8 s + u
+                const float m = q == 0 ? 1.f : q == 1 ? (float)u : q == 2 ? (float)v : q == 3 ? (float)(u * u)
+                              : q == 4 ? (float)(u * v) : q == 5 ? (float)(v * v) : 0.f;
+                bw[s][b] = __float_as_uint(m);
+                bc[s][b] = __float_as_uint(wr.w[q][8 * s + u]);
+            }
+        }
+        __syncwarp();
+    }
+    // ldmatrix row address of this lane: matrix i = lane/8 -> rows (i&1)*8 + lane%8, columns 4*(i>>1)
+    const unsigned lm_addr = (unsigned)__cvta_generic_to_shared(&wr.w[((lane >> 3) & 1) * 8 + (lane & 7)][4 * (lane >> 4)]);
+    unsigned wcol, wcst;  // shared addresses of this lane's column in the w plane / of cst[0] (32-bit registers)
+    asm volatile("mov.u32 %0, %1;" : "=r"(wcol) : "r"((unsigned)__cvta_generic_to_shared(&wr.w[0][lane])));
+    asm volatile("mov.u32 %0, %1;" : "=r"(wcst) : "r"((unsigned)__cvta_generic_to_shared(&wr.cst[0])));
     int pending = 0;
 
     // round r holds list entries k = hi - (r+1)*BB + slot, slot in [0, BB)
@@ -131,7 +235,7 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
     uint32_t id_next = 0;
     {
         const int k = hi - BB + slot;
-        if (k >= 0) bwd_gather(st[0], tid, (uint32_t)list[k], p.geom);
+        if (k >= 0) bwd_gather(sm.st[0], tid, (uint32_t)list[k], p.geom);
         cp_async_commit();
         if (k - BB >= 0) id_next = (uint32_t)list[k - BB];
     }
@@ -142,13 +246,13 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
         __syncthreads();
         if (r + 1 < rounds) {
             const int k = base - BB + slot;
-            if (k >= 0) bwd_gather(st[buf ^ 1], tid, id_next, p.geom);
+            if (k >= 0) bwd_gather(sm.st[buf ^ 1], tid, id_next, p.geom);
             if (k - BB >= 0) id_next = (uint32_t)list[k - BB];
         }
         cp_async_commit();
         if (base >= warp_last) continue;  // whole batch lies behind this warp's last contributor
 
-        const BwdStage& s = st[buf];
+        const BwdStage& s = sm.st[buf];
         for (int c0 = BB - 32; c0 >= 0; c0 -= 32) {
             const int mine = c0 + lane;
             const int kmine = base + mine;
@@ -166,7 +270,7 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
                 const int k = base + j;
                 const float4 a = s.rec0[j];
                 const float4 b = s.rec1[j];
-                float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f, v8 = 0.f, v9 = 0.f;
+                float w = 0.f, c = 0.f;
                 bool active = false;
                 if (k < last_contributor) {
                     const float dx = a.x - pixx, dy = a.y - pixy;
@@ -185,44 +289,40 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
                             last_x = x;
                             last_alpha = alpha;
                             const float dLa = fmaf(-tfbg, inv, (x - A) * T);  // dL/dalpha
-                            const float dch = alpha * T;
-                            const float t = b.y * dLa;                       // dL/dG
-                            const float aa = G * dx * t, bb = G * dy * t;
-                            v0 = fmaf(aa, a.z, bb * a.w);   // -> dL/dmean2D.x after * -(W/2)
-                            v1 = fmaf(bb, b.x, aa * a.w);   // -> dL/dmean2D.y after * -(H/2)
-                            v2 = aa * dx;                   // -> dL/dconic.x after * -1/2
-                            v3 = aa * dy;                   // -> dL/dconic.y after * -1/2
-                            v4 = bb * dy;                   // -> dL/dconic.w after * -1/2
-                            v5 = G * dLa;                   // dL/dopacity
-                            v6 = dch * dpx; v7 = dch * dpy; v8 = dch * dpz;  // dL/dcolor
-                            v9 = dch * dpd;                 // dL/ddepth
+                            c = alpha * T;
+                            w = G * dLa;
                         }
                     }
                 }
                 if (__any_sync(0xffffffffu, active)) {
-                    const unsigned c = wcol + pending * (10 * ROW * 4);
-                    asm volatile(
-                        "st.shared.f32 [%0], %1;\n\tst.shared.f32 [%0+144], %2;\n\tst.shared.f32 [%0+288], %3;\n\t"
-                        "st.shared.f32 [%0+432], %4;\n\tst.shared.f32 [%0+576], %5;\n\tst.shared.f32 [%0+720], %6;\n\t"
-                        "st.shared.f32 [%0+864], %7;\n\tst.shared.f32 [%0+1008], %8;\n\tst.shared.f32 [%0+1152], %9;\n\t"
-                        "st.shared.f32 [%0+1296], %10;\n" ::"r"(c), "f"(v0), "f"(v1), "f"(v2), "f"(v3), "f"(v4), "f"(v5),
-                        "f"(v6), "f"(v7), "f"(v8), "f"(v9) : "memory");
-                    const uint32_t gid = s.id[j];
-                    if (pending == my_g) my_id = gid;
-                    if (++pending == GROUP) {
-                        flush_group(wrow, my_id, GROUP, lane, my_sub, acc);
+                    const unsigned ca = wcol + pending * (VP * 4);
+                    asm volatile("st.shared.f32 [%0], %1;\n\tst.shared.f32 [%0+%3], %2;\n" ::"r"(ca), "f"(w), "f"(c),
+                                 "n"(MG * VP * 4) : "memory");
+                    {
+                        const float gid = __uint_as_float(s.id[j]), ex = a.x - rx0, ey = a.y - ry0;
+                        if (lane == 0)
+                            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %3};\n" ::"r"(wcst + pending * 16), "f"(gid),
+                                         "f"(ex), "f"(ey) : "memory");
+                    }
+                    if (++pending == MG) {
+                        flush_pending(wr, lm_addr, MG, lane, bw, bc, acc);
                         pending = 0;
                     }
                 }
             }
         }
     }
-    if (pending) flush_group(wrow, my_id, pending, lane, my_sub, acc);
+    if (pending) flush_pending(wr, lm_addr, pending, lane, bw, bc, acc);
     cp_async_wait<0>();
 }
 
 void launch_render_bwd(const RenderBwdParams& p, cudaStream_t s) {
-    render_bwd_kernel<<<p.ntiles, 256, 0, s>>>(p);
+    render_bwd_kernel<<<p.gx * p.gy, 256, sizeof(BwdSmem), s>>>(p);
+}
+
+int configure_render_bwd() {
+    return (int)cudaFuncSetAttribute(render_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(BwdSmem));
 }
 
 }  // namespace wgs

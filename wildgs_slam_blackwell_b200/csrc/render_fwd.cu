@@ -59,7 +59,9 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
     __shared__ FwdStage st[2];
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = p.tile0 + blockIdx.x;
+    // longest tiles first (tile_scan's order); a tile-row strip skips the tiles outside it
+    const int tile = (int)p.tile.order[blockIdx.x];
+    if (tile < p.tile0 || tile >= p.tile0 + p.ntiles) return;
     const int tx = tile % p.gx, ty = tile / p.gx;
     const int wx0 = tx * WGS_TILE + (warp & 1) * 8, wy0 = ty * WGS_TILE + (warp >> 1) * 4;
     const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
 }
 
 void launch_render_fwd(const RenderFwdParams& p, cudaStream_t s) {
-    render_fwd_kernel<<<p.ntiles, 256, 0, s>>>(p);
+    render_fwd_kernel<<<p.gx * p.gy, 256, 0, s>>>(p);
 }
 
 }  // namespace wgs
