@@ -170,7 +170,10 @@ class Workload:
         # (rasterizer.grad_sink) that NCCL then sums in place -- no packing copy
         self.bucket = torch.zeros(self.bucket_floats, dtype=torch.float32, device=dev)
         self.sink = None
+        self.fused_loss = None
         if hasattr(mod, "grad_sink"):
+            from wildgs_slam_blackwell_b200.loss import photometric_loss
+            self.fused_loss = photometric_loss
             views, off = {}, 0
             for name, t in zip(("means3D", "sh", "opacity", "scales", "rotations"), self.leaves):
                 views[name] = self.bucket[off:off + t.numel()].view(t.shape)
@@ -226,8 +229,15 @@ class Workload:
         self.prefetch(i + 1)
         self._zero_grads(st.leaves)
         color, radii, depth, opacity, n_touched = self._forward(st)
-        loss = (color - st.d["target_color"]).abs().mean() + (depth - st.d["target_depth"]).abs().mean()
-        self._backward(world, loss.backward)
+        if self.fused_loss is not None:
+            # own arm: the fused loss + cotangent kernel -- same value and gradients
+            loss, dcol, ddep, _ = self.fused_loss(color, st.d["target_color"], depth=depth,
+                                                  gt_depth=st.d["target_depth"], rgb_boundary_threshold=-1e30,
+                                                  depth_min=-1e30, color_weight=1.0, depth_weight=1.0)
+            self._backward(world, lambda: torch.autograd.backward([color, depth], [dcol, ddep]))
+        else:
+            loss = (color - st.d["target_color"]).abs().mean() + (depth - st.d["target_depth"]).abs().mean()
+            self._backward(world, loss.backward)
         res = torch.cat([loss.detach().reshape(1), self.rho.grad.reshape(-1), self.theta.grad.reshape(-1)])
         self.out_host.copy_(res, non_blocking=True)
         st.compute_done.record(cur)
@@ -386,7 +396,10 @@ def main():
         e2e_ms, _ = timed_loop(lambda: wl.step_e2e(world), a.steps, a.warmup, flush, world)
         e2e = {"value": round(frames / (e2e_ms * 1e-3), 3), "unit": "frames/s", "h2d_bytes_per_step": wl.h2d_bytes,
                "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": round(e2e_ms / a.steps, 4),
-               "pipelining": "inputs of step i+1 copied on a second stream during step i (double-buffered)"}
+               "pipelining": "inputs of step i+1 copied on a second stream during step i (double-buffered)",
+               "loss": "mean|color - target| + mean|depth - target|: " +
+                       ("fused loss+cotangent kernel (wgs_photometric_loss)" if wl.fused_loss is not None
+                        else "torch expression + autograd (what the reference's callers run)")}
 
     roof = stages = counts = None
     if a.impl == "ours" and rank == 0:
@@ -412,7 +425,7 @@ def main():
             "clocks": clocks,
             # our kernels per step: preprocess_fwd, tile_scan, scatter, tile_sort_small, tile_sort_large,
             # render_fwd, render_bwd, preprocess_bwd
-            "gpu_launches": 8 * a.steps if a.impl == "ours" else 0,
+            "gpu_launches": 8 * a.steps if a.impl == "ours" else 0,   # (+1 per e2e step: photometric_loss_kernel)
         }
         if e2e:
             line["e2e"] = e2e

@@ -1,0 +1,70 @@
+"""CPU: the numpy loss oracle (oracle/loss_oracle.py) against the golden vectors produced by the
+REFERENCE's own get_loss_tracking / get_loss_mapping (tests/golden/make_loss_golden.py), the ctypes
+struct against include/wgs_loss.h, and the exported symbols."""
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import loss_oracle  # noqa: E402
+from wildgs_slam_blackwell_b200 import _lib, loss  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+KINDS = ("tracking", "tracking_unc", "mapping", "mapping_init")
+
+
+def oracle_for(g):
+    kind = str(g["kind"])
+    kw = dict(rgb_boundary_threshold=float(g["threshold"]))
+    if kind.startswith("tracking"):
+        kw.update(opacity=g["opacity"], pixel_mask=g["grad_mask"].astype(np.float32), exposure_a=g["a"],
+                  exposure_b=g["b"], color_weight=1.0, depth_weight=0.0)
+        if kind == "tracking_unc":
+            kw["uncertainty"] = g["unc"]
+    else:
+        alpha = float(g["alpha"])
+        kw.update(depth=g["depth"], gt_depth=g["gt_depth"], color_weight=alpha, depth_weight=1.0 - alpha)
+        if kind == "mapping":
+            kw.update(exposure_a=g["a"], exposure_b=g["b"])
+    return kw
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_oracle_matches_reference_golden(kind):
+    g = dict(np.load(os.path.join(GOLDEN, f"loss_{kind}.npz")))
+    o = loss_oracle.photometric_loss(g["image"], g["gt"], **oracle_for(g))
+    np.testing.assert_allclose(o["loss"], g["loss"], rtol=2e-6)
+    np.testing.assert_allclose(o["dL_dcolor"], g["g_image"], rtol=1e-5, atol=1e-10)
+    np.testing.assert_allclose(o["dL_ddepth"], g["g_depth"], rtol=1e-5, atol=1e-10)
+    if kind != "mapping_init":
+        np.testing.assert_allclose(o["dL_da"], g["g_a"][0], rtol=2e-4)
+        np.testing.assert_allclose(o["dL_db"], g["g_b"][0], rtol=2e-4, atol=1e-7)
+
+
+def test_loss_abi_symbols_and_struct():
+    header = open(os.path.join(ROOT, "include", "wgs_loss.h")).read()
+    declared = set(re.findall(r"\b(wgs_[a-z_]+)\s*\(", header)) - {"wgs_backward", "wgs_last_error"}
+    assert declared == set(loss.EXPORTS), declared ^ set(loss.EXPORTS)
+    lib = _lib.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    body = re.search(r"typedef struct WgsLossArgs \{(.*?)\} WgsLossArgs;", header, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for decl in body.split(";"):
+        for part in decl.strip().split(","):
+            if part.strip():
+                names.append(re.findall(r"[A-Za-z_0-9]+", part)[-1])
+    assert names == [f[0] for f in loss.LossArgs._fields_]
+    assert loss._lib_loss().wgs_loss_workspace_bytes(640, 480) >= 256 + 300 * 32
+    assert loss._lib_loss().wgs_photometric_loss(None, None) == _lib.WGS_ERR_INVALID_ARGUMENT
+
+
+def test_no_cpu_fallback():
+    import torch
+    with pytest.raises(RuntimeError, match="CUDA"):
+        loss.photometric_loss(torch.zeros(3, 4, 4), torch.zeros(3, 4, 4))

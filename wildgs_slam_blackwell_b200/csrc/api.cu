@@ -66,6 +66,8 @@ extern "C" {
 
 int wgs_abi_version(void) { return WGS_ABI_VERSION; }
 const char* wgs_last_error(void) { return g_err; }
+// used by the other translation units of the library (loss.cu, ...)
+void wgs_set_error_message(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg ? msg : ""); }
 
 WgsContext* wgs_context_create(int device) {
     cudaDeviceProp prop;

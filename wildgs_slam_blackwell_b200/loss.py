@@ -1,0 +1,195 @@
+"""Fused photometric loss + cotangent producer (include/wgs_loss.h).
+
+Host-side mirror of the reference's loss entry points for the rasterizer's two callers,
+same names and argument meaning (src/utils/slam_utils.py):
+
+    get_loss_tracking(config, image, depth, opacity, viewpoint, monocular=True, uncertainty=None)   (:47-53)
+    get_loss_tracking_rgb(config, image, opacity, viewpoint, uncertainty=None)                      (:55-87)
+    get_loss_mapping(config, image, depth, viewpoint, initialization=False)                         (:107-113)
+    get_loss_mapping_rgbd(config, image, depth, viewpoint)                                          (:116-143)
+
+Each returns a scalar tensor whose `.backward()` feeds dL/dcolor, dL/ddepth and
+dL/d(exposure_a, exposure_b) to autograd, like the reference's torch expression, but the forward
+is ONE kernel that also produces those gradients (the backward only scales them by the incoming
+gradient).  `photometric_loss()` is the raw form: loss and cotangents without autograd, for
+callers that drive `torch.autograd.backward([color, depth], [dL_dcolor, dL_ddepth])` themselves.
+
+ssim_loss=True (a convolution chain) is not fused: those configs raise.
+No CPU / PyTorch fallback: the kernel lives in libwgs_rasterizer.so.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+_fp = C.c_void_p
+
+
+class LossArgs(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32),
+        ("rgb_boundary_threshold", C.c_float), ("depth_min", C.c_float),
+        ("color_weight", C.c_float), ("depth_weight", C.c_float),
+        ("color", _fp), ("depth", _fp), ("opacity", _fp), ("gt_color", _fp), ("gt_depth", _fp),
+        ("pixel_mask", _fp), ("uncertainty", _fp), ("exposure_a", _fp), ("exposure_b", _fp),
+        ("loss", _fp), ("dL_dcolor", _fp), ("dL_ddepth", _fp), ("dL_dexposure", _fp), ("workspace", _fp),
+    ]
+
+
+EXPORTS = ("wgs_loss_workspace_bytes", "wgs_photometric_loss")
+_ws = {}
+_proto_done = False
+
+
+def _lib_loss():
+    global _proto_done
+    lib = _lib.load()
+    if not _proto_done:
+        lib.wgs_loss_workspace_bytes.restype = C.c_size_t
+        lib.wgs_loss_workspace_bytes.argtypes = [C.c_int32, C.c_int32]
+        lib.wgs_photometric_loss.argtypes = [C.POINTER(LossArgs), C.c_void_p]
+        _proto_done = True
+    return lib
+
+
+def _workspace(device, W, H):
+    key = (device.index, W, H)
+    ws = _ws.get(key)
+    if ws is None:
+        ws = torch.zeros(int(_lib_loss().wgs_loss_workspace_bytes(W, H)), dtype=torch.uint8, device=device)
+        _ws[key] = ws
+    return ws
+
+
+def _f32(t, device, shape=None):
+    if t is None:
+        return None
+    if t.dtype != torch.float32 or t.device != device:
+        t = t.to(device=device, dtype=torch.float32)
+    t = t.contiguous()
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        t = t.reshape(shape)
+    return t
+
+
+def photometric_loss(color, gt_color, *, depth=None, gt_depth=None, opacity=None, pixel_mask=None,
+                     uncertainty=None, exposure_a=None, exposure_b=None, rgb_boundary_threshold=0.01,
+                     depth_min=0.01, color_weight=1.0, depth_weight=0.0):
+    """One launch: returns (loss (1,), dL_dcolor (3,H,W), dL_ddepth (1,H,W), dL_dexposure (2,) or None).
+    See include/wgs_loss.h for the exact expression."""
+    if color.dim() != 3 or color.shape[0] != 3:
+        raise RuntimeError("color must have dimensions (3, H, W)")
+    device = color.device
+    if device.type != "cuda":
+        raise RuntimeError("photometric_loss runs on a CUDA (sm_100) device only; there is no CPU fallback")
+    _, H, W = color.shape
+    color = _f32(color.detach(), device)
+    gt_color = _f32(gt_color, device, (3, H, W))
+    depth = _f32(None if depth is None else depth.detach(), device, (1, H, W))
+    gt_depth = _f32(gt_depth, device, (1, H, W))
+    opacity = _f32(None if opacity is None else opacity.detach(), device, (1, H, W))
+    pixel_mask = _f32(pixel_mask, device, (1, H, W))
+    uncertainty = _f32(uncertainty, device, (H, W))
+    ea = _f32(None if exposure_a is None else exposure_a.detach(), device, (1,))
+    eb = _f32(None if exposure_b is None else exposure_b.detach(), device, (1,))
+    if (ea is None) != (eb is None):
+        raise RuntimeError("exposure_a and exposure_b go together")
+    if depth_weight != 0.0 and (depth is None or gt_depth is None):
+        raise RuntimeError("depth_weight != 0 needs depth and gt_depth")
+    out = torch.empty(4 * H * W + 4, dtype=torch.float32, device=device)  # one allocation for all outputs
+    dL_dcolor = out[:3 * H * W].view(3, H, W)
+    dL_ddepth = out[3 * H * W:4 * H * W].view(1, H, W)
+    loss = out[4 * H * W:4 * H * W + 1]
+    dexp = out[4 * H * W + 1:4 * H * W + 3]
+    a = LossArgs()
+    a.width, a.height = W, H
+    a.rgb_boundary_threshold, a.depth_min = float(rgb_boundary_threshold), float(depth_min)
+    a.color_weight, a.depth_weight = float(color_weight), float(depth_weight)
+    p = lambda t: None if t is None else t.data_ptr()
+    a.color, a.depth, a.opacity, a.gt_color, a.gt_depth = p(color), p(depth), p(opacity), p(gt_color), p(gt_depth)
+    a.pixel_mask, a.uncertainty, a.exposure_a, a.exposure_b = p(pixel_mask), p(uncertainty), p(ea), p(eb)
+    a.loss, a.dL_dcolor, a.dL_ddepth = p(loss), p(dL_dcolor), p(dL_ddepth)
+    a.dL_dexposure = p(dexp) if ea is not None else None
+    a.workspace = _workspace(device, W, H).data_ptr()
+    with torch.cuda.device(device):
+        rc = _lib_loss().wgs_photometric_loss(C.byref(a), C.c_void_p(torch.cuda.current_stream(device).cuda_stream))
+    if rc != _lib.WGS_OK:
+        raise RuntimeError(f"wgs_photometric_loss failed ({rc}): {_lib.last_error()}")
+    return loss, dL_dcolor, dL_ddepth, (dexp if ea is not None else None)
+
+
+class _PhotometricLoss(torch.autograd.Function):
+    """loss = f(color, depth, exposure_a, exposure_b); the cotangents are computed in forward."""
+
+    @staticmethod
+    def forward(ctx, color, depth, exposure_a, exposure_b, kw):
+        loss, dc, dd, de = photometric_loss(color, kw["gt_color"], depth=depth, gt_depth=kw.get("gt_depth"),
+                                            opacity=kw.get("opacity"), pixel_mask=kw.get("pixel_mask"),
+                                            uncertainty=kw.get("uncertainty"), exposure_a=exposure_a,
+                                            exposure_b=exposure_b,
+                                            rgb_boundary_threshold=kw["rgb_boundary_threshold"],
+                                            color_weight=kw["color_weight"], depth_weight=kw["depth_weight"])
+        ctx.has_depth = depth is not None and kw["depth_weight"] != 0.0
+        ctx.has_exp = de is not None
+        ctx.save_for_backward(dc, dd, de if de is not None else dc.new_empty(0))
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        dc, dd, de = ctx.saved_tensors
+        ga = gb = None
+        if ctx.has_exp:
+            ge = de * g
+            ga, gb = ge[0:1], ge[1:2]
+        return dc * g, (dd * g if ctx.has_depth else None), ga, gb, None
+
+
+def _gt_image(viewpoint, device):
+    return viewpoint.original_image.to(device)
+
+
+def _gt_depth(viewpoint, device):
+    """viewpoint.depth is a numpy (H,W) array (src/utils/camera_utils.py); the reference re-uploads it on
+    every call (slam_utils.py:123-127).  Here the device copy is cached on the viewpoint."""
+    cache = getattr(viewpoint, "_wgs_depth_dev", None)
+    if cache is None or cache[0] is not viewpoint.depth or cache[1].device != device:
+        d = viewpoint.depth
+        t = torch.from_numpy(np.ascontiguousarray(d, np.float32)) if isinstance(d, np.ndarray) else d.float()
+        cache = (viewpoint.depth, t.to(device)[None].contiguous())
+        try:
+            viewpoint._wgs_depth_dev = cache
+        except AttributeError:
+            pass
+    return cache[1]
+
+
+def get_loss_tracking_rgb(config, image, opacity, viewpoint, uncertainty=None, _exposure=(None, None)):
+    kw = dict(gt_color=_gt_image(viewpoint, image.device), opacity=opacity,
+              pixel_mask=getattr(viewpoint, "grad_mask", None), uncertainty=uncertainty,
+              rgb_boundary_threshold=config["Training"]["rgb_boundary_threshold"], color_weight=1.0,
+              depth_weight=0.0)
+    return _PhotometricLoss.apply(image, None, _exposure[0], _exposure[1], kw)
+
+
+def get_loss_tracking(config, image, depth, opacity, viewpoint, monocular=True, uncertainty=None):
+    if not monocular:
+        raise NotImplementedError("Only implemented monocular, not rgbd for uncertainty-aware tracking")
+    return get_loss_tracking_rgb(config, image, opacity, viewpoint, uncertainty,
+                                 _exposure=(viewpoint.exposure_a, viewpoint.exposure_b))
+
+
+def get_loss_mapping_rgbd(config, image, depth, viewpoint, _exposure=(None, None)):
+    if config["Training"].get("ssim_loss", False):
+        raise NotImplementedError("ssim_loss=True is not fused (SURVEY.md §8(f)); use the torch expression")
+    alpha = config["Training"]["alpha"] if "alpha" in config["Training"] else 0.95
+    kw = dict(gt_color=_gt_image(viewpoint, image.device), gt_depth=_gt_depth(viewpoint, image.device),
+              rgb_boundary_threshold=config["Training"]["rgb_boundary_threshold"], color_weight=alpha,
+              depth_weight=1.0 - alpha)
+    return _PhotometricLoss.apply(image, depth, _exposure[0], _exposure[1], kw)
+
+
+def get_loss_mapping(config, image, depth, viewpoint, initialization=False):
+    exposure = (None, None) if initialization else (viewpoint.exposure_a, viewpoint.exposure_b)
+    return get_loss_mapping_rgbd(config, image, depth, viewpoint, _exposure=exposure)
