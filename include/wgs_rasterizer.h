@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define WGS_ABI_VERSION 7
+#define WGS_ABI_VERSION 8
 
 /* status codes (negative = error) */
 #define WGS_OK 0
@@ -94,6 +94,15 @@ typedef struct WgsForwardArgs {
    * Images, n_touched and (in the backward) all gradients of the strips of a partition of the image sum
    * to the whole-image results. */
   int32_t tile_row_begin, tile_row_end;
+  /* Raw-parameter mode (the activations the reference's render() wrapper
+   * applies with separate torch kernels before every rasterizer call,
+   * thirdparty/gaussian_splatting/scene/gaussian_model.py:54-63,77-97, fused into the per-Gaussian stage).
+   * activations != 0: `opacities` holds GaussianModel._opacity (sigmoid applied here), `scales` holds
+   * _scaling (exp applied here), `rotations` holds _rotation (normalised here, eps 1e-12 like
+   * torch.nn.functional.normalize).  sh_rest != null: `sh` holds _features_dc (P,1,3) and `sh_rest`
+   * _features_rest (P,M-1,3) -- the torch.cat of get_features is never materialised; M stays the total. */
+  int32_t activations;
+  const float* sh_rest;
 } WgsForwardArgs;
 
 /* Arguments of the backward pass.  Replaces RasterizeGaussiansBackwardCUDA
@@ -139,6 +148,13 @@ typedef struct WgsBackwardArgs {
   void* grad;           /* accumulators; must be zero before the FIRST backward that uses it (kernels re-zero it) */
   int64_t capacity;
   int32_t tile_row_begin, tile_row_end; /* must equal the matching forward's */
+  /* Raw-parameter mode, must equal the matching forward's.  With activations != 0, dL_dopacity,
+   * dL_dscales and dL_drotations are gradients w.r.t. the RAW parameters (chain rule through sigmoid /
+   * exp / normalize applied in the kernel).  With sh_rest != null, dL_dsh is (P,1,3) and dL_dsh_rest
+   * (P,M-1,3). */
+  int32_t activations;
+  const float* sh_rest;
+  float* dL_dsh_rest;
 } WgsBackwardArgs;
 
 /* library / device */
@@ -189,6 +205,14 @@ int wgs_export_geometry(const WgsForwardArgs* args, float* depths, float* means2
  *   [4] render_fwd      [5] render_bwd [6] preprocess_bwd   [7] reserved (0)
  * Stages that did not run since the last call report 0. */
 #define WGS_NUM_STAGES 8
+/* Camera matrices of one view in one launch.  Replaces the reference Camera's
+ * per-access properties world_view_transform / full_proj_transform / camera_center
+ * (src/utils/camera_utils.py:137-151; graphics_utils.py:33-46): R (3,3) row-major and T (3,) of the W2C
+ * pose, projection_matrix (4,4) = P^T as stored by the reference; outputs viewmatrix (4,4) = W2C^T,
+ * projmatrix (4,4) = viewmatrix @ projection_matrix, campos (3,) = -R^T T.  All device pointers. */
+int wgs_camera_matrices(const float* R, const float* T, const float* projection_matrix, float* viewmatrix,
+                        float* projmatrix, float* campos, void* cuda_stream);
+
 int wgs_stage_timing(WgsContext* ctx, int enable);
 int wgs_stage_times(WgsContext* ctx, float* ms_out /* WGS_NUM_STAGES floats, host */);
 

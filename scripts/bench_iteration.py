@@ -1,0 +1,107 @@
+#!/usr/bin/env python
+"""Tracking-iteration time (config 2: 300 k Gaussians, 640x480): render() + get_loss_tracking + backward,
+the loop body of Mapper.refine_pose_non_key_frame (src/mapper.py:886-904), in three arrangements:
+  composition : the reference's wrapper arrangement (torch activations, torch camera properties, torch loss
+                expression + autograd) on OUR rasterizer
+  fused       : renderer.render (raw-parameter mode + camera kernel) + fused loss kernel
+  reference   : the composition on the UNMODIFIED reference rasterizer (oracle/_ref), when built
+Prints one JSON line (ms per iteration, CUDA events, L2 flushed between iterations)."""
+import json
+import os
+import statistics
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from test_gpu_render import Cam, Model, Pipe  # noqa: E402
+from wildgs_slam_blackwell_b200 import loss as fused_loss, renderer, scenes  # noqa: E402
+
+DEV = "cuda:0"
+CONFIG = {"Training": {"rgb_boundary_threshold": 0.01}}
+
+
+def torch_loss_tracking(image, opacity, vp):
+    """get_loss_tracking + get_loss_tracking_rgb as torch expressions (slam_utils.py:47-87)."""
+    image_ab = torch.exp(vp.exposure_a) * image + vp.exposure_b
+    gt = vp.original_image
+    m = (gt.sum(dim=0) > CONFIG["Training"]["rgb_boundary_threshold"]).view(1, *gt.shape[1:]) * vp.grad_mask
+    return (opacity * torch.abs(image_ab * m - gt * m)).mean()
+
+
+def composition(mod, cam, pc, bg):
+    import math
+    sp = torch.zeros_like(pc.get_xyz, requires_grad=True) + 0
+    s = mod.GaussianRasterizationSettings(
+        image_height=cam.image_height, image_width=cam.image_width, tanfovx=math.tan(cam.FoVx * 0.5),
+        tanfovy=math.tan(cam.FoVy * 0.5), bg=bg, scale_modifier=1.0, viewmatrix=cam.world_view_transform,
+        projmatrix=cam.full_proj_transform, projmatrix_raw=cam.projection_matrix, sh_degree=pc.active_sh_degree,
+        campos=cam.camera_center, prefiltered=False, debug=False)
+    img, radii, depth, opacity, n_touched = mod.GaussianRasterizer(s)(
+        means3D=pc.get_xyz, means2D=sp, shs=pc.get_features, colors_precomp=None, opacities=pc.get_opacity,
+        scales=pc.get_scaling, rotations=pc.get_rotation, cov3D_precomp=None, theta=cam.cam_rot_delta,
+        rho=cam.cam_trans_delta)
+    return img, depth, opacity
+
+
+def timeit(fn, flush, warm=10, steps=60):
+    for _ in range(warm):
+        fn(); flush.add_(1)
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in ev:
+        flush.add_(1); a.record(); fn(); b.record()
+    torch.cuda.synchronize()
+    return statistics.median(a.elapsed_time(b) for a, b in ev)
+
+
+def main():
+    P, W, H, deg, _ = scenes.CONFIGS["config2"]
+    cam_d = scenes.make_camera(W, H, 1002)
+    g = scenes.make_gaussians(P, W, H, deg, 1002, cam_d)
+    rng = np.random.default_rng(3)
+    bg = torch.zeros(3, device=DEV)
+    flush = torch.zeros((512 << 20) // 4, device=DEV)
+    res = {}
+    arms = ["composition", "fused"]
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if os.path.exists(os.path.join(ref_dir, "diff_gaussian_rasterization", "_C.so")):
+        arms.append("reference")
+    for arm in arms:
+        pc, cam = Model(g, 1), Cam(cam_d)
+        cam.original_image = torch.from_numpy(rng.uniform(0, 1, (3, H, W)).astype(np.float32)).to(DEV)
+        cam.grad_mask = torch.from_numpy(rng.uniform(0, 1, (1, H, W)) > 0.3).to(DEV)
+        cam.exposure_a = torch.zeros(1, device=DEV, requires_grad=True)
+        cam.exposure_b = torch.zeros(1, device=DEV, requires_grad=True)
+        leaves = list(pc.leaves().values()) + [cam.cam_rot_delta, cam.cam_trans_delta, cam.exposure_a, cam.exposure_b]
+        if arm == "reference":
+            import importlib
+            for k in [k for k in sys.modules if k.startswith("diff_gaussian_rasterization")]:
+                del sys.modules[k]
+            sys.path.insert(0, ref_dir)
+            mod = importlib.import_module("diff_gaussian_rasterization")
+            assert os.path.abspath(mod.__file__).startswith(ref_dir)
+        else:
+            import wildgs_slam_blackwell_b200.rasterizer as mod
+
+        def step():
+            for t in leaves:
+                t.grad = None
+            if arm == "fused":
+                pkg = renderer.render(cam, pc, Pipe(), bg)
+                l = fused_loss.get_loss_tracking(CONFIG, pkg["render"], pkg["depth"], pkg["opacity"], cam)
+            else:
+                img, depth, opacity = composition(mod, cam, pc, bg)
+                l = torch_loss_tracking(img, opacity, cam)
+            l.backward()
+
+        res[arm] = round(timeit(step, flush), 4)
+    print(json.dumps({"what": "tracking iteration (render + tracking loss + backward), config2, ms per iteration (median)",
+                      **res}))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,179 @@
+"""GPU: render() (mirror of the reference's gaussian_renderer.render) with the activations, the dc|rest
+concatenation and the camera matrices fused into kernels, against the reference's own composition
+(torch activations + torch camera properties) run on top of the parity-pinned drop-in rasterizer.
+SURVEY.md §8(f) row 1."""
+import math
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import util  # noqa: E402
+from wildgs_slam_blackwell_b200 import renderer, scenes  # noqa: E402
+from wildgs_slam_blackwell_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+class Pipe:
+    compute_cov3D_python = False
+    convert_SHs_python = False
+
+
+class Model:
+    """The slice of the reference GaussianModel render() touches (gaussian_model.py:54-63,77-97)."""
+
+    def __init__(self, g, seed):
+        rng = np.random.default_rng(seed)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a, np.float32)).to(DEV).requires_grad_(True)
+        o = np.clip(g["opacities"], 1e-4, 1 - 1e-4)
+        self._xyz = t(g["means3D"])
+        self._features_dc = t(g["sh"][:, :1])
+        self._features_rest = t(g["sh"][:, 1:])
+        self._opacity = t(np.log(o / (1 - o)))
+        self._scaling = t(np.log(g["scales"]))
+        self._rotation = t(g["rotations"] * rng.uniform(0.5, 2.0, (g["rotations"].shape[0], 1)))  # not unit length
+        self.active_sh_degree = g["sh_degree"]
+        self.max_sh_degree = g["sh_degree"]
+
+    get_xyz = property(lambda s: s._xyz)
+    get_opacity = property(lambda s: torch.sigmoid(s._opacity))
+    get_scaling = property(lambda s: torch.exp(s._scaling))
+    get_rotation = property(lambda s: torch.nn.functional.normalize(s._rotation))
+    get_features = property(lambda s: torch.cat((s._features_dc, s._features_rest), dim=1))
+
+    def leaves(self):
+        return dict(xyz=self._xyz, f_dc=self._features_dc, f_rest=self._features_rest, opacity=self._opacity,
+                    scaling=self._scaling, rotation=self._rotation)
+
+
+class Cam:
+    """The slice of the reference Camera render() touches; the three properties are the reference's torch
+    expressions (camera_utils.py:137-151, graphics_utils.py:33-46)."""
+
+    def __init__(self, cam):
+        w2c = np.asarray(cam["viewmatrix"], np.float64).T
+        self.R = torch.from_numpy(w2c[:3, :3].astype(np.float32)).to(DEV)
+        self.T = torch.from_numpy(w2c[:3, 3].astype(np.float32)).to(DEV)
+        self.projection_matrix = torch.from_numpy(np.asarray(cam["projmatrix_raw"], np.float32)).to(DEV)
+        self.FoVx, self.FoVy = 2 * math.atan(cam["tanfovx"]), 2 * math.atan(cam["tanfovy"])
+        self.image_height, self.image_width = cam["height"], cam["width"]
+        self.cam_rot_delta = torch.zeros(3, device=DEV, requires_grad=True)
+        self.cam_trans_delta = torch.zeros(3, device=DEV, requires_grad=True)
+
+    @property
+    def world_view_transform(self):
+        Rt = torch.zeros((4, 4), device=DEV)
+        Rt[:3, :3] = self.R
+        Rt[:3, 3] = self.T
+        Rt[3, 3] = 1.0
+        return torch.linalg.inv(torch.linalg.inv(Rt)).transpose(0, 1)
+
+    @property
+    def full_proj_transform(self):
+        return self.world_view_transform.unsqueeze(0).bmm(self.projection_matrix.unsqueeze(0)).squeeze(0)
+
+    @property
+    def camera_center(self):
+        return self.world_view_transform.inverse()[3, :3]
+
+
+def reference_composition(cam, pc, bg):
+    """gaussian_renderer/__init__.py:41-141 verbatim in behaviour, on the drop-in rasterizer."""
+    screenspace_points = torch.zeros_like(pc.get_xyz, requires_grad=True)
+    s = GaussianRasterizationSettings(
+        image_height=int(cam.image_height), image_width=int(cam.image_width), tanfovx=math.tan(cam.FoVx * 0.5),
+        tanfovy=math.tan(cam.FoVy * 0.5), bg=bg, scale_modifier=1.0, viewmatrix=cam.world_view_transform,
+        projmatrix=cam.full_proj_transform, projmatrix_raw=cam.projection_matrix, sh_degree=pc.active_sh_degree,
+        campos=cam.camera_center, prefiltered=False, debug=False)
+    img, radii, depth, opacity, n_touched = GaussianRasterizer(s)(
+        means3D=pc.get_xyz, means2D=screenspace_points, shs=pc.get_features, colors_precomp=None,
+        opacities=pc.get_opacity, scales=pc.get_scaling, rotations=pc.get_rotation, cov3D_precomp=None,
+        theta=cam.cam_rot_delta, rho=cam.cam_trans_delta)
+    return dict(render=img, viewspace_points=screenspace_points, radii=radii, depth=depth, opacity=opacity,
+                n_touched=n_touched)
+
+
+def test_camera_matrices_match_reference_properties():
+    cam = Cam(scenes.make_camera(320, 240, 77))
+    v, p, c = renderer.camera_matrices(cam.R, cam.T, cam.projection_matrix)
+    torch.testing.assert_close(v, cam.world_view_transform, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(p, cam.full_proj_transform, rtol=1e-5, atol=2e-6)
+    torch.testing.assert_close(c, cam.camera_center, rtol=1e-5, atol=1e-6)
+    # cached until the pose tensors change
+    a = renderer._cached_matrices(cam)
+    assert renderer._cached_matrices(cam)[0] is a[0]
+    cam.T = cam.T + 0.1
+    assert renderer._cached_matrices(cam)[0] is not a[0]
+    with torch.no_grad():
+        cam.R.mul_(1.0)
+    b = renderer._cached_matrices(cam)
+    assert b[0] is not a[0]
+
+
+@pytest.mark.parametrize("P,W,H,deg,seed", [(20000, 320, 240, 0, 11), (8000, 200, 136, 3, 12), (5000, 96, 64, 1, 13)])
+def test_fused_render_matches_reference_composition(P, W, H, deg, seed):
+    cam_d = scenes.make_camera(W, H, seed, bg=(0.2, 0.4, 0.1))
+    g = scenes.make_gaussians(P, W, H, deg, seed, scenes.make_camera(W, H, seed))
+    dc, dd = scenes.make_cotangents(W, H, seed)
+    dc, dd = torch.from_numpy(dc).to(DEV), torch.from_numpy(dd).to(DEV)
+    bg = torch.tensor(cam_d["bg"], dtype=torch.float32, device=DEV)
+    out = {}
+    for name in ("fused", "ref"):
+        pc, cam = Model(g, seed), Cam(cam_d)
+        pkg = renderer.render(cam, pc, Pipe(), bg) if name == "fused" else reference_composition(cam, pc, bg)
+        ((pkg["render"] * dc).sum() + (pkg["depth"] * dd).sum()).backward()
+        torch.cuda.synchronize()
+        rec = {k: pkg[k].detach().cpu().numpy() for k in ("render", "depth", "opacity", "radii", "n_touched")}
+        rec.update({"g_" + k: v.grad.cpu().numpy() for k, v in pc.leaves().items() if v.grad is not None})
+        rec["g_means2D"] = pkg["viewspace_points"].grad.cpu().numpy()
+        rec["g_tau"] = np.concatenate([cam.cam_trans_delta.grad.cpu().numpy().ravel(), cam.cam_rot_delta.grad.cpu().numpy().ravel()])
+        out[name] = rec
+    f, r = out["fused"], out["ref"]
+    if name == "fused":
+        assert set(pkg) == {"render", "viewspace_points", "visibility_filter", "radii", "depth", "opacity", "n_touched"}
+    # activations and matrices are evaluated in a different (fused) order: radii may flip on a handful of
+    # Gaussians sitting on a ceil() boundary; images within 1e-4 of the image scale otherwise
+    assert (f["radii"] != r["radii"]).mean() < 2e-4
+    same = f["radii"] == r["radii"]
+    # Compositing is discontinuous at its alpha >= 1/255 test: an input perturbation of 1 ulp flips the
+    # decision for a few (pixel, Gaussian) pairs, each worth <= 1/255 of the pixel scale.  So: all but
+    # 1e-4 of the pixels within 2e-4 of the image scale, and no pixel off by more than two such flips.
+    for k in ("render", "depth", "opacity"):
+        scale = max(1.0, np.abs(r[k]).max())
+        err = np.abs(f[k] - r[k])
+        assert (err > 2e-4 * scale + 1e-3 * np.abs(r[k])).mean() < 1e-4, (k, err.max())
+        assert err.max() < 2.0 / 255.0 * scale, (k, err.max())
+    assert (f["n_touched"][same] != r["n_touched"][same]).mean() < 1e-3
+    for k in ("g_xyz", "g_f_dc", "g_opacity", "g_scaling", "g_rotation", "g_means2D", "g_tau") + (("g_f_rest",) if deg else ()):
+        # same tolerance as the rasterizer's own gradient parity, except on the Gaussians touched by a flip
+        a, b = np.asarray(f[k], np.float64), np.asarray(r[k], np.float64)
+        assert a.shape == b.shape, k
+        scale = np.abs(b).max()
+        err = np.abs(a - b)
+        bad = err > 2e-3 * np.abs(b) + 2e-4 * scale
+        assert bad.mean() < (5e-4 if a.size > 100 else 1e-9), (k, bad.sum(), a.size, err.max(), scale)
+        assert err.max() < 5e-2 * scale, (k, err.max(), scale)
+
+
+def test_unfused_branches_run():
+    W, H, P = 96, 64, 3000
+    cam_d = scenes.make_camera(W, H, 5)
+    g = scenes.make_gaussians(P, W, H, 0, 5, cam_d)
+    pc, cam = Model(g, 5), Cam(cam_d)
+    bg = torch.zeros(3, device=DEV)
+    full = renderer.render(cam, pc, Pipe(), bg)
+    mask = torch.ones(P, dtype=torch.bool, device=DEV)
+    masked = renderer.render(cam, pc, Pipe(), bg, mask=mask)
+    torch.testing.assert_close(masked["render"], full["render"], rtol=1e-3, atol=2e-4)
+    col = torch.rand(P, 3, device=DEV)
+    over = renderer.render(cam, pc, Pipe(), bg, override_color=col)
+    assert over["render"].shape == (3, H, W)
+    empty = Model(g, 5)
+    empty._xyz = torch.zeros(0, 3, device=DEV)
+    assert renderer.render(cam, empty, Pipe(), bg) is None

@@ -5,7 +5,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libwgs_rasterizer.so")
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 WGS_OK = 0
 WGS_ERR_INVALID_ARGUMENT = -1
@@ -32,6 +32,7 @@ class ForwardArgs(C.Structure):
         ("out_color", _fp), ("out_depth", _fp), ("out_opacity", _fp), ("radii", _fp), ("n_touched", _fp),
         ("geom", _fp), ("tile", _fp), ("binning", _fp), ("image", _fp),
         ("capacity", C.c_int64), ("tile_row_begin", C.c_int32), ("tile_row_end", C.c_int32),
+        ("activations", C.c_int32), ("sh_rest", _fp),
     ]
 
 
@@ -48,12 +49,13 @@ class BackwardArgs(C.Structure):
         ("dL_dscales", _fp), ("dL_drotations", _fp), ("dL_dcov3D", _fp), ("dL_dtau", _fp),
         ("geom", _fp), ("tile", _fp), ("binning", _fp), ("image", _fp), ("grad", _fp),
         ("capacity", C.c_int64), ("tile_row_begin", C.c_int32), ("tile_row_end", C.c_int32),
+        ("activations", C.c_int32), ("sh_rest", _fp), ("dL_dsh_rest", _fp),
     ]
 
 
 EXPORTS = ("wgs_abi_version", "wgs_last_error", "wgs_context_create", "wgs_context_destroy",
            "wgs_workspace_sizes", "wgs_forward", "wgs_backward", "wgs_mark_visible", "wgs_export_binning",
-           "wgs_export_geometry", "wgs_stage_timing", "wgs_stage_times")
+           "wgs_export_geometry", "wgs_stage_timing", "wgs_stage_times", "wgs_camera_matrices")
 NUM_STAGES = 8
 STAGE_NAMES = ("preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd", "render_bwd", "preprocess_bwd",
                "reserved")
@@ -83,6 +85,7 @@ def load():
     lib.wgs_mark_visible.argtypes = [C.c_int32, _fp, _fp, _fp, _fp, C.c_void_p]
     lib.wgs_export_binning.argtypes = [C.POINTER(ForwardArgs), C.c_int64, _fp, _fp, _fp, _fp, _fp, C.c_void_p]
     lib.wgs_export_geometry.argtypes = [C.POINTER(ForwardArgs), _fp, _fp, _fp, _fp, _fp, C.c_void_p]
+    lib.wgs_camera_matrices.argtypes = [_fp, _fp, _fp, _fp, _fp, _fp, C.c_void_p]
     lib.wgs_stage_timing.argtypes = [C.c_void_p, C.c_int]
     lib.wgs_stage_times.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     if lib.wgs_abi_version() != ABI_VERSION:

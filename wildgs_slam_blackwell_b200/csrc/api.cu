@@ -176,6 +176,7 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     pp.opacities = a->opacities; pp.scales = a->scales; pp.rotations = a->rotations; pp.cov3D_precomp = a->cov3D_precomp;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.campos = a->campos;
     pp.radii = a->radii; pp.n_touched = a->n_touched; pp.geom = geom; pp.tile = tile;
+    pp.act = a->activations; pp.sh_rest = a->colors_precomp ? nullptr : a->sh_rest;
     MARK(ctx, 0, s);
     launch_preprocess_fwd(pp, s);
     STAGE(a->debug, s, "preprocess_fwd");
@@ -274,6 +275,11 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     pb.dL_dmeans3D = a->dL_dmeans3D; pb.dL_dmeans2D = a->dL_dmeans2D; pb.dL_dsh = a->dL_dsh;
     pb.dL_dcolors = a->dL_dcolors; pb.dL_dopacity = a->dL_dopacity; pb.dL_dscales = a->dL_dscales;
     pb.dL_drotations = a->dL_drotations; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dtau = a->dL_dtau;
+    pb.act = a->activations; pb.sh_rest = use_sh ? a->sh_rest : nullptr; pb.dL_dsh_rest = a->dL_dsh_rest;
+    if (pb.sh_rest && pb.dL_dsh && !pb.dL_dsh_rest && a->M > 1) {
+        set_err("wgs_backward: sh_rest given without dL_dsh_rest", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
     launch_preprocess_bwd(pb, s);
     STAGE(a->debug, s, "preprocess_bwd");
     MARK(ctx, 8, s);

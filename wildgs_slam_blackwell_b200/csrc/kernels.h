@@ -8,6 +8,8 @@ namespace wgs {
 struct PreFwdParams {
     int P, D, M, W, H, gx, gy, prefiltered, copies;
     int row0, row1;  // tile-row strip to bin (whole image: 0, gy)
+    int act;         // raw-parameter mode: sigmoid / exp / normalize applied here
+    const float* sh_rest;  // non-null: sh = (P,1,3) DC, sh_rest = (P,M-1,3)
     float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
     const float *means3D, *sh, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
     const float *viewmatrix, *projmatrix, *campos;
@@ -52,6 +54,9 @@ struct RenderBwdParams {
 
 struct PreBwdParams {
     int P, D, M, W, H, accumulate;
+    int act;
+    const float* sh_rest;
+    float* dL_dsh_rest;
     float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
     const float *means3D, *sh, *colors_precomp, *scales, *rotations, *cov3D_precomp;
     const float *viewmatrix, *projmatrix, *projmatrix_raw, *campos;

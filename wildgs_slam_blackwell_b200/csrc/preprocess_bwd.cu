@@ -70,6 +70,15 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
 #pragma unroll
             for (int k = 0; k < 4; k++) q4[k] = __ldg(p.rotations + 4 * idx + k);
         }
+        // raw-parameter mode: the forward applied exp / normalize (preprocess_fwd.cu); redo them here
+        float qn = 1.f;
+        if (p.act && !p.cov3D_precomp) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) s3[k] = expf(s3[k]);
+            qn = fmaxf(sqrtf(q4[0] * q4[0] + q4[1] * q4[1] + q4[2] * q4[2] + q4[3] * q4[3]), 1e-12f);
+#pragma unroll
+            for (int k = 0; k < 4; k++) q4[k] = q4[k] / qn;
+        }
         const uint2 rect = __ldg(p.geom.rect + idx);
         const float4 ra = __ldcg(p.geom.rec + 2 * idx), rb = __ldcg(p.geom.rec + 2 * idx + 1);
         const bool vis = rad > 0 && rect.x != rect.y;  // rect is empty outside the rendered strip
@@ -87,7 +96,8 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
         const float dm2x = -0.5f * p.W * o * (kx * g0.y + ky * g0.z);   // dL/dmean2D (NDC-scaled)
         const float dm2y = -0.5f * p.H * o * (ky * g0.y + kz * g0.z);
         const float dcx = -0.5f * o * g0.w, dcy = -0.5f * o * g1.x, dcz = -0.5f * o * g1.y;  // dL/dconic (x, y, w)
-        const float dop = g0.x;
+        // dL/dopacity = S w; raw-parameter mode: through the sigmoid, d sigmoid = o (1 - o)
+        const float dop = p.act ? g0.x * o * (1.f - o) : g0.x;
         const float dcol[3] = {g1.z, g1.w, g2.x};
         const float ddepth = g2.y;
         V3 dmean = {0.f, 0.f, 0.f};
@@ -190,16 +200,22 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
             }
             // ---- SH backward (:21-145) ----
             if (p.sh) {
-                const float* __restrict__ sh = p.sh + (size_t)idx * p.M * 3;
-                float* __restrict__ dsh = p.dL_dsh + (size_t)idx * p.M * 3;
+                // packed (P,M,3) layout, or DC / rest split (raw-parameter mode): coefficient k >= 1 lives at shr + 3(k-1)
+                const float* __restrict__ sh0 = p.sh_rest ? p.sh + (size_t)idx * 3 : p.sh + (size_t)idx * p.M * 3;
+                const float* __restrict__ shr = p.sh_rest ? p.sh_rest + (size_t)idx * (p.M - 1) * 3 : sh0 + 3;
+                float* __restrict__ dsh0 = p.sh_rest ? p.dL_dsh + (size_t)idx * 3 : p.dL_dsh + (size_t)idx * p.M * 3;
+                float* __restrict__ dshr = p.sh_rest ? p.dL_dsh_rest + (size_t)idx * (p.M - 1) * 3 : dsh0 + 3;
                 const uint8_t cb = p.geom.clamped[idx];
                 const V3 dRGB = {(cb & 1) ? 0.f : dcol[0], (cb & 2) ? 0.f : dcol[1], (cb & 4) ? 0.f : dcol[2]};
                 const V3 dir_orig = {m.x - __ldg(p.campos), m.y - __ldg(p.campos + 1), m.z - __ldg(p.campos + 2)};
                 const float il = 1.f / sqrtf(dot(dir_orig, dir_orig));
                 const float x = dir_orig.x * il, y = dir_orig.y * il, z = dir_orig.z * il;
-                auto SH = [&](int k) { return V3{__ldg(sh + 3 * k), __ldg(sh + 3 * k + 1), __ldg(sh + 3 * k + 2)}; };
+                auto SH = [&](int k) {  // only called with k >= 1
+                    return V3{__ldg(shr + 3 * (k - 1)), __ldg(shr + 3 * (k - 1) + 1), __ldg(shr + 3 * (k - 1) + 2)};
+                };
                 auto put = [&](int k, float w) {
-                    gput(dsh, 3 * k, w * dRGB.x, accm); gput(dsh, 3 * k + 1, w * dRGB.y, accm); gput(dsh, 3 * k + 2, w * dRGB.z, accm);
+                    float* d = k ? dshr + 3 * (k - 1) : dsh0;
+                    gput(d, 0, w * dRGB.x, accm); gput(d, 1, w * dRGB.y, accm); gput(d, 2, w * dRGB.z, accm);
                 };
                 V3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
                 put(0, kSH_C0);
@@ -283,10 +299,24 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(con
                           4 * z * (DMT(1, 1) + DMT(0, 0));
 #undef DMT
             }
-        } else if (p.sh && p.dL_dsh) {
-            float* __restrict__ dsh = p.dL_dsh + (size_t)idx * p.M * 3;
-            if (!accm)
+        } else if (p.sh && p.dL_dsh && !accm) {
+            if (p.sh_rest) {
+                float* __restrict__ d0 = p.dL_dsh + (size_t)idx * 3;
+                float* __restrict__ dr = p.dL_dsh_rest + (size_t)idx * (p.M - 1) * 3;
+                d0[0] = d0[1] = d0[2] = 0.f;
+                for (int k = 0; k < 3 * (p.M - 1); k++) dr[k] = 0.f;
+            } else {
+                float* __restrict__ dsh = p.dL_dsh + (size_t)idx * p.M * 3;
                 for (int k = 0; k < 3 * p.M; k++) dsh[k] = 0.f;
+            }
+        }
+        if (p.act && vis && !p.cov3D_precomp) {
+            // chain through exp (d exp = s) and normalize (d q_hat = (I - q_hat q_hat^T) / |q|)
+#pragma unroll
+            for (int k = 0; k < 3; k++) dscale[k] *= s3[k];
+            const float qd = q4[0] * drot[0] + q4[1] * drot[1] + q4[2] * drot[2] + q4[3] * drot[3];
+#pragma unroll
+            for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q4[k] * qd) / qn;
         }
         if (p.dL_dmeans3D) { gput(p.dL_dmeans3D, 3 * idx, dmean.x, accm); gput(p.dL_dmeans3D, 3 * idx + 1, dmean.y, accm); gput(p.dL_dmeans3D, 3 * idx + 2, dmean.z, accm); }
         if (p.dL_dmeans2D) { gput(p.dL_dmeans2D, 3 * idx, dm2x, accm); gput(p.dL_dmeans2D, 3 * idx + 1, dm2y, accm); gput(p.dL_dmeans2D, 3 * idx + 2, 0.f, accm); }

@@ -11,12 +11,19 @@ namespace wgs {
 
 __device__ __forceinline__ void cov3d_from_scale_rot(const float* __restrict__ scales,
                                                      const float* __restrict__ rots, int idx, float mod,
-                                                     float c[6]) {
+                                                     bool act, float c[6]) {
     // reference computeCov3D (forward.cu:120-154); quaternion (r,x,y,z) is NOT normalised
-    const float sx = MUL(mod, __ldg(scales + 3 * idx)), sy = MUL(mod, __ldg(scales + 3 * idx + 1)),
-                sz = MUL(mod, __ldg(scales + 3 * idx + 2));
-    const float r = __ldg(rots + 4 * idx), x = __ldg(rots + 4 * idx + 1), y = __ldg(rots + 4 * idx + 2),
-                z = __ldg(rots + 4 * idx + 3);
+    float s0 = __ldg(scales + 3 * idx), s1 = __ldg(scales + 3 * idx + 1), s2 = __ldg(scales + 3 * idx + 2);
+    float r = __ldg(rots + 4 * idx), x = __ldg(rots + 4 * idx + 1), y = __ldg(rots + 4 * idx + 2),
+          z = __ldg(rots + 4 * idx + 3);
+    if (act) {
+        // raw-parameter mode: GaussianModel.get_scaling = exp(_scaling), get_rotation =
+        // F.normalize(_rotation) = q / max(|q|, 1e-12)  (gaussian_model.py:54-63,77-83)
+        s0 = expf(s0); s1 = expf(s1); s2 = expf(s2);
+        const float n = fmaxf(SQRT(ADD(ADD(ADD(MUL(r, r), MUL(x, x)), MUL(y, y)), MUL(z, z))), 1e-12f);
+        r = DIV(r, n); x = DIV(x, n); y = DIV(y, n); z = DIV(z, n);
+    }
+    const float sx = MUL(mod, s0), sy = MUL(mod, s1), sz = MUL(mod, s2);
     // ptxas fuses the second product of each 2-term sum into an FFMA (SASS-verified)
     const float yy = MUL(y, y), zz = MUL(z, z), xz = MUL(x, z), rx = MUL(r, x), rz = MUL(r, z);
     const float yy_zz = ADD(yy, zz), xx_zz = FMA(x, x, zz), xx_yy = FMA(x, x, yy);
@@ -39,8 +46,10 @@ __device__ __forceinline__ void cov3d_from_scale_rot(const float* __restrict__ s
 }
 
 // reference computeColorFromSH (forward.cu:22-73); returns rgb, sets clamp bits
-__device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, int deg, float px, float py,
-                                            float pz, const float* __restrict__ campos, uint32_t& clampbits) {
+// sh: coefficient 0 (DC); shr: coefficients 1.. (shr = sh + 3 for the packed (P,M,3) layout)
+__device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, const float* __restrict__ shr, int deg,
+                                            float px, float py, float pz, const float* __restrict__ campos,
+                                            uint32_t& clampbits) {
     const float dx = SUB(px, __ldg(campos)), dy = SUB(py, __ldg(campos + 1)), dz = SUB(pz, __ldg(campos + 2));
     const float len = SQRT(FMA(dz, dz, FMA(dx, dx, MUL(dy, dy))));
     const float x = DIV(dx, len), y = DIV(dy, len), z = DIV(dz, len);
@@ -51,9 +60,9 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, int de
         const float t1 = MUL(y, kSH_C1), t2 = MUL(z, kSH_C1), t3 = MUL(x, kSH_C1);
 #pragma unroll
         for (int c = 0; c < 3; c++) {
-            float v = FMA(-t1, __ldg(sh + 3 + c), res[c]);
-            v = FMA(t2, __ldg(sh + 6 + c), v);
-            res[c] = FMA(-t3, __ldg(sh + 9 + c), v);
+            float v = FMA(-t1, __ldg(shr + c), res[c]);
+            v = FMA(t2, __ldg(shr + 3 + c), v);
+            res[c] = FMA(-t3, __ldg(shr + 6 + c), v);
         }
         if (deg > 1) {
             const float xx = MUL(x, x), yy = MUL(y, y), zz = MUL(z, z), xy = MUL(x, y), yz = MUL(y, z),
@@ -64,11 +73,11 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, int de
                         b8 = MUL(xx_yy, kSH_C2[4]);
 #pragma unroll
             for (int c = 0; c < 3; c++) {
-                float v = FMA(b4, __ldg(sh + 12 + c), res[c]);
-                v = FMA(b5, __ldg(sh + 15 + c), v);
-                v = FMA(b6, __ldg(sh + 18 + c), v);
-                v = FMA(b7, __ldg(sh + 21 + c), v);
-                res[c] = FMA(b8, __ldg(sh + 24 + c), v);
+                float v = FMA(b4, __ldg(shr + 9 + c), res[c]);
+                v = FMA(b5, __ldg(shr + 12 + c), v);
+                v = FMA(b6, __ldg(shr + 15 + c), v);
+                v = FMA(b7, __ldg(shr + 18 + c), v);
+                res[c] = FMA(b8, __ldg(shr + 21 + c), v);
             }
             if (deg > 2) {
                 const float w = SUB(FMA(zz, 4.f, -xx), yy);
@@ -81,13 +90,13 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, int de
                 const float b15 = MUL(MUL(x, kSH_C3[6]), FMA(yy, -3.f, xx));
 #pragma unroll
                 for (int c = 0; c < 3; c++) {
-                    float v = FMA(b9, __ldg(sh + 27 + c), res[c]);
-                    v = FMA(b10, __ldg(sh + 30 + c), v);
-                    v = FMA(b11, __ldg(sh + 33 + c), v);
-                    v = FMA(b12, __ldg(sh + 36 + c), v);
-                    v = FMA(b13, __ldg(sh + 39 + c), v);
-                    v = FMA(b14, __ldg(sh + 42 + c), v);
-                    res[c] = FMA(b15, __ldg(sh + 45 + c), v);
+                    float v = FMA(b9, __ldg(shr + 24 + c), res[c]);
+                    v = FMA(b10, __ldg(shr + 27 + c), v);
+                    v = FMA(b11, __ldg(shr + 30 + c), v);
+                    v = FMA(b12, __ldg(shr + 33 + c), v);
+                    v = FMA(b13, __ldg(shr + 36 + c), v);
+                    v = FMA(b14, __ldg(shr + 39 + c), v);
+                    res[c] = FMA(b15, __ldg(shr + 42 + c), v);
                 }
             }
         }
@@ -127,7 +136,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
 #pragma unroll
                 for (int k = 0; k < 6; k++) c[k] = __ldg(p.cov3D_precomp + 6 * idx + k);
             } else {
-                cov3d_from_scale_rot(p.scales, p.rotations, idx, p.scale_modifier, c);
+                cov3d_from_scale_rot(p.scales, p.rotations, idx, p.scale_modifier, p.act != 0, c);
             }
             // computeCov2D (forward.cu:76-115)
             const float tx = dot3p(px, py, pz, V[0], V[4], V[8], V[12]);
@@ -177,9 +186,12 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
                 rgb = make_float3(__ldg(p.colors_precomp + 3 * idx), __ldg(p.colors_precomp + 3 * idx + 1),
                                   __ldg(p.colors_precomp + 3 * idx + 2));
             } else {
-                rgb = sh_to_rgb(p.sh + (size_t)idx * p.M * 3, p.D, px, py, pz, p.campos, cb);
+                const float* sh0 = p.sh_rest ? p.sh + (size_t)idx * 3 : p.sh + (size_t)idx * p.M * 3;
+                const float* shr = p.sh_rest ? p.sh_rest + (size_t)idx * (p.M - 1) * 3 : sh0 + 3;
+                rgb = sh_to_rgb(sh0, shr, p.D, px, py, pz, p.campos, cb);
             }
-            const float o = __ldg(p.opacities + idx);
+            float o = __ldg(p.opacities + idx);
+            if (p.act) o = DIV(1.f, ADD(1.f, expf(-o)));  // torch.sigmoid (gaussian_model.py:59,95-97)
             p.geom.rec[2 * idx] = make_float4(mx, my, cnx, cny);
             p.geom.rec[2 * idx + 1] = make_float4(cnz, o, depth, logf(255.f * o));
             p.geom.col[idx] = make_float4(rgb.x, rgb.y, rgb.z, 0.f);

@@ -78,8 +78,10 @@ class ForwardState:
     __slots__ = ("args", "geom", "tile", "binning", "image", "num_rendered", "keep")
 
 
-def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, s):
-    """Runs the forward through the C ABI.  Returns (color, radii, depth, opacity, n_touched, state)."""
+def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, s, sh_rest=None,
+                activations=False):
+    """Runs the forward through the C ABI.  Returns (color, radii, depth, opacity, n_touched, state).
+    sh_rest / activations: raw-parameter mode (WgsForwardArgs::activations, ::sh_rest)."""
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     if not means3D.is_cuda:
@@ -103,6 +105,11 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
         proj = _f32c(s.projmatrix, device)
         campos = _f32c(s.campos, device)
         M = int(sh.shape[1]) if (sh is not None and sh.numel() != 0) else 0
+        sh_rest = _f32c(sh_rest, device)
+        if sh_rest is not None and M:
+            if sh.shape[1] != 1:
+                raise RuntimeError("with sh_rest, sh must be the (P,1,3) DC coefficients")
+            M = 1 + int(sh_rest.shape[1])
 
         strip = tile_rows._active
         new_img = torch.zeros if strip is not None else torch.empty   # outside a strip nothing is written
@@ -128,6 +135,7 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
             if not (0 <= strip.begin < strip.end <= (H + 15) // 16):
                 raise RuntimeError(f"tile_rows({strip.begin}, {strip.end}) outside the {(H + 15) // 16} tile rows")
             a.tile_row_begin, a.tile_row_end = strip.begin, strip.end
+        a.activations, a.sh_rest = int(bool(activations)), (_ptr(sh_rest) if M > 1 else None)
         R = C.c_int64(0)
         stream = _stream_ptr(device)
         while True:
@@ -154,7 +162,8 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
         # outputs are deliberately not held: under autograd they carry grad_fn -> ctx -> state, and
         # holding them here would close a reference cycle that only the cyclic GC frees (workspaces
         # would pile up and every forward would hit cudaMalloc).
-        st.keep = (bg, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, view, proj, campos)
+        st.keep = (bg, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, view, proj, campos,
+                   sh_rest)
     return color, radii, depth, opacity, n_touched, st
 
 
@@ -247,7 +256,9 @@ def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_p
         # dL_dmeans2D only feeds densification statistics; in accumulate mode it is skipped (null)
         if sink is None or not sink.accumulate or "means2D" in sink.buffers:
             g["means2D"] = e("means2D", P, 3)
-        g["sh"] = e("sh", P, M, 3) if use_sh else None
+        split = bool(fa.sh_rest)
+        g["sh"] = e("sh", P, 1 if split else M, 3) if use_sh else None
+        g["sh_rest"] = e("sh_rest", P, M - 1, 3) if (use_sh and split) else None
         g["colors"] = e("colors", P, 3) if fa.colors_precomp else None
         g["scales"] = e("scales", P, 3) if not fa.cov3D_precomp else None
         g["rotations"] = e("rotations", P, 4) if not fa.cov3D_precomp else None
@@ -268,6 +279,7 @@ def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_p
         b.geom, b.tile, b.binning, b.image = fa.geom, fa.tile, fa.binning, fa.image
         b.capacity = fa.capacity
         b.tile_row_begin, b.tile_row_end = fa.tile_row_begin, fa.tile_row_end
+        b.activations, b.sh_rest, b.dL_dsh_rest = fa.activations, fa.sh_rest, _ptr(g["sh_rest"])
         if P > 0:
             b.grad = _grad_workspace(device, P).data_ptr()
         rc = lib.wgs_backward(ctx, C.byref(b), _stream_ptr(device))
@@ -341,6 +353,63 @@ class _RasterizeGaussians(torch.autograd.Function):
                 g[k] = None
         return (g["means3D"], g["means2D"], g["sh"], g["colors"], g["opacity"], g["scales"], g["rotations"],
                 g["cov3D"], grad_theta, grad_rho, None)
+
+
+class _RasterizeGaussianModel(torch.autograd.Function):
+    """Raw-parameter mode: takes GaussianModel's leaf tensors (_xyz, _features_dc,
+    _features_rest, _opacity, _scaling, _rotation) and applies sigmoid / exp / normalize and the dc|rest
+    concatenation inside the per-Gaussian kernels, forward and backward.  Replaces the torch kernels the
+    reference's render() launches around every rasterizer call
+    (thirdparty/gaussian_splatting/gaussian_renderer/__init__.py:77-110 via gaussian_model.py:77-97)."""
+
+    @staticmethod
+    def forward(ctx, xyz, means2D, f_dc, f_rest, opacity_raw, scaling_raw, rotation_raw, theta, rho, raster_settings):
+        empty = torch.Tensor([])
+        color, radii, depth, opacity, n_touched, st = forward_raw(xyz, f_dc, empty, opacity_raw, scaling_raw,
+                                                                  rotation_raw, empty, raster_settings,
+                                                                  sh_rest=f_rest, activations=True)
+        ctx.raster_settings = raster_settings
+        ctx.set_materialize_grads(False)
+        ctx.pose_shapes = (theta.shape, rho.shape)
+        ctx.state = st
+        ctx.save_for_backward(xyz, scaling_raw, rotation_raw, radii, f_dc)
+        ctx.mark_non_differentiable(radii, n_touched)
+        return color, radii, depth, opacity, n_touched
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_radii, grad_out_depth, grad_out_opacity, grad_n_touched):
+        s = ctx.raster_settings
+        xyz, scaling_raw, rotation_raw, radii, f_dc = ctx.saved_tensors
+        if grad_out_color is None:
+            grad_out_color = torch.zeros((3, s.image_height, s.image_width), device=xyz.device)
+        if grad_out_depth is None:
+            grad_out_depth = torch.zeros((1, s.image_height, s.image_width), device=xyz.device)
+        sink = grad_sink._active
+        empty = torch.Tensor([])
+        g = backward_raw(ctx.state, s, xyz, f_dc, empty, scaling_raw, rotation_raw, empty, radii, grad_out_color,
+                         grad_out_depth, sink)
+        th_shape, rho_shape = ctx.pose_shapes
+        grad_rho = g["tau"][:3].view(rho_shape if len(rho_shape) and rho_shape.numel() == 3 else (1, 3))
+        grad_theta = g["tau"][3:].view(th_shape if len(th_shape) and th_shape.numel() == 3 else (1, 3))
+        if sink is not None:
+            for k in sink.buffers:
+                g[k] = None
+        return (g["means3D"], g["means2D"], g["sh"], g["sh_rest"], g["opacity"], g["scales"], g["rotations"],
+                grad_theta, grad_rho, None)
+
+
+def rasterize_gaussian_model(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
+                             theta, rho, raster_settings):
+    """Same outputs as rasterize_gaussians(get_xyz, means2D, get_features, [], get_opacity, get_scaling,
+    get_rotation, [], theta, rho, settings) of the reference, from the RAW GaussianModel parameters."""
+    if theta is None:
+        theta = torch.Tensor([])
+    if rho is None:
+        rho = torch.Tensor([])
+    if features_rest is None:
+        features_rest = torch.Tensor([])
+    return _RasterizeGaussianModel.apply(xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw,
+                                         rotation_raw, theta, rho, raster_settings)
 
 
 class GaussianRasterizer(nn.Module):
