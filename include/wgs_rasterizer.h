@@ -177,6 +177,16 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* args, void* cuda_stream,
 
 int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* args, void* cuda_stream);
 
+/* No-wait operation.  The reference blocks the host once per forward on a D2H copy of R
+ * (rasterizer_impl.cu:283-284); wgs_forward waits on a 4-byte pinned word instead.  When the stream is
+ * being captured into a CUDA graph, or after wgs_set_async(ctx, 1), wgs_forward does not wait at all:
+ * *num_rendered is -1, kernels whose instance count exceeds `capacity` exit without touching memory
+ * (outputs are then undefined), and the caller checks wgs_last_num_rendered() after synchronising the
+ * stream (or after a graph replay): it returns WGS_ERR_CAPACITY if the most recent forward on this
+ * context overflowed, with the needed size in *num_rendered. */
+int wgs_set_async(WgsContext* ctx, int enable);
+int wgs_last_num_rendered(WgsContext* ctx, int64_t* num_rendered, int64_t* capacity);
+
 /* Replaces markVisible (RAST/rasterize_points.cu:213-232, rasterizer_impl.cu:54-66,141-153):
  * present[i] = view-space z > 0.2.  `present` is (P,) bytes (torch.bool). */
 int wgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

@@ -4,6 +4,7 @@ the loop body of Mapper.refine_pose_non_key_frame (src/mapper.py:886-904), in th
   composition : the reference's wrapper arrangement (torch activations, torch camera properties, torch loss
                 expression + autograd) on OUR rasterizer
   fused       : renderer.render (raw-parameter mode + camera kernel) + fused loss kernel
+  fused_graph : the fused iteration captured once into a CUDA graph and replayed (graph.CapturedIteration)
   reference   : the composition on the UNMODIFIED reference rasterizer (oracle/_ref), when built
 Prints one JSON line (ms per iteration, CUDA events, L2 flushed between iterations)."""
 import json
@@ -99,6 +100,11 @@ def main():
             l.backward()
 
         res[arm] = round(timeit(step, flush), 4)
+        if arm == "fused":
+            from wildgs_slam_blackwell_b200 import graph
+            it = graph.CapturedIteration(step, DEV)
+            res["fused_graph"] = round(timeit(it.replay, flush), 4)
+            it.check()
     print(json.dumps({"what": "tracking iteration (render + tracking loss + backward), config2, ms per iteration (median)",
                       **res}))
 

@@ -177,3 +177,67 @@ def test_unfused_branches_run():
     empty = Model(g, 5)
     empty._xyz = torch.zeros(0, 3, device=DEV)
     assert renderer.render(cam, empty, Pipe(), bg) is None
+
+
+def test_captured_iteration_matches_eager_and_follows_updates():
+    """The tracking loop body as one CUDA graph: same loss and gradients as the eager iteration, and in-place
+    updates of the pose deltas / exposure between replays are picked up."""
+    from wildgs_slam_blackwell_b200 import graph, loss as fused_loss
+    W, H, P = 160, 112, 6000
+    cam_d = scenes.make_camera(W, H, 21)
+    g = scenes.make_gaussians(P, W, H, 0, 21, cam_d)
+    pc, cam = Model(g, 21), Cam(cam_d)
+    rng = np.random.default_rng(0)
+    cam.original_image = torch.from_numpy(rng.uniform(0, 1, (3, H, W)).astype(np.float32)).to(DEV)
+    cam.grad_mask = torch.ones(1, H, W, dtype=torch.bool, device=DEV)
+    cam.exposure_a = torch.zeros(1, device=DEV, requires_grad=True)
+    cam.exposure_b = torch.zeros(1, device=DEV, requires_grad=True)
+    bg = torch.zeros(3, device=DEV)
+    cfg = {"Training": {"rgb_boundary_threshold": 0.01}}
+    leaves = [cam.cam_rot_delta, cam.cam_trans_delta, cam.exposure_a, cam.exposure_b, pc._xyz]
+
+    def step():
+        for t in leaves:
+            t.grad = None
+        pkg = renderer.render(cam, pc, Pipe(), bg)
+        l = fused_loss.get_loss_tracking(cfg, pkg["render"], pkg["depth"], pkg["opacity"], cam)
+        l.backward()
+        return l.detach()
+
+    def snapshot(l):
+        torch.cuda.synchronize()
+        return [l.item()] + [t.grad.clone() for t in leaves]
+
+    eager0 = snapshot(step())
+    it = graph.CapturedIteration(step, DEV)
+    cap0 = snapshot(it.replay())
+    assert abs(cap0[0] - eager0[0]) <= 1e-6 * abs(eager0[0])
+    for a, b in zip(cap0[1:], eager0[1:]):
+        util.assert_grad_close("captured", a.cpu().numpy(), b.cpu().numpy())
+    with torch.no_grad():
+        cam.exposure_b.add_(0.05)
+        pc._xyz.add_(0.01)
+    cap1 = snapshot(it.replay())
+    n = it.check()
+    assert n > 0
+    it = None
+    eager1 = snapshot(step())
+    assert abs(cap1[0] - eager1[0]) <= 1e-6 * abs(eager1[0]) and abs(cap1[0] - cap0[0]) > 1e-4
+    for a, b in zip(cap1[1:], eager1[1:]):
+        util.assert_grad_close("captured after update", a.cpu().numpy(), b.cpu().numpy())
+
+
+def test_async_forward_reports_overflow():
+    from wildgs_slam_blackwell_b200 import graph, rasterizer
+    W, H, P = 96, 64, 3000
+    cam_d = scenes.make_camera(W, H, 5)
+    g = scenes.make_gaussians(P, W, H, 0, 5, cam_d)
+    s = util.settings_from_cam(cam_d, 0, DEV)
+    args = [util.to_dev(g[k], DEV) for k in ("means3D", "sh")] + [torch.Tensor([])] + \
+           [util.to_dev(g[k], DEV) for k in ("opacities", "scales", "rotations")] + [torch.Tensor([]), s]
+    ref = rasterizer.forward_raw(*args)
+    with graph.async_forward(DEV):
+        out = rasterizer.forward_raw(*args)
+        assert out[-1].num_rendered == -1
+    assert graph.check_overflow(DEV) == ref[-1].num_rendered
+    assert torch.equal(out[0], ref[0])

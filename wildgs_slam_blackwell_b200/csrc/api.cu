@@ -19,6 +19,8 @@ struct WgsContext {
     unsigned int* dev_R = nullptr;   // device alias of host_R
     cudaEvent_t ev_R = nullptr;
     // stage timing (wgs_stage_timing): fwd boundaries 0..5, bwd boundaries 6..8
+    bool async = false;              // wgs_set_async: wgs_forward never waits for R
+    long long last_capacity = 0;     // capacity of the most recent forward (for wgs_last_num_rendered)
     bool timing = false;
     bool fwd_timed = false, bwd_timed = false;
     cudaEvent_t ev_stage[9] = {};
@@ -40,7 +42,7 @@ void set_err(const char* what, cudaError_t e) {
 // CHECK_CUDA(A, debug) of the reference (auxiliary.h:166-173)
 #define MARK(ctx, i, stream)                                       \
     do {                                                           \
-        if ((ctx)->timing) CK(cudaEventRecord((ctx)->ev_stage[i], stream)); \
+        if ((ctx)->timing && !capturing) CK(cudaEventRecord((ctx)->ev_stage[i], stream)); \
     } while (0)
 #define STAGE(debug, stream, name)                                 \
     do {                                                           \
@@ -123,6 +125,11 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     if (!ctx || !a || !num_rendered) { set_err("wgs_forward: null argument", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
     cudaStream_t s = (cudaStream_t)cuda_stream;
     *num_rendered = 0;
+    // Inside a CUDA-graph capture (or in async mode) the host must not wait on the device: R is not read
+    // back here, *num_rendered = -1, and the caller checks wgs_last_num_rendered() after a synchronisation.
+    cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
+    if (ctx && cudaStreamIsCapturing(s, &cap_status) != cudaSuccess) cap_status = cudaStreamCaptureStatusNone;
+    const bool capturing = cap_status == cudaStreamCaptureStatusActive;
     if (a->P < 0 || a->width <= 0 || a->height <= 0 || a->width > 65535 * 16 || a->height > 65535 * 16 ||
         a->sh_degree < 0 || a->sh_degree > 3) {
         set_err("wgs_forward: bad P / image size / sh_degree", cudaSuccess);
@@ -186,7 +193,9 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.copies = hist_copies((size_t)tiles); bp.capacity = a->capacity;
     bp.geom = geom; bp.tile = tile; bp.bucket = (unsigned long long*)a->binning; bp.host_R = ctx->dev_R;
     launch_tile_scan(bp, s);
-    CK(cudaEventRecord(ctx->ev_R, s));
+    const bool no_wait = capturing || ctx->async;
+    if (!no_wait) CK(cudaEventRecord(ctx->ev_R, s));
+    ctx->last_capacity = a->capacity;
     STAGE(a->debug, s, "tile_scan");
     MARK(ctx, 2, s);
     launch_scatter(bp, s);
@@ -204,7 +213,11 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     launch_render_fwd(rp, s);
     STAGE(a->debug, s, "render_fwd");
     MARK(ctx, 5, s);
-    ctx->fwd_timed = ctx->timing;
+    ctx->fwd_timed = ctx->timing && !capturing;
+    if (no_wait) {
+        *num_rendered = -1;
+        return WGS_OK;
+    }
 
     // Everything is enqueued; now wait for R only (the GPU keeps running the later stages).
     CK(cudaEventSynchronize(ctx->ev_R));
@@ -221,6 +234,9 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
 int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     if (!ctx || !a) { set_err("wgs_backward: null argument", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
     cudaStream_t s = (cudaStream_t)cuda_stream;
+    cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cap_status) != cudaSuccess) cap_status = cudaStreamCaptureStatusNone;
+    const bool capturing = cap_status == cudaStreamCaptureStatusActive;
     if (a->P < 0 || a->width <= 0 || a->height <= 0) {
         set_err("wgs_backward: bad P / image size", cudaSuccess);
         return WGS_ERR_INVALID_ARGUMENT;
@@ -283,8 +299,21 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     launch_preprocess_bwd(pb, s);
     STAGE(a->debug, s, "preprocess_bwd");
     MARK(ctx, 8, s);
-    ctx->bwd_timed = ctx->timing;
+    ctx->bwd_timed = ctx->timing && !capturing;
     return WGS_OK;
+}
+
+int wgs_set_async(WgsContext* ctx, int enable) {
+    if (!ctx) { set_err("wgs_set_async: null context", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    ctx->async = enable != 0;
+    return WGS_OK;
+}
+
+int wgs_last_num_rendered(WgsContext* ctx, int64_t* num_rendered, int64_t* capacity) {
+    if (!ctx || !num_rendered) { set_err("wgs_last_num_rendered: null argument", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    *num_rendered = (int64_t)*(volatile unsigned int*)ctx->host_R;
+    if (capacity) *capacity = ctx->last_capacity;
+    return *num_rendered > ctx->last_capacity ? WGS_ERR_CAPACITY : WGS_OK;
 }
 
 int wgs_stage_timing(WgsContext* ctx, int enable) {

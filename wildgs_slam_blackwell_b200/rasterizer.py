@@ -153,9 +153,10 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
                 continue
             _check(rc, "wgs_forward")
             break
-        old = _capacity_hint.get(key, 0)
-        if not (R.value * 1.2 <= old <= R.value * 4):
-            _capacity_hint[key] = int(R.value * 1.5)
+        if R.value >= 0:   # (-1: graph capture / async mode, R is not read back)
+            old = _capacity_hint.get(key, 0)
+            if not (R.value * 1.2 <= old <= R.value * 4):
+                _capacity_hint[key] = int(R.value * 1.5)
         st.args = a
         st.num_rendered = int(R.value)
         # Keep every INPUT the argument block points at alive as long as the state lives.  The
