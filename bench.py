@@ -118,10 +118,13 @@ def load_impl(impl):
 
 
 class _Set:
-    """One set of device-resident step inputs (+ the autograd leaves / rasterizer bound to them)."""
+    """One set of device-resident step inputs (+ the autograd leaves / rasterizer bound to them).  The
+    inputs are views into ONE flat device buffer so that a step's H2D traffic is a single copy."""
 
     def __init__(self, wl, mod, dev):
-        self.d = {k: v.to(dev) for k, v in wl.host.items()}
+        self.flat = torch.empty_like(wl.host_flat, device=dev)
+        self.flat.copy_(wl.host_flat)
+        self.d = {k: self.flat[o:o + n].view(shape) for k, (o, n, shape) in wl.layout.items()}
         self.leaves = [self.d[k].requires_grad_(True) for k in ("means3D", "sh", "opacities", "scales", "rotations")]
         self.settings = mod.GaussianRasterizationSettings(
             image_height=wl.H, image_width=wl.W, tanfovx=wl.cam["tanfovx"], tanfovy=wl.cam["tanfovy"],
@@ -146,12 +149,20 @@ class Workload:
         rng = np.random.default_rng(seed + 900 + rank)
         self.P, self.W, self.H, self.deg, self.dev, self.mod = P, W, H, deg, dev, mod
         # pinned host copies of everything a step consumes (e2e copies them every step)
-        pin = lambda a: torch.from_numpy(np.ascontiguousarray(a, np.float32)).pin_memory()
-        self.host = dict(means3D=pin(self.g["means3D"]), sh=pin(self.g["sh"]), opacities=pin(self.g["opacities"]),
-                         scales=pin(self.g["scales"]), rotations=pin(self.g["rotations"]),
-                         viewmatrix=pin(self.cam["viewmatrix"]), projmatrix=pin(self.cam["projmatrix"]),
-                         campos=pin(self.cam["campos"]),
-                         target_color=pin(rng.uniform(0, 1, (3, H, W))), target_depth=pin(rng.uniform(0.5, 6, (1, H, W))))
+        # ... packed into one pinned buffer (each array 256-B aligned): one H2D copy per step
+        arrays = dict(means3D=self.g["means3D"], sh=self.g["sh"], opacities=self.g["opacities"],
+                      scales=self.g["scales"], rotations=self.g["rotations"], viewmatrix=self.cam["viewmatrix"],
+                      projmatrix=self.cam["projmatrix"], campos=self.cam["campos"],
+                      target_color=rng.uniform(0, 1, (3, H, W)), target_depth=rng.uniform(0.5, 6, (1, H, W)))
+        self.layout, off = {}, 0
+        for k, a in arrays.items():
+            a = np.asarray(a)
+            self.layout[k] = (off, a.size, tuple(a.shape))
+            off += (a.size + 63) // 64 * 64
+        self.host_flat = torch.zeros(off, dtype=torch.float32).pin_memory()
+        for k, a in arrays.items():
+            o, n, _ = self.layout[k]
+            self.host_flat[o:o + n] = torch.from_numpy(np.ascontiguousarray(a, np.float32).reshape(-1))
         # two input sets: the e2e loop copies step i+1's inputs (copy stream) while step i computes
         self.sets = [_Set(self, mod, dev), _Set(self, mod, dev)]
         self.copy_stream = torch.cuda.Stream(device=dev)
@@ -163,7 +174,7 @@ class Workload:
         self.rho = torch.zeros(3, device=dev, requires_grad=True)
         self.dc, self.dd = torch.from_numpy(dc).to(dev), torch.from_numpy(dd).to(dev)
         self.out_host = torch.zeros(7, dtype=torch.float32).pin_memory()
-        self.h2d_bytes = sum(v.numel() * 4 for v in self.host.values())
+        self.h2d_bytes = self.host_flat.numel() * 4
         self.d2h_bytes = 7 * 4
         self.bucket_floats = sum(t.numel() for t in self.leaves)
         # multi-GPU: the backward kernel writes the Gaussian gradients straight into one flat bucket
@@ -171,6 +182,7 @@ class Workload:
         self.bucket = torch.zeros(self.bucket_floats, dtype=torch.float32, device=dev)
         self.sink = None
         self.fused_loss = None
+        self.use_graph, self.graphs = hasattr(mod, "grad_sink"), {}
         if hasattr(mod, "grad_sink"):
             from wildgs_slam_blackwell_b200.loss import photometric_loss
             self.fused_loss = photometric_loss
@@ -212,21 +224,10 @@ class Workload:
         st = self.sets[i % 2]
         with torch.cuda.stream(self.copy_stream), torch.no_grad():
             self.copy_stream.wait_event(st.compute_done)      # the step that last used this set has finished
-            for k, h in self.host.items():
-                st.d[k].copy_(h, non_blocking=True)
+            st.flat.copy_(self.host_flat, non_blocking=True)
             st.copy_done.record(self.copy_stream)
 
-    def step_e2e(self, world):
-        """Host buffers in, loss + pose gradient out.  Every step's inputs cross PCIe inside the timed
-        region; the copy for step i+1 is issued at the start of step i so that it overlaps compute."""
-        i = self.e2e_i
-        self.e2e_i += 1
-        st = self.sets[i % 2]
-        if i == 0:
-            self.prefetch(0)
-        cur = torch.cuda.current_stream()
-        cur.wait_event(st.copy_done)
-        self.prefetch(i + 1)
+    def _compute_e2e(self, st, world):
         self._zero_grads(st.leaves)
         color, radii, depth, opacity, n_touched = self._forward(st)
         if self.fused_loss is not None:
@@ -240,6 +241,28 @@ class Workload:
             self._backward(world, loss.backward)
         res = torch.cat([loss.detach().reshape(1), self.rho.grad.reshape(-1), self.theta.grad.reshape(-1)])
         self.out_host.copy_(res, non_blocking=True)
+
+    def step_e2e(self, world):
+        """Host buffers in, loss + pose gradient out.  Every step's inputs cross PCIe inside the timed
+        region; the copy for step i+1 is issued at the start of step i so that it overlaps compute."""
+        i = self.e2e_i
+        self.e2e_i += 1
+        st = self.sets[i % 2]
+        if i == 0:
+            self.prefetch(0)
+        cur = torch.cuda.current_stream()
+        cur.wait_event(st.copy_done)
+        self.prefetch(i + 1)
+        if self.use_graph and world == 1:
+            # own arm: the step's device work (forward, fused loss, backward, result gather, D2H) is captured
+            # once per input set into a CUDA graph (graph.CapturedIteration) and replayed with one launch
+            it = self.graphs.get(i % 2)
+            if it is None:
+                from wildgs_slam_blackwell_b200 import graph
+                it = self.graphs[i % 2] = graph.CapturedIteration(lambda: self._compute_e2e(st, world), self.dev)
+            it.replay()
+        else:
+            self._compute_e2e(st, world)
         st.compute_done.record(cur)
 
 
@@ -393,10 +416,21 @@ def main():
 
     e2e = None
     if not a.no_e2e:
-        e2e_ms, _ = timed_loop(lambda: wl.step_e2e(world), a.steps, a.warmup, flush, world)
+        if a.impl == "ours":
+            # no-wait forwards (wgs_set_async): the host does not block on num_rendered, so it can run ahead
+            # of the device; the instance capacity (1.5x the count of the resident loop) is checked afterwards
+            from wildgs_slam_blackwell_b200 import graph
+            with graph.async_forward(dev):
+                e2e_ms, _ = timed_loop(lambda: wl.step_e2e(world), a.steps, a.warmup, flush, world)
+            graph.check_overflow(dev)
+        else:
+            e2e_ms, _ = timed_loop(lambda: wl.step_e2e(world), a.steps, a.warmup, flush, world)
         e2e = {"value": round(frames / (e2e_ms * 1e-3), 3), "unit": "frames/s", "h2d_bytes_per_step": wl.h2d_bytes,
                "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": round(e2e_ms / a.steps, 4),
-               "pipelining": "inputs of step i+1 copied on a second stream during step i (double-buffered)",
+               "pipelining": "inputs of step i+1 copied (one packed H2D copy) on a second stream during step i "
+                              "(double-buffered)" + ("; the step's device work replayed from a CUDA graph (graph.CapturedIteration), "
+                                                     "instance-capacity overflow checked after the loop"
+                                                     if a.impl == "ours" else ""),
                "loss": "mean|color - target| + mean|depth - target|: " +
                        ("fused loss+cotangent kernel (wgs_photometric_loss)" if wl.fused_loss is not None
                         else "torch expression + autograd (what the reference's callers run)")}
