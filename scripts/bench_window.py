@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="config3")
     ap.add_argument("--no-sink", action="store_true", help="let autograd allocate/add per-view gradients")
+    ap.add_argument("--strips", action="store_true",
+                    help="sub-frame units (tile-row strips) when the window does not divide by the world size")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -70,7 +72,8 @@ def main():
         return loss, (lambda: torch.cat([vw["rho"].grad.reshape(-1), vw["theta"].grad.reshape(-1)]))
 
     def step():
-        return trainer.step(n_views, render_loss, cost_fn=lambda v: last_R.get(v, 1.0))
+        return trainer.step(n_views, render_loss, cost_fn=None if a.strips else (lambda v: last_R.get(v, 1.0)),
+                            tile_rows=(H + 15) // 16 if a.strips else None)
 
     flush = torch.zeros((512 << 20) // 4, device=dev)
     for _ in range(a.warmup):
@@ -102,7 +105,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": f"{a.workload}: {P} Gaussians, {n_views} keyframes {W}x{H}, SH degree {deg}",
                        "assignment": out["assignment"], "bucket_bytes": out["bucket_bytes"],
-                       "grad_sink": not a.no_sink, "l2": "flushed between steps"}}), flush=True)
+                       "grad_sink": not a.no_sink, "strips": a.strips, "l2": "flushed between steps"}}), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

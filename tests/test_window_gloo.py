@@ -12,7 +12,7 @@ import torch.multiprocessing as mp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from wildgs_slam_blackwell_b200.window import GradBucket, WindowTrainer, assign_views  # noqa: E402
+from wildgs_slam_blackwell_b200.window import GradBucket, WindowTrainer, assign_strips, assign_views  # noqa: E402
 
 N_VIEWS, P = 5, 37
 
@@ -40,6 +40,81 @@ def _make_render(params):
         loss = (img ** 2).mean() + (poses[v] * torch.arange(6.0) * (v + 1)).sum() * img.mean().detach()
         return loss, (lambda: poses[v].grad)
     return render_loss
+
+
+def _make_strip_render(params, rows):
+    """Stand-in for a strip render: the loss of view v is a sum over `rows` tile rows; inside
+    rasterizer.tile_rows(b, e) only rows [b, e) contribute (what the real rasterizer does per pixel)."""
+    from wildgs_slam_blackwell_b200 import rasterizer
+    poses = [torch.zeros(6, requires_grad=True) for _ in range(N_VIEWS)]
+
+    def render_loss(v):
+        act = rasterizer.tile_rows._active
+        b, e = (0, rows) if act is None else (act.begin, act.end)
+        poses[v].grad = None
+        loss = 0.0
+        for row in range(b, e):
+            w = torch.linspace(0.5, 1.5, P).view(P, 1) * (v + 1) * (row + 1)
+            img = (params["means3D"] * w).sum(1, keepdim=True) * params["opacity"] + params["sh"].view(P, 3).mean(1, keepdim=True)
+            loss = loss + (img ** 2).mean() + (poses[v] * torch.arange(6.0) * (row + 1)).sum()
+        return loss, (lambda: poses[v].grad)
+    return render_loss
+
+
+def _strip_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        params = _params()
+        tr = WindowTrainer(params)
+        out = tr.step(N_VIEWS, _make_strip_render(params, 4), tile_rows=4)     # 5 views on 2 ranks: view 2 is split
+        torch.save((rank, {k: p.grad.clone() for k, p in params.items()}, out["losses"].clone(),
+                    out["pose_grads"].clone(), out["assignment"]), os.path.join(q, f"strip{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_window_step_with_strips_world2(tmp_path):
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_strip_worker, args=(r, 2, port, str(tmp_path))) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    params = _params()
+    render = _make_strip_render(params, 4)
+    ref_l, ref_p = [], []
+    for v in range(N_VIEWS):
+        loss, pg = render(v)
+        loss.backward()
+        ref_l.append(loss.detach())
+        ref_p.append(pg().clone())
+    for r in range(2):
+        rank, g, losses, pose, plan = torch.load(tmp_path / f"strip{r}.pt")
+        for k in params:
+            torch.testing.assert_close(g[k], params[k].grad, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(losses, torch.stack(ref_l), rtol=1e-5, atol=1e-6)     # summed over a view's strips
+        torch.testing.assert_close(pose, torch.stack(ref_p), rtol=1e-5, atol=1e-6)
+        assert plan == [[(0, 0, 4), (1, 0, 4), (2, 0, 2)], [(2, 2, 4), (3, 0, 4), (4, 0, 4)]]
+
+
+def test_assign_strips_properties():
+    for costs, world, rows in [([1] * 10, 8, 30), ([3, 1, 2, 5, 1, 1, 2, 2, 4, 1], 8, 30), ([1] * 3, 2, 4), ([1, 1], 4, 30)]:
+        plan = assign_strips(costs, world, rows)
+        seen = set()
+        for units in plan:
+            for v, b, e in units:
+                assert 0 <= b < e <= rows
+                for row in range(b, e):
+                    assert (v, row) not in seen
+                    seen.add((v, row))
+        assert len(seen) == len(costs) * rows                       # every (view, row) exactly once
+        loads = [sum(costs[v] * (e - b) / rows for v, b, e in units) for units in plan]
+        assert max(loads) <= sum(costs) / world + max(costs) / rows + 1e-9     # balanced to one tile row
+    assert max(len(u) for u in assign_strips([1] * 10, 8, 30)) == 2   # config 3: at most two units per rank
 
 
 def _single_process_reference():

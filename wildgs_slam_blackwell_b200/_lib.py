@@ -56,7 +56,7 @@ class BackwardArgs(C.Structure):
 EXPORTS = ("wgs_abi_version", "wgs_last_error", "wgs_context_create", "wgs_context_destroy",
            "wgs_workspace_sizes", "wgs_forward", "wgs_backward", "wgs_mark_visible", "wgs_export_binning",
            "wgs_export_geometry", "wgs_stage_timing", "wgs_stage_times", "wgs_camera_matrices", "wgs_set_async",
-           "wgs_last_num_rendered")
+           "wgs_last_num_rendered", "wgs_peer_flags_bytes", "wgs_peer_allreduce")
 NUM_STAGES = 8
 STAGE_NAMES = ("preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd", "render_bwd", "preprocess_bwd",
                "reserved")
@@ -87,6 +87,9 @@ def load():
     lib.wgs_export_binning.argtypes = [C.POINTER(ForwardArgs), C.c_int64, _fp, _fp, _fp, _fp, _fp, C.c_void_p]
     lib.wgs_export_geometry.argtypes = [C.POINTER(ForwardArgs), _fp, _fp, _fp, _fp, _fp, C.c_void_p]
     lib.wgs_camera_matrices.argtypes = [_fp, _fp, _fp, _fp, _fp, _fp, C.c_void_p]
+    lib.wgs_peer_flags_bytes.restype = C.c_size_t
+    lib.wgs_peer_allreduce.argtypes = [C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_uint64, C.c_int32, C.c_int32,
+                                       C.c_uint64, C.c_uint32, C.c_void_p]
     lib.wgs_set_async.argtypes = [C.c_void_p, C.c_int]
     lib.wgs_last_num_rendered.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.wgs_stage_timing.argtypes = [C.c_void_p, C.c_int]

@@ -1,0 +1,132 @@
+// Gradient-bucket allreduce over NVLink peer memory (the one exchange step of the
+// mapping window).  Every rank's bucket lives in a symmetric allocation that all peers have mapped
+// (and, where the fabric offers it, in an NVSwitch multicast mapping).  One kernel per rank:
+//   block-level start barrier  (flags in peer memory; proves every peer's backward has finished)
+//   two-shot reduction of this rank's 1/world slice:
+//     NVLS path : multimem.ld_reduce (the switch adds the `world` copies) + multimem.st (the switch
+//                 broadcasts the sum into every copy)            -> ~1x bucket bytes per NVLink direction
+//     P2P path  : vector loads from every peer, fixed-order fp32 sum, vector stores to every peer
+//   block-level end barrier    (all slices of this rank's copy have been written when the kernel ends)
+// The sum of a slice is formed once and broadcast, so all ranks hold bit-identical results.
+#include "../../include/wgs_rasterizer.h"
+#include "common.cuh"
+
+namespace wgs {
+
+constexpr int PEER_MAX_WORLD = 16;
+constexpr int PEER_BLOCKS = 144;  // ~one CTA per SM: the kernel runs alone, what matters is bytes in flight on NVLink
+constexpr int PEER_THREADS = 512;
+
+struct PeerParams {
+    float* buf[PEER_MAX_WORLD];        // this rank's mapping of every rank's bucket
+    uint32_t* flags[PEER_MAX_WORLD];   // ... and of every rank's flag array [PEER_BLOCKS][PEER_MAX_WORLD]
+    float* mc;                         // multicast mapping of the bucket (null: P2P path)
+    int rank, world;
+    size_t n4;                         // float4 elements
+    uint32_t epoch;                    // odd: start barrier value; epoch + 1: end barrier value
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Block b of every rank meets block b of every other rank.  The flag values only grow, so no reset is needed.
+__device__ __forceinline__ void block_barrier(const PeerParams& p, uint32_t value) {
+    __syncthreads();
+    if ((int)threadIdx.x < p.world) {
+        const int t = threadIdx.x;
+        st_release_sys(p.flags[t] + blockIdx.x * PEER_MAX_WORLD + p.rank, value);
+        const uint32_t* mine = p.flags[p.rank] + blockIdx.x * PEER_MAX_WORLD + t;
+        while ((int32_t)(ld_acquire_sys(mine) - value) < 0) {}
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 multimem_ld_reduce(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w) : "memory");
+}
+
+template <bool NVLS>
+__global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const __grid_constant__ PeerParams p) {
+    block_barrier(p, p.epoch);
+    const size_t per = (p.n4 + p.world - 1) / p.world;
+    const size_t begin = min(p.n4, per * p.rank), end = min(p.n4, begin + per);
+    const size_t stride = (size_t)gridDim.x * PEER_THREADS;
+    constexpr int U = 4;  // independent float4 per thread and trip: keeps U (x world) 16-B requests in flight
+    for (size_t i0 = begin + (size_t)blockIdx.x * PEER_THREADS + threadIdx.x; i0 < end; i0 += U * stride) {
+        float4 s[U];
+        if (NVLS) {
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                if (i0 + u * stride < end) s[u] = multimem_ld_reduce(p.mc + 4 * (i0 + u * stride));
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                if (i0 + u * stride < end) multimem_st(p.mc + 4 * (i0 + u * stride), s[u]);
+        } else {
+#pragma unroll
+            for (int u = 0; u < U; u++) s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int r = 0; r < p.world; r++) {   // fixed order: identical bits on every run
+                float4 v[U];
+#pragma unroll
+                for (int u = 0; u < U; u++)
+                    v[u] = i0 + u * stride < end ? __ldcg(reinterpret_cast<const float4*>(p.buf[r]) + i0 + u * stride)
+                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < U; u++) { s[u].x += v[u].x; s[u].y += v[u].y; s[u].z += v[u].z; s[u].w += v[u].w; }
+            }
+            for (int r = 0; r < p.world; r++)
+#pragma unroll
+                for (int u = 0; u < U; u++)
+                    if (i0 + u * stride < end) __stcg(reinterpret_cast<float4*>(p.buf[r]) + i0 + u * stride, s[u]);
+        }
+    }
+    block_barrier(p, p.epoch + 1);
+}
+
+}  // namespace wgs
+
+extern "C" {
+void wgs_set_error_message(const char* msg);
+
+size_t wgs_peer_flags_bytes(void) { return (size_t)wgs::PEER_BLOCKS * wgs::PEER_MAX_WORLD * sizeof(uint32_t); }
+
+int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
+                       int32_t world, uint64_t n_floats, uint32_t epoch, void* cuda_stream) {
+    using namespace wgs;
+    if (!buffer_ptrs || !flag_ptrs || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world ||
+        (n_floats & 3u) || !(epoch & 1u)) {
+        wgs_set_error_message("wgs_peer_allreduce: bad world/rank, n_floats not a multiple of 4, or even epoch");
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    PeerParams p;
+    for (int r = 0; r < PEER_MAX_WORLD; r++) {
+        p.buf[r] = r < world ? (float*)buffer_ptrs[r] : nullptr;
+        p.flags[r] = r < world ? (uint32_t*)flag_ptrs[r] : nullptr;
+        if (r < world && (!p.buf[r] || !p.flags[r] || (buffer_ptrs[r] & 15u))) {
+            wgs_set_error_message("wgs_peer_allreduce: null or misaligned peer pointer");
+            return WGS_ERR_INVALID_ARGUMENT;
+        }
+    }
+    p.mc = (float*)multicast_ptr; p.rank = rank; p.world = world; p.n4 = n_floats / 4; p.epoch = epoch;
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    if (p.mc) peer_allreduce_kernel<true><<<PEER_BLOCKS, PEER_THREADS, 0, s>>>(p);
+    else peer_allreduce_kernel<false><<<PEER_BLOCKS, PEER_THREADS, 0, s>>>(p);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        wgs_set_error_message(cudaGetErrorString(e));
+        return WGS_ERR_CUDA;
+    }
+    return WGS_OK;
+}
+}

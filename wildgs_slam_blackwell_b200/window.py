@@ -32,6 +32,34 @@ def assign_views(costs: Sequence[float], world: int) -> List[List[int]]:
     return out
 
 
+def assign_strips(costs: Sequence[float], world: int, tile_rows: int) -> List[List[tuple]]:
+    """Sub-frame sharding: lay the views end to end (view v weighs costs[v], spread evenly over its
+    `tile_rows` rows of 16 pixels), cut the line into `world` pieces of equal weight at tile-row
+    granularity, and hand piece r to rank r.  Returns per rank a list of (view, row_begin, row_end);
+    every (view, row) appears exactly once, a view is split between at most two neighbouring ranks
+    whenever a rank's share is at least one view, and every rank computes the same plan.  Needed when
+    the window does not divide by the world size (10 keyframes on 8 GPUs cap at 5x with whole views,
+    SURVEY.md §8e)."""
+    world = max(int(world), 1)
+    n, rows = len(costs), int(tile_rows)
+    w = [max(float(c), 1e-9) / rows for c in costs]           # weight of one tile row of view v
+    total = sum(w[v] * rows for v in range(n))
+    out: List[List[tuple]] = [[] for _ in range(world)]
+    acc, r, begin_v, begin_row = 0.0, 0, 0, 0
+    for v in range(n):
+        begin_row = 0
+        for row in range(rows):
+            acc += w[v]
+            # close rank r's piece after this row once it has reached its share (the last rank takes the rest)
+            if r < world - 1 and acc >= total * (r + 1) / world - 1e-12 * total:
+                out[r].append((v, begin_row, row + 1))
+                begin_row = row + 1
+                r += 1
+        if begin_row < rows:
+            out[r].append((v, begin_row, rows))
+    return out
+
+
 class GradBucket:
     """One flat fp32 buffer holding the gradients of all replicated leaves back to back, plus
     per-leaf views into it.  Installing the views as `.grad` makes autograd accumulate straight into
@@ -101,9 +129,16 @@ class WindowTrainer:
         else:
             self.bucket.params = params
 
-    def step(self, n_views: int, render_loss: Callable, cost_fn: Optional[Callable[[int], float]] = None):
+    def step(self, n_views: int, render_loss: Callable, cost_fn: Optional[Callable[[int], float]] = None,
+             tile_rows: Optional[int] = None):
+        """`tile_rows` (= ceil(H/16)), when given and the window does not divide by the world size, switches to
+        sub-frame units (assign_strips): render_loss(v) is then called inside rasterizer.tile_rows(b, e) and
+        must return a loss that is a sum over pixels (images are zero outside the strip); per-view losses,
+        costs and pose gradients are summed over the strips of a view."""
         if len(self.costs) != n_views:
             self.costs = [1.0] * n_views
+        if tile_rows is not None and self.world > 1 and n_views % self.world != 0:
+            return self._step_strips(n_views, render_loss, cost_fn, int(tile_rows))
         assignment = assign_views(self.costs, self.world)
         mine = assignment[self.rank]
         b = self.bucket
@@ -137,3 +172,45 @@ class WindowTrainer:
         self.costs = [float(c) for c in side[:, 1].tolist()]
         return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": assignment,
                 "bucket_bytes": b.nbytes}
+
+    def _step_strips(self, n_views, render_loss, cost_fn, tile_rows):
+        from . import rasterizer
+        plan = assign_strips(self.costs, self.world, tile_rows)
+        mine = plan[self.rank]
+        b = self.bucket
+        use_sink = self.sink_names is not None and len(mine) > 0
+        if use_sink:
+            sink_bufs = {g: b.views[k] for k, g in self.sink_names.items()}
+            for p in b.params.values():
+                p.grad = None
+        else:
+            b.install()
+        side = torch.zeros(n_views, 8, dtype=torch.float32, device=b.flat.device)
+        for n_done, (v, r0, r1) in enumerate(mine):
+            whole = r0 == 0 and r1 == tile_rows
+            with rasterizer.tile_rows(r0, r1) if not whole else _null():
+                loss, pose_grad_fn = render_loss(v)
+                if use_sink:
+                    with rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0):
+                        loss.backward()
+                else:
+                    loss.backward()
+            side[v, 0] += loss.detach()
+            side[v, 1] += float(cost_fn(v)) if cost_fn is not None else (r1 - r0) / tile_rows
+            if pose_grad_fn is not None:
+                side[v, 2:8] += pose_grad_fn().reshape(6)
+        if use_sink:
+            b.install(zero=False)
+        work = dist.all_reduce(b.flat, group=self.group, async_op=True)
+        dist.all_reduce(side, group=self.group)
+        work.wait()
+        self.costs = [float(c) for c in side[:, 1].tolist()]
+        return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": plan, "bucket_bytes": b.nbytes}
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
