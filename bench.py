@@ -179,7 +179,17 @@ class Workload:
         self.bucket_floats = sum(t.numel() for t in self.leaves)
         # multi-GPU: the backward kernel writes the Gaussian gradients straight into one flat bucket
         # (rasterizer.grad_sink) that NCCL then sums in place -- no packing copy
-        self.bucket = torch.zeros(self.bucket_floats, dtype=torch.float32, device=dev)
+        # ... which lives in NVLink peer memory and is summed by the library's own kernel (peer.PeerBucket,
+        # csrc/peer_allreduce.cu) unless WGS_ALLREDUCE=nccl
+        self.peer = None
+        mode = os.environ.get("WGS_ALLREDUCE", "auto")
+        if hasattr(mod, "grad_sink") and dist.is_initialized() and dist.get_world_size() > 1 and mode != "nccl":
+            from wildgs_slam_blackwell_b200.peer import PeerBucket
+            w = dist.get_world_size()
+            self.peer = PeerBucket(self.bucket_floats, dev, use_multicast=(mode == "nvls" or (mode == "auto" and w >= 4)))
+            self.bucket = self.peer.flat
+        else:
+            self.bucket = torch.zeros(self.bucket_floats, dtype=torch.float32, device=dev)
         self.sink = None
         self.fused_loss = None
         self.use_graph, self.graphs = hasattr(mod, "grad_sink"), {}
@@ -196,7 +206,10 @@ class Workload:
         if world > 1 and self.sink is not None:
             with self.sink:
                 fn()
-            dist.all_reduce(self.bucket)
+            if self.peer is not None:
+                self.peer.all_reduce()
+            else:
+                dist.all_reduce(self.bucket)
         else:
             fn()
             if world > 1:
@@ -253,7 +266,7 @@ class Workload:
         cur = torch.cuda.current_stream()
         cur.wait_event(st.copy_done)
         self.prefetch(i + 1)
-        if self.use_graph and world == 1:
+        if self.use_graph and (world == 1 or self.peer is not None):
             # own arm: the step's device work (forward, fused loss, backward, result gather, D2H) is captured
             # once per input set into a CUDA graph (graph.CapturedIteration) and replayed with one launch
             it = self.graphs.get(i % 2)
@@ -452,8 +465,10 @@ def main():
             "config": {"workload": f"{a.workload}: {P} Gaussians, {W}x{H}, SH degree {deg}, fwd+bwd with rho/theta "
                                    "pose gradients, one view per GPU per step",
                        "frames_per_step": world, "l2": "flushed between steps (512 MiB write)",
-                       "sharding": "views across ranks, replicated Gaussians, NCCL allreduce of the "
-                                   f"{wl.bucket_floats * 4} B gradient bucket per step" if world > 1 else "single GPU",
+                       "sharding": "views across ranks, replicated Gaussians, " +
+                                   (("peer-memory allreduce kernel (" + ("NVLS multimem" if wl.peer.multicast else "P2P two-shot") + ")")
+                                    if wl.peer is not None else "NCCL allreduce") +
+                                   f" of the {wl.bucket_floats * 4} B gradient bucket per step" if world > 1 else "single GPU",
                        "p50_ms": round(statistics.median(per), 4), "p10_ms": round(sorted(per)[len(per) // 10], 4),
                        "p90_ms": round(sorted(per)[(len(per) * 9) // 10], 4)},
             "clocks": clocks,

@@ -227,11 +227,12 @@ int wgs_camera_matrices(const float* R, const float* T, const float* projection_
  * NVLink/NVSwitch domain, through peer-mapped memory instead of ncclAllReduce.  buffer_ptrs[r] / flag_ptrs[r]
  * (host arrays of `world` device addresses) are THIS rank's mappings of rank r's bucket and flag array
  * (wgs_peer_flags_bytes() bytes, zeroed once); multicast_ptr is the NVSwitch multicast mapping of the bucket
- * or 0 (then plain peer loads/stores are used).  n_floats must be a multiple of 4; `epoch` must be odd and
- * grow by 2 per call on all ranks.  Every rank enqueues the same call; results are bit-identical on all ranks. */
+ * or 0 (then plain peer loads/stores are used).  n_floats must be a multiple of 4.  Every rank enqueues the
+ * same sequence of calls (the barrier generation is kept on the device, so the launch can be captured into a
+ * CUDA graph); results are bit-identical on all ranks. */
 size_t wgs_peer_flags_bytes(void);
 int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
-                       int32_t world, uint64_t n_floats, uint32_t epoch, void* cuda_stream);
+                       int32_t world, uint64_t n_floats, void* cuda_stream);
 
 int wgs_stage_timing(WgsContext* ctx, int enable);
 int wgs_stage_times(WgsContext* ctx, float* ms_out /* WGS_NUM_STAGES floats, host */);

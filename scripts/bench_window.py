@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="config3")
     ap.add_argument("--no-sink", action="store_true", help="let autograd allocate/add per-view gradients")
+    ap.add_argument("--peer", default="off", choices=["off", "auto", "nvls", "p2p"],
+                    help="bucket in NVLink peer memory, summed by wgs_peer_allreduce instead of NCCL")
     ap.add_argument("--strips", action="store_true",
                     help="sub-frame units (tile-row strips) when the window does not divide by the world size")
     a = ap.parse_args()
@@ -47,7 +49,7 @@ def main():
     params = {k: t(g[k]).requires_grad_(True) for k in ("means3D", "sh", "opacities", "scales", "rotations")}
     sink_names = None if a.no_sink else {"means3D": "means3D", "sh": "sh", "opacities": "opacity",
                                          "scales": "scales", "rotations": "rotations"}
-    trainer = WindowTrainer(params, sink_names=sink_names)
+    trainer = WindowTrainer(params, sink_names=sink_names, peer=a.peer != "off", peer_mode=a.peer)
     means2D = torch.zeros(P, 3, device=dev, requires_grad=True)
     views = []
     for cam, cot in zip(cams, cots):
@@ -105,7 +107,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": f"{a.workload}: {P} Gaussians, {n_views} keyframes {W}x{H}, SH degree {deg}",
                        "assignment": out["assignment"], "bucket_bytes": out["bucket_bytes"],
-                       "grad_sink": not a.no_sink, "strips": a.strips, "l2": "flushed between steps"}}), flush=True)
+                       "grad_sink": not a.no_sink, "strips": a.strips, "allreduce": "nccl" if a.peer == "off" or world == 1 else "peer:" + a.peer, "l2": "flushed between steps"}}), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -89,7 +89,7 @@ def load():
     lib.wgs_camera_matrices.argtypes = [_fp, _fp, _fp, _fp, _fp, _fp, C.c_void_p]
     lib.wgs_peer_flags_bytes.restype = C.c_size_t
     lib.wgs_peer_allreduce.argtypes = [C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_uint64, C.c_int32, C.c_int32,
-                                       C.c_uint64, C.c_uint32, C.c_void_p]
+                                       C.c_uint64, C.c_void_p]
     lib.wgs_set_async.argtypes = [C.c_void_p, C.c_int]
     lib.wgs_last_num_rendered.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.wgs_stage_timing.argtypes = [C.c_void_p, C.c_int]

@@ -23,7 +23,7 @@ struct PeerParams {
     float* mc;                         // multicast mapping of the bucket (null: P2P path)
     int rank, world;
     size_t n4;                         // float4 elements
-    uint32_t epoch;                    // odd: start barrier value; epoch + 1: end barrier value
+    uint32_t* epochs;                  // [PEER_BLOCKS] in THIS rank's flag area: barrier generation of each block
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -59,7 +59,13 @@ __device__ __forceinline__ void multimem_st(float* mc, float4 v) {
 
 template <bool NVLS>
 __global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const __grid_constant__ PeerParams p) {
-    block_barrier(p, p.epoch);
+    // The barrier generation lives on the device (one counter per block, advanced by 2 per launch), so the
+    // launch has no per-call host argument and can be replayed from a CUDA graph; all ranks launch equally often.
+    __shared__ uint32_t s_epoch;
+    if (threadIdx.x == 0) s_epoch = p.epochs[blockIdx.x] + 1u;
+    __syncthreads();
+    const uint32_t epoch = s_epoch;
+    block_barrier(p, epoch);
     const size_t per = (p.n4 + p.world - 1) / p.world;
     const size_t begin = min(p.n4, per * p.rank), end = min(p.n4, begin + per);
     const size_t stride = (size_t)gridDim.x * PEER_THREADS;
@@ -91,7 +97,8 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const __gr
                     if (i0 + u * stride < end) __stcg(reinterpret_cast<float4*>(p.buf[r]) + i0 + u * stride, s[u]);
         }
     }
-    block_barrier(p, p.epoch + 1);
+    block_barrier(p, epoch + 1u);
+    if (threadIdx.x == 0) p.epochs[blockIdx.x] = epoch + 1u;
 }
 
 }  // namespace wgs
@@ -99,14 +106,16 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const __gr
 extern "C" {
 void wgs_set_error_message(const char* msg);
 
-size_t wgs_peer_flags_bytes(void) { return (size_t)wgs::PEER_BLOCKS * wgs::PEER_MAX_WORLD * sizeof(uint32_t); }
+size_t wgs_peer_flags_bytes(void) {
+    return (size_t)wgs::PEER_BLOCKS * (wgs::PEER_MAX_WORLD + 1) * sizeof(uint32_t);  // flags + per-block generation
+}
 
 int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
-                       int32_t world, uint64_t n_floats, uint32_t epoch, void* cuda_stream) {
+                       int32_t world, uint64_t n_floats, void* cuda_stream) {
     using namespace wgs;
     if (!buffer_ptrs || !flag_ptrs || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world ||
-        (n_floats & 3u) || !(epoch & 1u)) {
-        wgs_set_error_message("wgs_peer_allreduce: bad world/rank, n_floats not a multiple of 4, or even epoch");
+        (n_floats & 3u)) {
+        wgs_set_error_message("wgs_peer_allreduce: bad world/rank or n_floats not a multiple of 4");
         return WGS_ERR_INVALID_ARGUMENT;
     }
     PeerParams p;
@@ -118,7 +127,8 @@ int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, u
             return WGS_ERR_INVALID_ARGUMENT;
         }
     }
-    p.mc = (float*)multicast_ptr; p.rank = rank; p.world = world; p.n4 = n_floats / 4; p.epoch = epoch;
+    p.mc = (float*)multicast_ptr; p.rank = rank; p.world = world; p.n4 = n_floats / 4;
+    p.epochs = p.flags[rank] + PEER_BLOCKS * PEER_MAX_WORLD;
     cudaStream_t s = (cudaStream_t)cuda_stream;
     if (p.mc) peer_allreduce_kernel<true><<<PEER_BLOCKS, PEER_THREADS, 0, s>>>(p);
     else peer_allreduce_kernel<false><<<PEER_BLOCKS, PEER_THREADS, 0, s>>>(p);

@@ -38,7 +38,6 @@ class PeerBucket:
         mc = int(getattr(self._h, "multicast_ptr", 0) or 0)
         self.multicast = bool(mc) and use_multicast
         self._mc = mc if self.multicast else 0
-        self._epoch = 1
         torch.cuda.synchronize(self.device)
         dist.barrier(self.group)                               # every rank's flags are zero before the first call
 
@@ -50,8 +49,7 @@ class PeerBucket:
         """In-place sum of `flat` over the group, enqueued on the current stream."""
         with torch.cuda.device(self.device):
             rc = _lib.load().wgs_peer_allreduce(self._bufs, self._flags, self._mc, self.rank, self.world, self.n_pad,
-                                                self._epoch, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+                                                C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
         if rc != _lib.WGS_OK:
             raise RuntimeError(f"wgs_peer_allreduce failed ({rc}): {_lib.last_error()}")
-        self._epoch += 2
         return self.flat

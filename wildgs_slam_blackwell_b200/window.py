@@ -65,12 +65,23 @@ class GradBucket:
     per-leaf views into it.  Installing the views as `.grad` makes autograd accumulate straight into
     the buffer, so the allreduce needs no packing copy."""
 
-    def __init__(self, params: Dict[str, torch.Tensor]):
+    def __init__(self, params: Dict[str, torch.Tensor], peer_group=None, peer_mode: str = "auto"):
+        """peer_group: a process group whose ranks share one NVLink domain -> the buffer is allocated in
+        symmetric peer memory (peer.PeerBucket) and all_reduce() runs the library's own kernel instead of
+        ncclAllReduce.  peer_mode: 'nvls' | 'p2p' | 'auto' (multicast from 4 ranks up)."""
         self.names = list(params)
         self.params = params
         n = sum(p.numel() for p in params.values())
         first = next(iter(params.values()))
-        self.flat = torch.zeros(n, dtype=torch.float32, device=first.device)
+        self.peer = None
+        if peer_group is not None and first.is_cuda:
+            from .peer import PeerBucket
+            world = dist.get_world_size(peer_group)
+            mc = peer_mode == "nvls" or (peer_mode == "auto" and world >= 4)
+            self.peer = PeerBucket(n, first.device, peer_group, use_multicast=mc)
+            self.flat = self.peer.flat
+        else:
+            self.flat = torch.zeros(n, dtype=torch.float32, device=first.device)
         self.views: Dict[str, torch.Tensor] = {}
         off = 0
         for k, p in params.items():
@@ -94,6 +105,13 @@ class GradBucket:
     def nbytes(self) -> int:
         return self.flat.numel() * 4
 
+    def all_reduce(self, group=None, async_op=False):
+        """Sum the bucket over the ranks: the peer-memory kernel when allocated there, else NCCL/gloo."""
+        if self.peer is not None:
+            self.peer.all_reduce()
+            return None
+        return dist.all_reduce(self.flat, group=group, async_op=async_op)
+
 
 class WindowTrainer:
     """Drives one window step.
@@ -108,7 +126,7 @@ class WindowTrainer:
     """
 
     def __init__(self, params: Dict[str, torch.Tensor], group: Optional[dist.ProcessGroup] = None,
-                 sink_names: Optional[Dict[str, str]] = None):
+                 sink_names: Optional[Dict[str, str]] = None, peer: bool = False, peer_mode: str = "auto"):
         """`sink_names` (optional): leaf name -> rasterizer gradient name ('means3D', 'sh', 'opacity',
         'scales', 'rotations', ...).  When given, the rasterizer's backward kernel writes / accumulates
         straight into the bucket (rasterizer.grad_sink) instead of autograd allocating per-view
@@ -119,13 +137,16 @@ class WindowTrainer:
         self.distributed = dist.is_available() and dist.is_initialized()
         self.world = dist.get_world_size(group) if self.distributed else 1
         self.rank = dist.get_rank(group) if self.distributed else 0
-        self.bucket = GradBucket(params)
+        # peer=True: bucket in NVLink peer memory, summed by wgs_peer_allreduce (single node, CUDA only)
+        self._peer_group = (group if group is not None else dist.group.WORLD) if (peer and self.world > 1) else None
+        self._peer_mode = peer_mode
+        self.bucket = GradBucket(params, self._peer_group, peer_mode)
         self.costs: List[float] = []
 
     def rebind(self, params: Dict[str, torch.Tensor]):
         """Call after densify/prune changed the number of Gaussians."""
         if not self.bucket.matches(params):
-            self.bucket = GradBucket(params)
+            self.bucket = GradBucket(params, self._peer_group, self._peer_mode)
         else:
             self.bucket.params = params
 
@@ -166,9 +187,10 @@ class WindowTrainer:
         if use_sink:
             b.install(zero=False)
         if self.world > 1:
-            work = dist.all_reduce(b.flat, group=self.group, async_op=True)
+            work = b.all_reduce(self.group, async_op=True)
             dist.all_reduce(side, group=self.group)
-            work.wait()
+            if work is not None:
+                work.wait()
         self.costs = [float(c) for c in side[:, 1].tolist()]
         return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": assignment,
                 "bucket_bytes": b.nbytes}
@@ -201,9 +223,10 @@ class WindowTrainer:
                 side[v, 2:8] += pose_grad_fn().reshape(6)
         if use_sink:
             b.install(zero=False)
-        work = dist.all_reduce(b.flat, group=self.group, async_op=True)
+        work = b.all_reduce(self.group, async_op=True)
         dist.all_reduce(side, group=self.group)
-        work.wait()
+        if work is not None:
+            work.wait()
         self.costs = [float(c) for c in side[:, 1].tolist()]
         return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": plan, "bucket_bytes": b.nbytes}
 
