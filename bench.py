@@ -368,7 +368,11 @@ def roofline_pass(wl, steps, flush):
     roof = {"kernel": top + "_kernel", "bound": "hbm", "achieved": stages[top]["gbs"], "peak": peak, "unit": "GB/s",
             "frac": stages[top]["frac"], "traffic": committed_traffic(top), "peak_source": peak_src,
             "ms_per_launch": stages[top]["ms"], "alg_bytes_per_launch": stages[top]["alg_bytes"],
-            "note": "render stages are FP32-issue/atomic bound (no dense contraction); HBM fraction reported per contract"}
+            "note": "render stages are FP32-issue bound, not HBM bound; HBM fraction reported per contract, "
+                    "issue_active_pct (ncu smsp__issue_active, committed profile) is the utilisation that bounds them"}
+    issue = committed_traffic("_issue_active_pct")
+    if isinstance(issue, dict) and top in issue:
+        roof["issue_active_pct"] = issue[top]
     return roof, stages, dict(P_vis=P_vis, R=R)
 
 

@@ -25,7 +25,7 @@ M = [("gpu__time_duration.sum", "time us"), ("launch__registers_per_thread", "re
      ("smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio", "stall lg_throttle"),
      ("smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio", "stall barrier"),
      ("smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio", "stall not_selected")]
-seen, traffic, lines = set(), {}, []
+seen, traffic, issue, lines = set(), {}, {}, []
 lines.append(f"# {tag}: ncu --set full --clock-control none (one launch per kernel, cold-ish cache, serialised)\n")
 lines.append("| kernel | " + " | ".join(n for _, n in M) + " | dram MB (r+w) |")
 lines.append("|---|" + "---|" * (len(M) + 1))
@@ -36,6 +36,10 @@ for r in rows[2:]:
     seen.add(k)
     b = sum(float(r[col(n)]) * MUL[U[col(n)]] for n in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
     traffic[k.replace("_kernel", "")] = int(b)
+    try:
+        issue[k.replace("_kernel", "")] = round(float(r[col("smsp__issue_active.avg.pct_of_peak_sustained_active")]), 2)
+    except Exception:
+        pass
     vals = []
     for n, _ in M:
         try:
@@ -59,6 +63,7 @@ if os.path.exists(launches):
     lines.append("| kernel | launches | avg us | share % |\n|---|---|---|---|")
     for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         lines.append(f"| {k} | {a[0]} | {a[1] / a[0] / 1e3:.1f} | {100 * a[1] / tot:.1f} |")
+traffic["_issue_active_pct"] = issue
 traffic["_source"] = f"{tag}: ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch (see profiles/{tag}_ncu_summary.md)"
 os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
 open(os.path.join(ROOT, "profiles", f"{tag}_ncu_summary.md"), "w").write("\n".join(lines) + "\n")
