@@ -90,6 +90,21 @@ def build_torch_ext(force=False):
     return target
 
 
+def build_simple_knn(force=False):
+    """The unmodified reference simple-knn (thirdparty/simple-knn/simple_knn.cu) + ref_knn_shim.cu
+    -> oracle/_ref/libref_simple_knn.so (raw-pointer C entry ref_dist_cuda2)."""
+    knn = os.path.join(REF, "thirdparty", "simple-knn")
+    srcs = [os.path.join(knn, "simple_knn.cu"), os.path.join(HERE, "ref_knn_shim.cu")]
+    target = os.path.join(OUT, "libref_simple_knn.so")
+    if not force and newer(target, srcs):
+        print("up to date:", target)
+        return target
+    os.makedirs(OUT, exist_ok=True)
+    run(["nvcc", "-shared", "-o", target, *srcs, *ARCH, "-include", "cstdint", "-include", "cfloat", "-std=c++17",
+         '-DREF_SIMPLE_KNN_H="%s"' % os.path.join(knn, "simple_knn.h"), "-Xcompiler", "-fPIC", "-lcudart", "-w"])
+    return target
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--no-torch-ext", action="store_true")
@@ -99,6 +114,7 @@ def main():
         print("reference tree not present at", RAST, "- nothing to do")
         return 0
     build_shim(a.force)
+    build_simple_knn(a.force)
     if not a.no_torch_ext:
         build_torch_ext(a.force)
     return 0

@@ -68,3 +68,25 @@ def test_no_cpu_fallback():
     import torch
     with pytest.raises(RuntimeError, match="CUDA"):
         loss.photometric_loss(torch.zeros(3, 4, 4), torch.zeros(3, 4, 4))
+
+
+def test_knn_abi_symbols_and_oracle_bruteforce():
+    from oracle import knn_oracle
+    from wildgs_slam_blackwell_b200 import knn
+    header = open(os.path.join(ROOT, "include", "wgs_knn.h")).read()
+    declared = set(re.findall(r"\b(wgs_[a-z_0-9]+)\s*\(", header))
+    assert declared == set(knn.EXPORTS), declared ^ set(knn.EXPORTS)
+    lib = knn._lib_knn()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.wgs_knn_workspace_bytes(100000) > 100000 * 20
+    assert lib.wgs_dist_cuda2(-1, None, None, None, None) == _lib.WGS_ERR_INVALID_ARGUMENT
+    rng = np.random.default_rng(0)
+    pts = rng.uniform(0, 1, (300, 3)).astype(np.float32)
+    pts[10] = pts[11]                                               # a duplicate pair
+    d = pts[:, None, :] - pts[None, :, :]
+    d2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1] + d[..., 2] * d[..., 2]).astype(np.float32)
+    np.fill_diagonal(d2, np.inf)
+    d2.sort(axis=1)
+    brute = (d2[:, 0] + d2[:, 1] + d2[:, 2]) / np.float32(3.0)
+    np.testing.assert_allclose(knn_oracle.dist_cuda2(pts), brute, rtol=1e-6)
