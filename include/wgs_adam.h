@@ -1,0 +1,38 @@
+/*
+ * wgs_adam.h — C ABI of the fused multi-tensor Adam step (libwgs_rasterizer.so).  SURVEY.md §8(f) row 3
+ * (optimiser side): ONE launch updates every parameter tensor of the Gaussian model (xyz, f_dc, f_rest,
+ * opacity, scaling, rotation: thirdparty/gaussian_splatting/scene/gaussian_model.py training_setup, a
+ * torch.optim.Adam with one param group per tensor, eps 1e-15) instead of torch's per-op foreach kernels.
+ * Arithmetic of torch.optim.Adam (amsgrad off, weight_decay 0, maximize off):
+ *   m = m + (1 - beta1) (g - m);  v = beta2 v + (1 - beta2) g g;
+ *   p = p - (lr / bias_correction1) * m / (sqrt(v) / sqrt(bias_correction2) + eps)
+ * The bias corrections are passed in (the host computes 1 - beta^step in double like torch).
+ */
+#ifndef WGS_ADAM_H_
+#define WGS_ADAM_H_
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WGS_ADAM_MAX_TENSORS 16
+
+typedef struct WgsAdamTensor {
+  float* param;            /* (n) updated in place */
+  const float* grad;       /* (n) */
+  float* exp_avg;          /* (n) updated in place */
+  float* exp_avg_sq;       /* (n) updated in place */
+  uint64_t n;
+  float step_size;         /* lr / (1 - beta1^step) */
+  float bias_correction2_sqrt; /* sqrt(1 - beta2^step) */
+} WgsAdamTensor;
+
+/* tensors: HOST array of `count` (<= WGS_ADAM_MAX_TENSORS) descriptors with DEVICE pointers */
+int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, float beta1, float beta2, float eps,
+                  void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WGS_ADAM_H_ */

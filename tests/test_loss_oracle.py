@@ -90,3 +90,18 @@ def test_knn_abi_symbols_and_oracle_bruteforce():
     d2.sort(axis=1)
     brute = (d2[:, 0] + d2[:, 1] + d2[:, 2]) / np.float32(3.0)
     np.testing.assert_allclose(knn_oracle.dist_cuda2(pts), brute, rtol=1e-6)
+
+
+def test_adam_and_peer_abi_symbols():
+    from wildgs_slam_blackwell_b200 import adam
+    header = open(os.path.join(ROOT, "include", "wgs_adam.h")).read()
+    declared = set(re.findall(r"\b(wgs_[a-z_0-9]+)\s*\(", header))
+    assert declared == set(adam.EXPORTS)
+    lib = adam._lib_adam()
+    assert hasattr(lib, "wgs_adam_step")
+    body = re.search(r"typedef struct WgsAdamTensor \{(.*?)\} WgsAdamTensor;", header, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = [re.findall(r"[A-Za-z_0-9]+", d)[-1] for d in body.split(";") if d.strip()]
+    assert names == [f[0] for f in adam.AdamTensor._fields_]
+    assert lib.wgs_adam_step(None, 3, 0.9, 0.999, 1e-8, None) == _lib.WGS_ERR_INVALID_ARGUMENT
+    assert lib.wgs_adam_step(None, 0, 0.9, 0.999, 1e-8, None) == _lib.WGS_OK
