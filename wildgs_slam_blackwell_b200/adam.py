@@ -28,7 +28,7 @@ def _lib_adam():
     global _proto_done
     lib = _lib.load()
     if not _proto_done:
-        lib.wgs_adam_step.argtypes = [C.POINTER(AdamTensor), C.c_int32, C.c_float, C.c_float, C.c_float, C.c_void_p]
+        lib.wgs_adam_step.argtypes = [C.POINTER(AdamTensor), C.c_int32, C.c_double, C.c_double, C.c_double, C.c_void_p]
         _proto_done = True
     return lib
 

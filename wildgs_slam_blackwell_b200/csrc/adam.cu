@@ -13,7 +13,7 @@ struct AdamParams {
     WgsAdamTensor t[WGS_ADAM_MAX_TENSORS];
     uint32_t first_block[WGS_ADAM_MAX_TENSORS + 1];
     int count;
-    float beta1, beta2, eps;
+    float beta2, w1, w2, eps;   // w = 1 - beta, formed in double on the host
 };
 
 __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const __grid_constant__ AdamParams p) {
@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const __grid_constan
     while (e + 1 < p.count && blockIdx.x >= p.first_block[e + 1]) e++;
     const WgsAdamTensor& t = p.t[e];
     const size_t base = ((size_t)(blockIdx.x - p.first_block[e]) * ADAM_THREADS + threadIdx.x) * ADAM_EPT;
-    const float w1 = 1.f - p.beta1, w2 = 1.f - p.beta2;
+    const float w1 = p.w1, w2 = p.w2;
 #pragma unroll
     for (int k = 0; k < ADAM_EPT; k++) {
         const size_t i = base + k;
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const __grid_constan
 extern "C" {
 void wgs_set_error_message(const char* msg);
 
-int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, float beta1, float beta2, float eps,
+int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, double beta1, double beta2, double eps,
                   void* cuda_stream) {
     using namespace wgs;
     if (count < 0 || count > WGS_ADAM_MAX_TENSORS || (count > 0 && !tensors)) {
@@ -51,7 +51,7 @@ int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, float beta1, floa
         return WGS_ERR_INVALID_ARGUMENT;
     }
     AdamParams p;
-    p.count = 0; p.beta1 = beta1; p.beta2 = beta2; p.eps = eps;
+    p.count = 0; p.beta2 = (float)beta2; p.w1 = (float)(1.0 - beta1); p.w2 = (float)(1.0 - beta2); p.eps = (float)eps;
     uint32_t blocks = 0;
     for (int i = 0; i < count; i++) {
         const WgsAdamTensor& t = tensors[i];
