@@ -59,8 +59,18 @@ def timeit(fn, flush, warm=10, steps=60):
     return statistics.median(a.elapsed_time(b) for a, b in ev)
 
 
+def torch_loss_mapping(image, depth, vp, gt_depth):
+    """get_loss_mapping + get_loss_mapping_rgbd as torch expressions (slam_utils.py:107-143, ssim off)."""
+    image_ab = torch.exp(vp.exposure_a) * image + vp.exposure_b
+    gt = vp.original_image
+    m = (gt.sum(dim=0) > CONFIG["Training"]["rgb_boundary_threshold"]).view(1, *gt.shape[1:])
+    dm = (gt_depth > 0.01).view(*depth.shape)
+    return 0.95 * torch.abs(image_ab * m - gt * m).mean() + 0.05 * torch.abs(depth * dm - gt_depth * dm).mean()
+
+
 def main():
-    P, W, H, deg, _ = scenes.CONFIGS["config2"]
+    mapping = len(sys.argv) > 1 and sys.argv[1] == "mapping"
+    P, W, H, deg, _ = scenes.CONFIGS["config3" if mapping else "config2"]
     cam_d = scenes.make_camera(W, H, 1002)
     g = scenes.make_gaussians(P, W, H, deg, 1002, cam_d)
     rng = np.random.default_rng(3)
@@ -78,6 +88,16 @@ def main():
         cam.exposure_a = torch.zeros(1, device=DEV, requires_grad=True)
         cam.exposure_b = torch.zeros(1, device=DEV, requires_grad=True)
         leaves = list(pc.leaves().values()) + [cam.cam_rot_delta, cam.cam_trans_delta, cam.exposure_a, cam.exposure_b]
+        opt = None
+        if mapping:   # one keyframe per iteration + Adam over the Gaussian parameters, as map_opt_online does
+            cam.depth = rng.uniform(0.5, 6.0, (H, W)).astype(np.float32)
+            gt_depth = torch.from_numpy(cam.depth).to(DEV)[None]
+            groups = [{"params": [t], "lr": lr} for t, lr in zip(pc.leaves().values(), (1.6e-4, 2.5e-3, 1.25e-4, 0.05, 1e-3, 1e-3))]
+            if arm == "fused":
+                from wildgs_slam_blackwell_b200.adam import FusedAdam
+                opt = FusedAdam(groups, lr=0.0, eps=1e-15)
+            else:
+                opt = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
         if arm == "reference":
             import importlib
             for k in [k for k in sys.modules if k.startswith("diff_gaussian_rasterization")]:
@@ -93,19 +113,27 @@ def main():
                 t.grad = None
             if arm == "fused":
                 pkg = renderer.render(cam, pc, Pipe(), bg)
-                l = fused_loss.get_loss_tracking(CONFIG, pkg["render"], pkg["depth"], pkg["opacity"], cam)
+                if mapping:
+                    l = fused_loss.get_loss_mapping({"Training": {"rgb_boundary_threshold": 0.01, "alpha": 0.95}},
+                                                    pkg["render"], pkg["depth"], cam)
+                else:
+                    l = fused_loss.get_loss_tracking(CONFIG, pkg["render"], pkg["depth"], pkg["opacity"], cam)
             else:
                 img, depth, opacity = composition(mod, cam, pc, bg)
-                l = torch_loss_tracking(img, opacity, cam)
+                l = torch_loss_mapping(img, depth, cam, gt_depth) if mapping else torch_loss_tracking(img, opacity, cam)
             l.backward()
+            if opt is not None:
+                opt.step()
 
         res[arm] = round(timeit(step, flush), 4)
-        if arm == "fused":
+        if arm == "fused" and not mapping:
             from wildgs_slam_blackwell_b200 import graph
             it = graph.CapturedIteration(step, DEV)
             res["fused_graph"] = round(timeit(it.replay, flush), 4)
             it.check()
-    print(json.dumps({"what": "tracking iteration (render + tracking loss + backward), config2, ms per iteration (median)",
+    what = ("mapping iteration (render + mapping loss + backward + Adam step), config3 Gaussians (1 M), one keyframe"
+            if mapping else "tracking iteration (render + tracking loss + backward), config2")
+    print(json.dumps({"what": what + ", ms per iteration (median)",
                       **res}))
 
 
