@@ -105,3 +105,21 @@ def test_adam_and_peer_abi_symbols():
     assert names == [f[0] for f in adam.AdamTensor._fields_]
     assert lib.wgs_adam_step(None, 3, 0.9, 0.999, 1e-8, None) == _lib.WGS_ERR_INVALID_ARGUMENT
     assert lib.wgs_adam_step(None, 0, 0.9, 0.999, 1e-8, None) == _lib.WGS_OK
+
+
+def test_pose_abi_symbols_and_structs():
+    from wildgs_slam_blackwell_b200 import pose
+    header = open(os.path.join(ROOT, "include", "wgs_pose.h")).read()
+    declared = set(re.findall(r"\b(wgs_[a-z_0-9]+)\s*\(", header)) - {"wgs_camera_matrices"}
+    assert declared == set(pose.EXPORTS), declared
+    assert hasattr(pose._lib_pose(), "wgs_pose_step")
+    for cname, cls in (("WgsPoseAdam", pose.PoseAdam), ("WgsPoseStepArgs", pose.PoseStepArgs)):
+        body = re.search(r"typedef struct " + cname + r" \{(.*?)\} " + cname + ";", header, re.S).group(1)
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        names = []
+        for decl in body.split(";"):
+            for part in decl.strip().split(","):
+                if part.strip():
+                    names.append(re.findall(r"[A-Za-z_0-9]+", part)[-1])
+        assert names == [f[0] for f in cls._fields_], cname
+    assert pose._lib_pose().wgs_pose_step(None, None) == _lib.WGS_ERR_INVALID_ARGUMENT
