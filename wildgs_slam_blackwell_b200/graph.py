@@ -66,7 +66,13 @@ class CapturedIteration:
     """
 
     def __init__(self, step, device, warmup=3):
+        import gc
         self.device = torch.device(device)
+        # autograd binds a leaf's gradient accumulator to the stream that was current when it was created and keeps
+        # it while any graph references it; drop dead graphs from earlier eager iterations so that the warm-up below
+        # (on the side stream) creates fresh ones -- a live graph built on the default stream would make the captured
+        # backward launch on that stream and invalidate the capture
+        gc.collect()
         side = torch.cuda.Stream(self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(side):       # eager warm-up: contexts, workspaces, capacity hint

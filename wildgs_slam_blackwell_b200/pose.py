@@ -110,6 +110,22 @@ class FusedPoseOptimizer:
         self.hyper = dict(lr_rot=lr_rot, lr_trans=lr_trans, lr_exposure_a=lr_exposure_a, lr_exposure_b=lr_exposure_b,
                           beta1=betas[0], beta2=betas[1], eps=eps)
 
+    def reset(self, R=None, T=None):
+        """Start a new refinement with the same (possibly graph-captured) buffers: Adam state and step counter
+        zeroed, optionally a new initial pose copied INTO camera.R / camera.T, deltas zeroed, camera matrices
+        refreshed in place.  Lets one captured iteration serve every frame of a sequence."""
+        cam = self.camera
+        with torch.no_grad():
+            self.state.zero_()
+            self.step_count.zero_()
+            if R is not None:
+                cam.R.copy_(R)
+            if T is not None:
+                cam.T.copy_(T)
+            cam.cam_rot_delta.zero_()
+            cam.cam_trans_delta.zero_()
+        update_pose(cam, self.threshold)
+
     def zero_grad(self):
         cam = self.camera
         for t in (cam.cam_rot_delta, cam.cam_trans_delta, getattr(cam, "exposure_a", None), getattr(cam, "exposure_b", None)):
