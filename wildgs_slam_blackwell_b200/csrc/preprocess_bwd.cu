@@ -49,7 +49,7 @@ __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const 
     c[5] = M[6] * M[6] + M[7] * M[7] + M[8] * M[8];
 }
 
-__global__ void __launch_bounds__(WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
+__global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
     const int idx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
     const bool accm = p.accumulate != 0;
     float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
