@@ -123,3 +123,19 @@ def test_pose_abi_symbols_and_structs():
                     names.append(re.findall(r"[A-Za-z_0-9]+", part)[-1])
         assert names == [f[0] for f in cls._fields_], cname
     assert pose._lib_pose().wgs_pose_step(None, None) == _lib.WGS_ERR_INVALID_ARGUMENT
+
+
+def test_compact_abi_symbols():
+    from wildgs_slam_blackwell_b200 import compaction
+    header = open(os.path.join(ROOT, "include", "wgs_compact.h")).read()
+    declared = set(re.findall(r"\b(wgs_[a-z_0-9]+)\s*\(", header))
+    assert declared == set(compaction.EXPORTS), declared
+    lib = compaction._lib_compact()
+    for name in declared:
+        assert hasattr(lib, name)
+    body = re.search(r"typedef struct WgsCompactTensor \{(.*?)\} WgsCompactTensor;", header, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = [re.findall(r"[A-Za-z_0-9]+", d)[-1] for d in body.split(";") if d.strip()]
+    assert names == [f[0] for f in compaction.CompactTensor._fields_]
+    assert lib.wgs_compact_workspace_bytes(3_000_000) >= 2930 * 4
+    assert lib.wgs_compact_plan(-1, None, None, None, None, None) == _lib.WGS_ERR_INVALID_ARGUMENT
