@@ -124,6 +124,8 @@ def test_whole_tracking_iteration_as_one_graph():
     le, Re, Te = run(False)
     lc, Rc, Tc = run(True)
     np.testing.assert_allclose(lc, le, rtol=1e-4)
-    torch.testing.assert_close(Rc, Re, rtol=1e-4, atol=1e-5)
-    torch.testing.assert_close(Tc, Te, rtol=1e-4, atol=1e-5)
+    # float-atomic summation order differs from run to run and Adam's normalised step magnifies it (a step is
+    # ~lr = 1e-3 whatever the gradient's size): 1e-4 is about 1 % of the distance moved in these 8 iterations
+    torch.testing.assert_close(Rc, Re, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(Tc, Te, rtol=1e-4, atol=1e-4)
     assert le[-1] < le[0]          # the pose moves towards the target view

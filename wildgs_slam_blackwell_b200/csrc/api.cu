@@ -90,6 +90,8 @@ WgsContext* wgs_context_create(int device) {
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_R, cudaEventDisableTiming);
     if (e == cudaSuccess) e = (cudaError_t)configure_binning();
     if (e == cudaSuccess) e = (cudaError_t)configure_render_bwd();
+    if (e == cudaSuccess) e = (cudaError_t)configure_preprocess_bwd();
+    if (e == cudaSuccess) e = (cudaError_t)configure_preprocess_fwd();
     if (e != cudaSuccess) {
         set_err("wgs_context_create", e);
         delete c;

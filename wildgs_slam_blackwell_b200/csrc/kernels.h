@@ -82,5 +82,7 @@ void launch_export_geometry(int P, const GeomView& g, const int* radii, float* d
                             float* conic_opacity, float* rgb, uint8_t* clamped, cudaStream_t s);
 int configure_binning();  // one-time cudaFuncSetAttribute calls; returns cudaError_t
 int configure_render_bwd();
+int configure_preprocess_bwd();
+int configure_preprocess_fwd();
 
 }  // namespace wgs

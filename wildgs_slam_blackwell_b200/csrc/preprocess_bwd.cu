@@ -11,6 +11,7 @@
 // block sums them in a fixed order: deterministic, no (P,6) buffer, no atomics on dL_dtau).
 #include "common.cuh"
 #include "kernels.h"
+#include "sh_stage.cuh"
 
 namespace wgs {
 
@@ -49,11 +50,25 @@ __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const 
     c[5] = M[6] * M[6] + M[7] * M[7] + M[8] * M[8];
 }
 
+// STAGED (1 < M <= 16): the block's SH rows -- one contiguous span of global memory -- are copied into shared
+// memory with coalesced loads (rows of culled Gaussians skipped), each thread reads its coefficients and leaves its
+// dL_dsh there in place, and the span is written back coalesced (zeros for culled rows).  Per-thread row access
+// to global memory (192-B stride) moved 1.9 GB for 1.2 GB of algorithmic traffic at config 4.
+template <bool STAGED>
 __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
-    const int idx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
+    extern __shared__ float sh_stage[];
+    __shared__ uint8_t s_vis[WGS_PRE_BWD_THREADS];
+    const int gidx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
+    const bool live = gidx < p.P;
+    const int idx = live ? gidx : p.P - 1;  // dead threads of the last block shadow its last Gaussian, write nothing
     const bool accm = p.accumulate != 0;
     float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (idx < p.P) {
+    // staged SH span of this block: packed (P,M,3) rows, or the (P,M-1,3) rest rows in raw-parameter mode
+    const int sh_rw = STAGED ? (p.sh_rest ? 3 * (p.M - 1) : 3 * p.M) : 1;
+    const int sh_rs = sh_row_stride(sh_rw);
+    const size_t sh_span0 = (size_t)blockIdx.x * WGS_PRE_BWD_THREADS * sh_rw;
+    const uint32_t sh_nw = (uint32_t)min(WGS_PRE_BWD_THREADS, p.P - (int)(blockIdx.x * WGS_PRE_BWD_THREADS)) * sh_rw;
+    {
         // Issue every load this Gaussian can need before looking at radii, so that the latencies
         // overlap (the kernel is latency-bound: 108 registers, 2 CTAs/SM).  Accumulator records of
         // culled Gaussians are never written, so they read as zero.
@@ -81,7 +96,13 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
         }
         const uint2 rect = __ldg(p.geom.rect + idx);
         const float4 ra = __ldcg(p.geom.rec + 2 * idx), rb = __ldcg(p.geom.rec + 2 * idx + 1);
-        const bool vis = rad > 0 && rect.x != rect.y;  // rect is empty outside the rendered strip
+        const bool vis = live && rad > 0 && rect.x != rect.y;  // rect is empty outside the rendered strip
+        if (STAGED) {
+            s_vis[threadIdx.x] = vis;
+            __syncthreads();
+            sh_stage_load(sh_stage, s_vis, (p.sh_rest ? p.sh_rest : p.sh) + sh_span0, sh_nw, sh_rw, sh_rs);
+            __syncthreads();
+        }
         if (vis) {
             const float4 z4 = make_float4(0, 0, 0, 0);
             p.grad.acc[3 * idx] = z4; p.grad.acc[3 * idx + 1] = z4; p.grad.acc[3 * idx + 2] = z4;
@@ -210,30 +231,36 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
                 const V3 dir_orig = {m.x - __ldg(p.campos), m.y - __ldg(p.campos + 1), m.z - __ldg(p.campos + 2)};
                 const float il = 1.f / sqrtf(dot(dir_orig, dir_orig));
                 const float x = dir_orig.x * il, y = dir_orig.y * il, z = dir_orig.z * il;
+                // STAGED: coefficient k of this thread's row sits at srow + 3 (k + koff); dL_dsh replaces it in place,
+                // so every band reads its coefficients before it puts its gradients
+                float* __restrict__ srow = sh_stage + threadIdx.x * sh_rs;
+                const int koff = p.sh_rest ? -1 : 0;
                 auto SH = [&](int k) {  // only called with k >= 1
+                    if (STAGED) return V3{srow[3 * (k + koff)], srow[3 * (k + koff) + 1], srow[3 * (k + koff) + 2]};
                     return V3{__ldg(shr + 3 * (k - 1)), __ldg(shr + 3 * (k - 1) + 1), __ldg(shr + 3 * (k - 1) + 2)};
                 };
                 auto put = [&](int k, float w) {
+                    if (STAGED && (k || !p.sh_rest)) {
+                        float* d = srow + 3 * (k + koff);
+                        d[0] = w * dRGB.x; d[1] = w * dRGB.y; d[2] = w * dRGB.z;
+                        return;
+                    }
                     float* d = k ? dshr + 3 * (k - 1) : dsh0;
                     gput(d, 0, w * dRGB.x, accm); gput(d, 1, w * dRGB.y, accm); gput(d, 2, w * dRGB.z, accm);
                 };
                 V3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
                 put(0, kSH_C0);
                 if (p.D > 0) {
-                    put(1, -kSH_C1 * y); put(2, kSH_C1 * z); put(3, -kSH_C1 * x);
                     dx = -kSH_C1 * SH(3); dy = -kSH_C1 * SH(1); dz = kSH_C1 * SH(2);
+                    put(1, -kSH_C1 * y); put(2, kSH_C1 * z); put(3, -kSH_C1 * x);
                     if (p.D > 1) {
                         const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-                        put(4, kSH_C2[0] * xy); put(5, kSH_C2[1] * yz); put(6, kSH_C2[2] * (2.f * zz - xx - yy));
-                        put(7, kSH_C2[3] * xz); put(8, kSH_C2[4] * (xx - yy));
                         dx = dx + (kSH_C2[0] * y) * SH(4) + (kSH_C2[2] * 2.f * -x) * SH(6) + (kSH_C2[3] * z) * SH(7) + (kSH_C2[4] * 2.f * x) * SH(8);
                         dy = dy + (kSH_C2[0] * x) * SH(4) + (kSH_C2[1] * z) * SH(5) + (kSH_C2[2] * 2.f * -y) * SH(6) + (kSH_C2[4] * 2.f * -y) * SH(8);
                         dz = dz + (kSH_C2[1] * y) * SH(5) + (kSH_C2[2] * 2.f * 2.f * z) * SH(6) + (kSH_C2[3] * x) * SH(7);
+                        put(4, kSH_C2[0] * xy); put(5, kSH_C2[1] * yz); put(6, kSH_C2[2] * (2.f * zz - xx - yy));
+                        put(7, kSH_C2[3] * xz); put(8, kSH_C2[4] * (xx - yy));
                         if (p.D > 2) {
-                            put(9, kSH_C3[0] * y * (3.f * xx - yy)); put(10, kSH_C3[1] * xy * z);
-                            put(11, kSH_C3[2] * y * (4.f * zz - xx - yy)); put(12, kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
-                            put(13, kSH_C3[4] * x * (4.f * zz - xx - yy)); put(14, kSH_C3[5] * z * (xx - yy));
-                            put(15, kSH_C3[6] * x * (xx - 3.f * yy));
                             dx = dx + (kSH_C3[0] * 3.f * 2.f * xy) * SH(9) + (kSH_C3[1] * yz) * SH(10) + (kSH_C3[2] * -2.f * xy) * SH(11) +
                                  (kSH_C3[3] * -3.f * 2.f * xz) * SH(12) + (kSH_C3[4] * (-3.f * xx + 4.f * zz - yy)) * SH(13) +
                                  (kSH_C3[5] * 2.f * xz) * SH(14) + (kSH_C3[6] * 3.f * (xx - yy)) * SH(15);
@@ -243,6 +270,10 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
                             dz = dz + (kSH_C3[1] * xy) * SH(10) + (kSH_C3[2] * 4.f * 2.f * yz) * SH(11) +
                                  (kSH_C3[3] * 3.f * (2.f * zz - xx - yy)) * SH(12) + (kSH_C3[4] * 4.f * 2.f * xz) * SH(13) +
                                  (kSH_C3[5] * (xx - yy)) * SH(14);
+                            put(9, kSH_C3[0] * y * (3.f * xx - yy)); put(10, kSH_C3[1] * xy * z);
+                            put(11, kSH_C3[2] * y * (4.f * zz - xx - yy)); put(12, kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
+                            put(13, kSH_C3[4] * x * (4.f * zz - xx - yy)); put(14, kSH_C3[5] * z * (xx - yy));
+                            put(15, kSH_C3[6] * x * (xx - 3.f * yy));
                         }
                     }
                 }
@@ -299,13 +330,14 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
                           4 * z * (DMT(1, 1) + DMT(0, 0));
 #undef DMT
             }
-        } else if (p.sh && p.dL_dsh && !accm) {
+        } else if (live && p.sh && p.dL_dsh && !accm) {
             if (p.sh_rest) {
                 float* __restrict__ d0 = p.dL_dsh + (size_t)idx * 3;
                 float* __restrict__ dr = p.dL_dsh_rest + (size_t)idx * (p.M - 1) * 3;
                 d0[0] = d0[1] = d0[2] = 0.f;
-                for (int k = 0; k < 3 * (p.M - 1); k++) dr[k] = 0.f;
-            } else {
+                if (!STAGED)
+                    for (int k = 0; k < 3 * (p.M - 1); k++) dr[k] = 0.f;
+            } else if (!STAGED) {
                 float* __restrict__ dsh = p.dL_dsh + (size_t)idx * p.M * 3;
                 for (int k = 0; k < 3 * p.M; k++) dsh[k] = 0.f;
             }
@@ -318,6 +350,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
 #pragma unroll
             for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q4[k] * qd) / qn;
         }
+        if (live) {
         if (p.dL_dmeans3D) { gput(p.dL_dmeans3D, 3 * idx, dmean.x, accm); gput(p.dL_dmeans3D, 3 * idx + 1, dmean.y, accm); gput(p.dL_dmeans3D, 3 * idx + 2, dmean.z, accm); }
         if (p.dL_dmeans2D) { gput(p.dL_dmeans2D, 3 * idx, dm2x, accm); gput(p.dL_dmeans2D, 3 * idx + 1, dm2y, accm); gput(p.dL_dmeans2D, 3 * idx + 2, 0.f, accm); }
         if (p.dL_dopacity) gput(p.dL_dopacity, idx, dop, accm);
@@ -330,6 +363,15 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
         if (p.dL_drotations) {
 #pragma unroll
             for (int k = 0; k < 4; k++) gput(p.dL_drotations, 4 * idx + k, drot[k], accm);
+        }
+        }
+    }
+    if (STAGED) {
+        // write the block's dL_dsh span back, coalesced; culled rows are zero (or left alone when accumulating)
+        __syncthreads();
+        float* __restrict__ dst = p.sh_rest ? p.dL_dsh_rest : p.dL_dsh;
+        if (dst) {
+            sh_stage_store<8>(sh_stage, s_vis, dst + sh_span0, sh_nw, sh_rw, sh_rs, accm);
         }
     }
     // ---- pose gradient: warp -> block -> grid, deterministic ----
@@ -370,9 +412,20 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
     }
 }
 
+static_assert(WGS_PRE_BWD_THREADS == SH_STAGE_THREADS, "staging helpers assume 256-thread blocks");
+
+int configure_preprocess_bwd() {
+    return (int)cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sh_stage_bytes(SH_STAGE_MAX_M));
+}
+
 void launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
-    if (p.P > 0)
-        preprocess_bwd_kernel<<<(p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS, WGS_PRE_BWD_THREADS, 0, s>>>(p);
+    if (p.P <= 0) return;
+    const int blocks = (p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS;
+    if (p.sh && p.M > 1 && p.M <= SH_STAGE_MAX_M)
+        preprocess_bwd_kernel<true><<<blocks, WGS_PRE_BWD_THREADS, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M), s>>>(p);
+    else
+        preprocess_bwd_kernel<false><<<blocks, WGS_PRE_BWD_THREADS, 0, s>>>(p);
 }
 
 }  // namespace wgs

@@ -6,6 +6,7 @@
 // reference (PTX-verified), so those outputs are bit-identical.
 #include "common.cuh"
 #include "kernels.h"
+#include "sh_stage.cuh"
 
 namespace wgs {
 
@@ -47,22 +48,25 @@ __device__ __forceinline__ void cov3d_from_scale_rot(const float* __restrict__ s
 
 // reference computeColorFromSH (forward.cu:22-73); returns rgb, sets clamp bits
 // sh: coefficient 0 (DC); shr: coefficients 1.. (shr = sh + 3 for the packed (P,M,3) layout)
+// SMEM: both pointers address the block's staged copy in shared memory (plain loads instead of ld.global.nc)
+template <bool SMEM>
 __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, const float* __restrict__ shr, int deg,
                                             float px, float py, float pz, const float* __restrict__ campos,
-                                            uint32_t& clampbits) {
+                                            uint32_t& clampbits, bool sh_global = false) {
     const float dx = SUB(px, __ldg(campos)), dy = SUB(py, __ldg(campos + 1)), dz = SUB(pz, __ldg(campos + 2));
     const float len = SQRT(FMA(dz, dz, FMA(dx, dx, MUL(dy, dy))));
     const float x = DIV(dx, len), y = DIV(dy, len), z = DIV(dz, len);
+    auto LD = [](const float* q) { return SMEM ? *q : __ldg(q); };
     float res[3];
 #pragma unroll
-    for (int c = 0; c < 3; c++) res[c] = MUL(__ldg(sh + c), kSH_C0);
+    for (int c = 0; c < 3; c++) res[c] = MUL(SMEM && sh_global ? __ldg(sh + c) : LD(sh + c), kSH_C0);
     if (deg > 0) {
         const float t1 = MUL(y, kSH_C1), t2 = MUL(z, kSH_C1), t3 = MUL(x, kSH_C1);
 #pragma unroll
         for (int c = 0; c < 3; c++) {
-            float v = FMA(-t1, __ldg(shr + c), res[c]);
-            v = FMA(t2, __ldg(shr + 3 + c), v);
-            res[c] = FMA(-t3, __ldg(shr + 6 + c), v);
+            float v = FMA(-t1, LD(shr + c), res[c]);
+            v = FMA(t2, LD(shr + 3 + c), v);
+            res[c] = FMA(-t3, LD(shr + 6 + c), v);
         }
         if (deg > 1) {
             const float xx = MUL(x, x), yy = MUL(y, y), zz = MUL(z, z), xy = MUL(x, y), yz = MUL(y, z),
@@ -73,11 +77,11 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, const 
                         b8 = MUL(xx_yy, kSH_C2[4]);
 #pragma unroll
             for (int c = 0; c < 3; c++) {
-                float v = FMA(b4, __ldg(shr + 9 + c), res[c]);
-                v = FMA(b5, __ldg(shr + 12 + c), v);
-                v = FMA(b6, __ldg(shr + 15 + c), v);
-                v = FMA(b7, __ldg(shr + 18 + c), v);
-                res[c] = FMA(b8, __ldg(shr + 21 + c), v);
+                float v = FMA(b4, LD(shr + 9 + c), res[c]);
+                v = FMA(b5, LD(shr + 12 + c), v);
+                v = FMA(b6, LD(shr + 15 + c), v);
+                v = FMA(b7, LD(shr + 18 + c), v);
+                res[c] = FMA(b8, LD(shr + 21 + c), v);
             }
             if (deg > 2) {
                 const float w = SUB(FMA(zz, 4.f, -xx), yy);
@@ -90,13 +94,13 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, const 
                 const float b15 = MUL(MUL(x, kSH_C3[6]), FMA(yy, -3.f, xx));
 #pragma unroll
                 for (int c = 0; c < 3; c++) {
-                    float v = FMA(b9, __ldg(shr + 24 + c), res[c]);
-                    v = FMA(b10, __ldg(shr + 27 + c), v);
-                    v = FMA(b11, __ldg(shr + 30 + c), v);
-                    v = FMA(b12, __ldg(shr + 33 + c), v);
-                    v = FMA(b13, __ldg(shr + 36 + c), v);
-                    v = FMA(b14, __ldg(shr + 39 + c), v);
-                    res[c] = FMA(b15, __ldg(shr + 42 + c), v);
+                    float v = FMA(b9, LD(shr + 24 + c), res[c]);
+                    v = FMA(b10, LD(shr + 27 + c), v);
+                    v = FMA(b11, LD(shr + 30 + c), v);
+                    v = FMA(b12, LD(shr + 33 + c), v);
+                    v = FMA(b13, LD(shr + 36 + c), v);
+                    v = FMA(b14, LD(shr + 39 + c), v);
+                    res[c] = FMA(b15, LD(shr + 42 + c), v);
                 }
             }
         }
@@ -110,19 +114,26 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, const 
     return make_float3(res[0], res[1], res[2]);
 }
 
+// STAGED (1 < M <= 16, SH colours): once visibility is known, the SH rows of the block's visible Gaussians -- one
+// contiguous span of global memory -- are copied into shared memory with coalesced loads and every thread reads
+// its row from there; per-thread row reads (192-B stride at M = 16) reached only 2.9 TB/s at config 4.
+template <bool STAGED>
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_constant__ PreFwdParams p) {
+    extern __shared__ float sh_stage[];
+    __shared__ uint8_t s_vis[256];
     const int idx = blockIdx.x * 256 + threadIdx.x;
     const int lane = threadIdx.x & 31;
     uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
     bool visible = false;
+    float px = 0.f, py = 0.f, pz = 0.f, depth = 0.f;
+    float mx = 0.f, my = 0.f, cnx = 0.f, cny = 0.f, cnz = 0.f;
     if (idx < p.P) {
         const float* __restrict__ V = p.viewmatrix;
         const float* __restrict__ Pm = p.projmatrix;
-        const float px = __ldg(p.means3D + 3 * idx), py = __ldg(p.means3D + 3 * idx + 1),
-                    pz = __ldg(p.means3D + 3 * idx + 2);
-        const float depth = dot3p(px, py, pz, V[2], V[6], V[10], V[14]);
+        px = __ldg(p.means3D + 3 * idx); py = __ldg(p.means3D + 3 * idx + 1);
+        pz = __ldg(p.means3D + 3 * idx + 2);
+        depth = dot3p(px, py, pz, V[2], V[6], V[10], V[14]);
         int radius = 0;
-        float mx = 0.f, my = 0.f, cnx = 0.f, cny = 0.f, cnz = 0.f;
         if (depth <= 0.2f) {  // in_frustum (auxiliary.h:139-164)
             if (p.prefiltered) p.tile.misc[MISC_PREFILTER_HIT] = 1;
         } else {
@@ -179,6 +190,18 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
         }
         p.radii[idx] = radius;
         p.n_touched[idx] = 0;
+    }
+    const int sh_rw = STAGED ? (p.sh_rest ? 3 * (p.M - 1) : 3 * p.M) : 1;
+    const int sh_rs = sh_row_stride(sh_rw);
+    if (STAGED) {
+        s_vis[threadIdx.x] = visible;
+        __syncthreads();
+        const float* __restrict__ src = (p.sh_rest ? p.sh_rest : p.sh) + (size_t)blockIdx.x * 256 * sh_rw;
+        const uint32_t nw = (uint32_t)min(256, p.P - (int)(blockIdx.x * 256)) * sh_rw;
+        sh_stage_load(sh_stage, s_vis, src, nw, sh_rw, sh_rs);
+        __syncthreads();
+    }
+    if (idx < p.P) {
         if (visible) {
             float3 rgb;
             uint32_t cb = 0;
@@ -186,9 +209,16 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
                 rgb = make_float3(__ldg(p.colors_precomp + 3 * idx), __ldg(p.colors_precomp + 3 * idx + 1),
                                   __ldg(p.colors_precomp + 3 * idx + 2));
             } else {
-                const float* sh0 = p.sh_rest ? p.sh + (size_t)idx * 3 : p.sh + (size_t)idx * p.M * 3;
-                const float* shr = p.sh_rest ? p.sh_rest + (size_t)idx * (p.M - 1) * 3 : sh0 + 3;
-                rgb = sh_to_rgb(sh0, shr, p.D, px, py, pz, p.campos, cb);
+                if (STAGED) {
+                    // packed rows hold the DC term too; in the dc | rest split it stays a (near-coalesced) global read
+                    const float* srow = sh_stage + threadIdx.x * sh_rs;
+                    if (p.sh_rest) rgb = sh_to_rgb<true>(p.sh + (size_t)idx * 3, srow, p.D, px, py, pz, p.campos, cb, true);
+                    else rgb = sh_to_rgb<true>(srow, srow + 3, p.D, px, py, pz, p.campos, cb);
+                } else {
+                    const float* sh0 = p.sh_rest ? p.sh + (size_t)idx * 3 : p.sh + (size_t)idx * p.M * 3;
+                    const float* shr = p.sh_rest ? p.sh_rest + (size_t)idx * (p.M - 1) * 3 : sh0 + 3;
+                    rgb = sh_to_rgb<false>(sh0, shr, p.D, px, py, pz, p.campos, cb);
+                }
             }
             float o = __ldg(p.opacities + idx);
             if (p.act) o = DIV(1.f, ADD(1.f, expf(-o)));  // torch.sigmoid (gaussian_model.py:59,95-97)
@@ -230,8 +260,17 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
     present[idx] = !(depth <= 0.2f);
 }
 
+int configure_preprocess_fwd() {
+    return (int)cudaFuncSetAttribute(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sh_stage_bytes(SH_STAGE_MAX_M));
+}
+
 void launch_preprocess_fwd(const PreFwdParams& p, cudaStream_t s) {
-    if (p.P > 0) preprocess_fwd_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p);
+    if (p.P <= 0) return;
+    if (p.sh && !p.colors_precomp && p.M > 1 && p.M <= SH_STAGE_MAX_M)
+        preprocess_fwd_kernel<true><<<(p.P + 255) / 256, 256, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M), s>>>(p);
+    else
+        preprocess_fwd_kernel<false><<<(p.P + 255) / 256, 256, 0, s>>>(p);
 }
 void launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s) {
     if (P > 0) mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, V, present);
