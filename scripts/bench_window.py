@@ -34,6 +34,8 @@ def main():
                     help="bucket in NVLink peer memory, summed by wgs_peer_allreduce instead of NCCL")
     ap.add_argument("--strips", action="store_true",
                     help="sub-frame units (tile-row strips) when the window does not divide by the world size")
+    ap.add_argument("--graph", action="store_true",
+                    help="capture the rank's whole window step (all its units + the peer allreduce) in one CUDA graph")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -74,10 +76,17 @@ def main():
         return loss, (lambda: torch.cat([vw["rho"].grad.reshape(-1), vw["theta"].grad.reshape(-1)]))
 
     def step():
-        return trainer.step(n_views, render_loss, cost_fn=None if a.strips else (lambda v: last_R.get(v, 1.0)),
+        return trainer.step(n_views, render_loss, cost_fn=None if (a.strips or a.graph) else (lambda v: last_R.get(v, 1.0)),
                             tile_rows=(H + 15) // 16 if a.strips else None)
 
     flush = torch.zeros((512 << 20) // 4, device=dev)
+    if a.graph:
+        if world > 1 and a.peer == "off":
+            raise SystemExit("--graph needs --peer (an NCCL allreduce is not captured here)")
+        from wildgs_slam_blackwell_b200 import graph
+        eager_out = step()
+        it = graph.CapturedIteration(lambda: step()["losses"], dev, warmup=2)
+        eager_step, step = step, (lambda: (it.replay(), eager_out)[1])
     for _ in range(a.warmup):
         step()
         flush.add_(1)
@@ -107,7 +116,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": f"{a.workload}: {P} Gaussians, {n_views} keyframes {W}x{H}, SH degree {deg}",
                        "assignment": out["assignment"], "bucket_bytes": out["bucket_bytes"],
-                       "grad_sink": not a.no_sink, "strips": a.strips, "allreduce": "nccl" if a.peer == "off" or world == 1 else "peer:" + a.peer, "l2": "flushed between steps"}}), flush=True)
+                       "grad_sink": not a.no_sink, "strips": a.strips, "cuda_graph": a.graph, "allreduce": "nccl" if a.peer == "off" or world == 1 else "peer:" + a.peer, "l2": "flushed between steps"}}), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -50,24 +50,24 @@ __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const 
     c[5] = M[6] * M[6] + M[7] * M[7] + M[8] * M[8];
 }
 
-// STAGED (1 < M <= 16): the block's SH rows -- one contiguous span of global memory -- are copied into shared
-// memory with coalesced loads (rows of culled Gaussians skipped), each thread reads its coefficients and leaves its
-// dL_dsh there in place, and the span is written back coalesced (zeros for culled rows).  Per-thread row access
-// to global memory (192-B stride) moved 1.9 GB for 1.2 GB of algorithmic traffic at config 4.
+// STAGED (1 < M <= 16): every warp moves the SH rows of its 32 Gaussians -- one contiguous span of global memory --
+// through shared memory (sh_stage.cuh): coalesced cp.async in (rows of culled Gaussians skipped), each thread reads
+// its coefficients and leaves its dL_dsh there in place, coalesced write-back (zeros for culled rows).  Per-thread
+// row access to global memory (192-B stride) moved 1.9 GB for 1.2 GB of algorithmic traffic at config 4.
 template <bool STAGED>
 __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
     extern __shared__ float sh_stage[];
-    __shared__ uint8_t s_vis[WGS_PRE_BWD_THREADS];
     const int gidx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
     const bool live = gidx < p.P;
     const int idx = live ? gidx : p.P - 1;  // dead threads of the last block shadow its last Gaussian, write nothing
     const bool accm = p.accumulate != 0;
     float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    // staged SH span of this block: packed (P,M,3) rows, or the (P,M-1,3) rest rows in raw-parameter mode
+    // staged SH rows of this warp: packed (P,M,3) rows, or the (P,M-1,3) rest rows in raw-parameter mode
     const int sh_rw = STAGED ? (p.sh_rest ? 3 * (p.M - 1) : 3 * p.M) : 1;
     const int sh_rs = sh_row_stride(sh_rw);
-    const size_t sh_span0 = (size_t)blockIdx.x * WGS_PRE_BWD_THREADS * sh_rw;
-    const uint32_t sh_nw = (uint32_t)min(WGS_PRE_BWD_THREADS, p.P - (int)(blockIdx.x * WGS_PRE_BWD_THREADS)) * sh_rw;
+    const int wrow0 = blockIdx.x * WGS_PRE_BWD_THREADS + (threadIdx.x & ~31);  // first Gaussian of the warp
+    float* const wstage = sh_stage + (threadIdx.x & ~31) * sh_rs;
+    unsigned vmask = 0;
     {
         // Issue every load this Gaussian can need before looking at radii, so that the latencies
         // overlap (the kernel is latency-bound: 108 registers, 2 CTAs/SM).  Accumulator records of
@@ -98,10 +98,8 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
         const float4 ra = __ldcg(p.geom.rec + 2 * idx), rb = __ldcg(p.geom.rec + 2 * idx + 1);
         const bool vis = live && rad > 0 && rect.x != rect.y;  // rect is empty outside the rendered strip
         if (STAGED) {
-            s_vis[threadIdx.x] = vis;
-            __syncthreads();
-            sh_stage_load(sh_stage, s_vis, (p.sh_rest ? p.sh_rest : p.sh) + sh_span0, sh_nw, sh_rw, sh_rs);
-            __syncthreads();
+            vmask = __ballot_sync(0xffffffffu, vis);
+            sh_stage_load(wstage, (p.sh_rest ? p.sh_rest : p.sh) + (size_t)wrow0 * sh_rw, vmask, sh_rw, sh_rs);
         }
         if (vis) {
             const float4 z4 = make_float4(0, 0, 0, 0);
@@ -233,7 +231,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
                 const float x = dir_orig.x * il, y = dir_orig.y * il, z = dir_orig.z * il;
                 // STAGED: coefficient k of this thread's row sits at srow + 3 (k + koff); dL_dsh replaces it in place,
                 // so every band reads its coefficients before it puts its gradients
-                float* __restrict__ srow = sh_stage + threadIdx.x * sh_rs;
+                float* __restrict__ srow = sh_stage + threadIdx.x * sh_rs;  // == wstage + lane * sh_rs
                 const int koff = p.sh_rest ? -1 : 0;
                 auto SH = [&](int k) {  // only called with k >= 1
                     if (STAGED) return V3{srow[3 * (k + koff)], srow[3 * (k + koff) + 1], srow[3 * (k + koff) + 2]};
@@ -367,12 +365,9 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
         }
     }
     if (STAGED) {
-        // write the block's dL_dsh span back, coalesced; culled rows are zero (or left alone when accumulating)
-        __syncthreads();
-        float* __restrict__ dst = p.sh_rest ? p.dL_dsh_rest : p.dL_dsh;
-        if (dst) {
-            sh_stage_store<8>(sh_stage, s_vis, dst + sh_span0, sh_nw, sh_rw, sh_rs, accm);
-        }
+        float* dst = p.sh_rest ? p.dL_dsh_rest : p.dL_dsh;
+        if (dst && wrow0 < p.P)
+            sh_stage_store(wstage, dst + (size_t)wrow0 * sh_rw, vmask, (uint32_t)min(32, p.P - wrow0), sh_rw, sh_rs, accm);
     }
     // ---- pose gradient: warp -> block -> grid, deterministic ----
     __shared__ float s_part[WGS_PRE_BWD_THREADS / 32][6];

@@ -114,13 +114,12 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, const 
     return make_float3(res[0], res[1], res[2]);
 }
 
-// STAGED (1 < M <= 16, SH colours): once visibility is known, the SH rows of the block's visible Gaussians -- one
-// contiguous span of global memory -- are copied into shared memory with coalesced loads and every thread reads
-// its row from there; per-thread row reads (192-B stride at M = 16) reached only 2.9 TB/s at config 4.
+// STAGED (1 < M <= 16, SH colours): once visibility is known, every warp copies the SH rows of its visible
+// Gaussians -- contiguous in global memory -- into shared memory with coalesced cp.async (sh_stage.cuh) and each
+// thread reads its row from there; per-thread row reads (192-B stride at M = 16) reached only 2.9 TB/s at config 4.
 template <bool STAGED>
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_constant__ PreFwdParams p) {
     extern __shared__ float sh_stage[];
-    __shared__ uint8_t s_vis[256];
     const int idx = blockIdx.x * 256 + threadIdx.x;
     const int lane = threadIdx.x & 31;
     uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
@@ -194,12 +193,9 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
     const int sh_rw = STAGED ? (p.sh_rest ? 3 * (p.M - 1) : 3 * p.M) : 1;
     const int sh_rs = sh_row_stride(sh_rw);
     if (STAGED) {
-        s_vis[threadIdx.x] = visible;
-        __syncthreads();
-        const float* __restrict__ src = (p.sh_rest ? p.sh_rest : p.sh) + (size_t)blockIdx.x * 256 * sh_rw;
-        const uint32_t nw = (uint32_t)min(256, p.P - (int)(blockIdx.x * 256)) * sh_rw;
-        sh_stage_load(sh_stage, s_vis, src, nw, sh_rw, sh_rs);
-        __syncthreads();
+        const int wrow0 = blockIdx.x * 256 + (threadIdx.x & ~31);
+        sh_stage_load(sh_stage + (threadIdx.x & ~31) * sh_rs, (p.sh_rest ? p.sh_rest : p.sh) + (size_t)wrow0 * sh_rw,
+                      __ballot_sync(0xffffffffu, visible), sh_rw, sh_rs);
     }
     if (idx < p.P) {
         if (visible) {

@@ -1,71 +1,65 @@
-// Staging of a block's SH rows through shared memory (preprocess_fwd / preprocess_bwd, 1 < M <= 16).
-// The rows of the 256 Gaussians of a block form one contiguous span of global memory.  The span is brought in with
-// cp.async (no register staging, so every word of the span is in flight at once): 16-byte copies of the whole span
-// when the shared-memory rows are unpadded and the span is 16-byte aligned, else 4-byte copies with consecutive
-// lanes on consecutive words (coalesced for any row size), rows of culled Gaussians skipped.  Rows in shared memory
-// have an odd stride, so per-thread row access is conflict-free.  row = word / row_words is one mul.hi.
+// Staging of SH rows through shared memory (preprocess_fwd / preprocess_bwd, 1 < M <= 16), warp-local.
+// The rows of the 32 Gaussians of a warp form one contiguous span of global memory.  The warp brings in the rows of
+// its visible Gaussians one row per step -- lanes on consecutive words, so every request is a contiguous 128-B (+
+// remainder) piece whatever the row size -- with cp.async (no register staging: all rows are in flight at once),
+// each lane then reads ITS row from shared memory (odd row stride: conflict-free) and, in the backward pass,
+// leaves its dL_dsh there; the warp writes the rows back the same way.  Only the warp touches its rows, so the
+// steps are ordered by __syncwarp alone and the warps of a block run their phases independently.
 #pragma once
 #include <cstdint>
 
 namespace wgs {
 
-constexpr int SH_STAGE_MAX_M = 16;
+constexpr int SH_STAGE_MAX_M = 16;        // rows of at most 48 words: two requests per row
 constexpr int SH_STAGE_THREADS = 256;
 __host__ __device__ inline int sh_row_stride(int row_words) { return row_words | 1; }
 inline size_t sh_stage_bytes(int M) { return (size_t)SH_STAGE_THREADS * sh_row_stride(3 * M) * sizeof(float); }
 
-// exact floor(w / rw) for w < 2^16, rw <= 48:  umulhi(w, ceil(2^32 / rw))
-__device__ __forceinline__ uint32_t sh_div_magic(uint32_t rw) { return 0xFFFFFFFFu / rw + 1u; }
-
-__device__ __forceinline__ void sh_stage_load(float* stage, const uint8_t* vis, const float* __restrict__ src,
-                                              uint32_t nw, uint32_t rw, uint32_t rs) {
-    const uint32_t pad = rs - rw;
-    if (pad == 0 && ((uintptr_t)src & 15u) == 0 && (nw & 3u) == 0) {
-        for (uint32_t w = 4 * threadIdx.x; w < nw; w += 4 * SH_STAGE_THREADS) {
-            const unsigned s = (unsigned)__cvta_generic_to_shared(stage + w);
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(src + w) : "memory");
-        }
-    } else {
-        const uint32_t magic = sh_div_magic(rw);
-#pragma unroll 4
-        for (uint32_t w = threadIdx.x; w < nw; w += SH_STAGE_THREADS) {
-            const uint32_t row = __umulhi(w, magic);
-            if (vis[row]) {
-                const unsigned s = (unsigned)__cvta_generic_to_shared(stage + w + row * pad);
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(src + w) : "memory");
-            }
-        }
-    }
-    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+__device__ __forceinline__ void sh_cp_async4(float* smem_dst, const float* gsrc) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gsrc) : "memory");
 }
 
-// dst[w] = stage (0 for culled rows), or dst[w] += stage for the visible rows when accumulating
-template <int U>
-__device__ __forceinline__ void sh_stage_store(const float* stage, const uint8_t* vis, float* __restrict__ dst,
-                                               uint32_t nw, uint32_t rw, uint32_t rs, bool accumulate) {
-    const uint32_t pad = rs - rw, magic = sh_div_magic(rw);
-    for (uint32_t w0 = threadIdx.x; w0 < nw; w0 += SH_STAGE_THREADS * U) {
-        float v[U];
-        bool pin[U], pv[U];
-#pragma unroll
-        for (int j = 0; j < U; j++) {
-            const uint32_t w = w0 + SH_STAGE_THREADS * j;
-            const uint32_t row = __umulhi(w, magic);
-            pin[j] = w < nw;
-            pv[j] = pin[j] && vis[row];
-            v[j] = pv[j] ? stage[w + row * pad] : 0.f;
+// wstage / wsrc: the warp's first row in shared / global memory; vmask: ballot of the lanes' visibility
+__device__ __forceinline__ void sh_stage_load(float* wstage, const float* __restrict__ wsrc, unsigned vmask,
+                                              uint32_t rw, uint32_t rs) {
+    const uint32_t lane = threadIdx.x & 31;
+    const bool second = lane + 32 < rw, first = lane < rw;
+    while (vmask) {
+        const uint32_t i = __ffs(vmask) - 1;
+        vmask &= vmask - 1;
+        float* d = wstage + i * rs + lane;
+        const float* s = wsrc + i * rw + lane;
+        if (first) sh_cp_async4(d, s);
+        if (second) sh_cp_async4(d + 32, s + 32);
+    }
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+    __syncwarp();
+}
+
+// rows [0, nrows) of the warp: wdst = staged row (0 for culled rows), or += for the visible rows when accumulating
+__device__ __forceinline__ void sh_stage_store(const float* wstage, float* __restrict__ wdst, unsigned vmask,
+                                               uint32_t nrows, uint32_t rw, uint32_t rs, bool accumulate) {
+    const uint32_t lane = threadIdx.x & 31;
+    const bool second = lane + 32 < rw, first = lane < rw;
+    __syncwarp();
+    if (accumulate) {
+        while (vmask) {
+            const uint32_t i = __ffs(vmask) - 1;
+            vmask &= vmask - 1;
+            const float* s = wstage + i * rs + lane;
+            float* d = wdst + i * rw + lane;
+            if (first) d[0] += s[0];
+            if (second) d[32] += s[32];
         }
-        if (accumulate) {
-#pragma unroll
-            for (int j = 0; j < U; j++)
-                if (pv[j]) v[j] += dst[w0 + SH_STAGE_THREADS * j];
-#pragma unroll
-            for (int j = 0; j < U; j++)
-                if (pv[j]) dst[w0 + SH_STAGE_THREADS * j] = v[j];
-        } else {
-#pragma unroll
-            for (int j = 0; j < U; j++)
-                if (pin[j]) dst[w0 + SH_STAGE_THREADS * j] = v[j];
+    } else {
+#pragma unroll 4
+        for (uint32_t i = 0; i < nrows; i++) {
+            const bool v = (vmask >> i) & 1u;
+            const float* s = wstage + i * rs + lane;
+            float* d = wdst + i * rw + lane;
+            if (first) d[0] = v ? s[0] : 0.f;
+            if (second) d[32] = v ? s[32] : 0.f;
         }
     }
 }

@@ -65,8 +65,10 @@ class GradBucket:
     per-leaf views into it.  Installing the views as `.grad` makes autograd accumulate straight into
     the buffer, so the allreduce needs no packing copy."""
 
-    def __init__(self, params: Dict[str, torch.Tensor], peer_group=None, peer_mode: str = "auto"):
-        """peer_group: a process group whose ranks share one NVLink domain -> the buffer is allocated in
+    def __init__(self, params: Dict[str, torch.Tensor], peer_group=None, peer_mode: str = "auto", side_floats: int = 0):
+        """side_floats: extra floats behind the gradients (`self.side`) that ride in the same allreduce -- the window's
+        per-view losses / costs / pose gradients, so that a step is ONE collective.
+        peer_group: a process group whose ranks share one NVLink domain -> the buffer is allocated in
         symmetric peer memory (peer.PeerBucket) and all_reduce() runs the library's own kernel instead of
         ncclAllReduce.  peer_mode: 'nvls' | 'p2p' | 'auto' (multicast from 4 ranks up)."""
         self.names = list(params)
@@ -78,10 +80,11 @@ class GradBucket:
             from .peer import PeerBucket
             world = dist.get_world_size(peer_group)
             mc = peer_mode == "nvls" or (peer_mode == "auto" and world >= 4)
-            self.peer = PeerBucket(n, first.device, peer_group, use_multicast=mc)
-            self.flat = self.peer.flat
+            self.peer = PeerBucket(n + side_floats, first.device, peer_group, use_multicast=mc)
+            self._all = self.peer.flat
         else:
-            self.flat = torch.zeros(n, dtype=torch.float32, device=first.device)
+            self._all = torch.zeros(n + side_floats, dtype=torch.float32, device=first.device)
+        self.flat, self.side = self._all[:n], self._all[n:]
         self.views: Dict[str, torch.Tensor] = {}
         off = 0
         for k, p in params.items():
@@ -110,7 +113,7 @@ class GradBucket:
         if self.peer is not None:
             self.peer.all_reduce()
             return None
-        return dist.all_reduce(self.flat, group=group, async_op=async_op)
+        return dist.all_reduce(self._all, group=group, async_op=async_op)
 
 
 class WindowTrainer:
@@ -124,6 +127,29 @@ class WindowTrainer:
     every leaf's .grad holds the gradient summed over ALL views of the window (identical on every
     rank), `out["losses"]` (n_views,), `out["pose_grads"]` (n_views, 6), `out["assignment"]`.
     """
+
+    SIDE_FLOATS = 8 * 64   # (loss, cost, pose gradient) of up to 64 views ride behind the gradients in the bucket
+
+    def _side(self, n_views):
+        """(n_views, 8) zeroed side block: inside the bucket when it fits (one collective per step), else its own."""
+        b = self.bucket
+        if 8 * n_views <= b.side.numel():
+            b.side.zero_()
+            return b.side[:8 * n_views].view(n_views, 8), True
+        return torch.zeros(n_views, 8, dtype=torch.float32, device=b.flat.device), False
+
+    def _finish(self, side, fused, cost_fn, assignment):
+        b = self.bucket
+        if self.world > 1:
+            work = b.all_reduce(self.group, async_op=True)
+            if not fused:
+                dist.all_reduce(side, group=self.group)
+            if work is not None:
+                work.wait()
+        side = side.clone() if fused else side
+        if cost_fn is not None:   # measured costs feed the next assignment: the step's one host synchronisation
+            self.costs = [float(c) for c in side[:, 1].tolist()]
+        return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": assignment, "bucket_bytes": b.nbytes}
 
     def __init__(self, params: Dict[str, torch.Tensor], group: Optional[dist.ProcessGroup] = None,
                  sink_names: Optional[Dict[str, str]] = None, peer: bool = False, peer_mode: str = "auto"):
@@ -140,13 +166,13 @@ class WindowTrainer:
         # peer=True: bucket in NVLink peer memory, summed by wgs_peer_allreduce (single node, CUDA only)
         self._peer_group = (group if group is not None else dist.group.WORLD) if (peer and self.world > 1) else None
         self._peer_mode = peer_mode
-        self.bucket = GradBucket(params, self._peer_group, peer_mode)
+        self.bucket = GradBucket(params, self._peer_group, peer_mode, self.SIDE_FLOATS)
         self.costs: List[float] = []
 
     def rebind(self, params: Dict[str, torch.Tensor]):
         """Call after densify/prune changed the number of Gaussians."""
         if not self.bucket.matches(params):
-            self.bucket = GradBucket(params, self._peer_group, self._peer_mode)
+            self.bucket = GradBucket(params, self._peer_group, self._peer_mode, self.SIDE_FLOATS)
         else:
             self.bucket.params = params
 
@@ -171,8 +197,7 @@ class WindowTrainer:
                 p.grad = None
         else:
             b.install()
-        dev = b.flat.device
-        side = torch.zeros(n_views, 8, dtype=torch.float32, device=dev)  # loss, cost, pose grad (6)
+        side, fused = self._side(n_views)  # loss, cost, pose grad (6)
         for n_done, v in enumerate(mine):
             loss, pose_grad_fn = render_loss(v)
             if use_sink:
@@ -181,19 +206,12 @@ class WindowTrainer:
             else:
                 loss.backward()
             side[v, 0] = loss.detach()
-            side[v, 1] = float(cost_fn(v)) if cost_fn is not None else 1.0
+            side[v, 1].fill_(float(cost_fn(v)) if cost_fn is not None else 1.0)  # fill_: no H2D copy (graph capture)
             if pose_grad_fn is not None:
                 side[v, 2:8] = pose_grad_fn().reshape(6)
         if use_sink:
             b.install(zero=False)
-        if self.world > 1:
-            work = b.all_reduce(self.group, async_op=True)
-            dist.all_reduce(side, group=self.group)
-            if work is not None:
-                work.wait()
-        self.costs = [float(c) for c in side[:, 1].tolist()]
-        return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": assignment,
-                "bucket_bytes": b.nbytes}
+        return self._finish(side, fused, cost_fn, assignment)
 
     def _step_strips(self, n_views, render_loss, cost_fn, tile_rows):
         from . import rasterizer
@@ -207,7 +225,7 @@ class WindowTrainer:
                 p.grad = None
         else:
             b.install()
-        side = torch.zeros(n_views, 8, dtype=torch.float32, device=b.flat.device)
+        side, fused = self._side(n_views)
         for n_done, (v, r0, r1) in enumerate(mine):
             whole = r0 == 0 and r1 == tile_rows
             with rasterizer.tile_rows(r0, r1) if not whole else _null():
@@ -218,17 +236,12 @@ class WindowTrainer:
                 else:
                     loss.backward()
             side[v, 0] += loss.detach()
-            side[v, 1] += float(cost_fn(v)) if cost_fn is not None else (r1 - r0) / tile_rows
+            side[v, 1].add_(float(cost_fn(v)) if cost_fn is not None else (r1 - r0) / tile_rows)
             if pose_grad_fn is not None:
                 side[v, 2:8] += pose_grad_fn().reshape(6)
         if use_sink:
             b.install(zero=False)
-        work = b.all_reduce(self.group, async_op=True)
-        dist.all_reduce(side, group=self.group)
-        if work is not None:
-            work.wait()
-        self.costs = [float(c) for c in side[:, 1].tolist()]
-        return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": plan, "bucket_bytes": b.nbytes}
+        return self._finish(side, fused, cost_fn, plan)
 
 
 class _null:
