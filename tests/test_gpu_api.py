@@ -320,3 +320,41 @@ def test_tile_row_strips_sum_to_the_whole_image():
     with pytest.raises(RuntimeError, match="tile_rows"):
         with rasterizer.tile_rows(4, 11):
             rasterizer.GaussianRasterizer(s)(m3, m2, op, shs=sh, scales=sc, rotations=ro, theta=th, rho=rh)
+
+
+@pytest.mark.parametrize("P,deg,active", [(5003, 1, 1), (5003, 2, 2), (2999, 3, 3), (4001, 3, 1), (37, 2, 0)])
+def test_staged_sh_rows_match_cpu_oracle(P, deg, active):
+    """SH degrees 1-3 (M = 4, 9, 16) go through the shared-memory staging of preprocess fwd/bwd: ragged P (partial
+    last warp and block), active degree below the stored one (inactive bands get zero gradients), and the
+    accumulating write-back (grad_sink) -- all against the C oracle."""
+    g, cams, cots = scenes.make_scene(P, 176, 120, deg, seed=70 + deg)
+    g = dict(g, sh_degree=active)
+    ours = util.run_ours(g, cams[0], cots[0])
+    o = cpu_oracle.forward_backward(g, cams[0], cots[0], export=True)
+    np.testing.assert_array_equal(ours["radii"], o["radii"])
+    np.testing.assert_array_equal(ours["st_point_list"].view(np.uint32), o["st_point_list"])
+    vis = o["radii"] > 0
+    np.testing.assert_allclose(ours["st_rgb"][vis], o["st_rgb"][vis], rtol=1e-5, atol=1e-6)      # SH -> RGB
+    assert (ours["st_clamped"][vis].astype(bool) != o["st_clamped"][vis].astype(bool)).mean() < 1e-3   # rgb within 1 ulp of 0
+    for k in ("g_dL_dsh", "g_dL_dmeans3D"):
+        ref = o[k]
+        bad = np.abs(ours[k] - ref) > 1e-3 * np.abs(ref) + 1e-4 * np.abs(ref).max()
+        assert bad.mean() < 2e-3, k
+    M = (deg + 1) ** 2
+    assert ours["g_dL_dsh"].shape == (P, M, 3)
+    assert not ours["g_dL_dsh"][:, (active + 1) ** 2:].any()         # inactive bands
+    assert not ours["g_dL_dsh"][~vis].any()                          # culled rows are written as zeros
+    # accumulating write-back: second backward into the same buffers doubles them
+    s = util.settings_from_cam(cams[0], active)
+    leaf = lambda a: util.to_dev(a).requires_grad_(True)
+    m3, op, sh, sc, ro = leaf(g["means3D"]), leaf(g["opacities"]), leaf(g["sh"]), leaf(g["scales"]), leaf(g["rotations"])
+    m2 = torch.zeros(P, 3, device=DEV, requires_grad=True)
+    bufs = {"means3D": torch.full_like(m3, 3.0), "sh": torch.full_like(sh, 3.0), "opacity": torch.full_like(op, 3.0),
+            "scales": torch.full_like(sc, 3.0), "rotations": torch.full_like(ro, 3.0)}
+    dc, dd = util.to_dev(cots[0][0]), util.to_dev(cots[0][1])
+    rast = rasterizer.GaussianRasterizer(s)
+    for k in range(2):
+        color, radii, depth, opacity, n_touched = rast(m3, m2, op, shs=sh, scales=sc, rotations=ro)
+        with rasterizer.grad_sink(bufs, accumulate=k > 0):
+            ((color * dc).sum() + (depth * dd).sum()).backward()
+        util.assert_grad_close("sh", bufs["sh"].cpu().numpy(), (k + 1.0) * ours["g_dL_dsh"])
