@@ -1,6 +1,7 @@
 """CPU: the numpy loss oracle (oracle/loss_oracle.py) against the golden vectors produced by the
 REFERENCE's own get_loss_tracking / get_loss_mapping (tests/golden/make_loss_golden.py), the ctypes
 struct against include/wgs_loss.h, and the exported symbols."""
+import ctypes as C
 import os
 import re
 import sys
@@ -139,3 +140,47 @@ def test_compact_abi_symbols():
     assert names == [f[0] for f in compaction.CompactTensor._fields_]
     assert lib.wgs_compact_workspace_bytes(3_000_000) >= 2930 * 4
     assert lib.wgs_compact_plan(-1, None, None, None, None, None) == _lib.WGS_ERR_INVALID_ARGUMENT
+
+
+@pytest.mark.parametrize("name", ["ssim_a", "ssim_b", "ssim_batch"])
+def test_ssim_oracle_matches_reference_golden(name):
+    """oracle/ssim_oracle.py (numpy float64) against vectors made by the reference's loss_utils.ssim (+ autograd) and
+    mapping_utils.compute_ssim_components (tests/golden/make_ssim_golden.py)."""
+    from oracle import ssim_oracle
+    d = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    a, b = d["img1"], d["img2"]
+    batched = a.ndim == 4
+    val = ssim_oracle.ssim(a, b, 11, size_average=not batched)
+    np.testing.assert_allclose(val, d["ssim"], rtol=2e-5, atol=2e-6)
+    items = list(zip(a, b, d["dmean"], d["grad"])) if batched else [(a, b, d["dmean"], d["grad"])]
+    for x, y, g, want in items:
+        got = float(g) * ssim_oracle.ssim_grad(x, y, 11)
+        np.testing.assert_allclose(got, want, rtol=2e-3, atol=2e-4 * np.abs(want).max())   # the golden is float32 torch
+    for ws in (7, 11):
+        for x, y, k in (zip(a, b, range(len(a))) if batched else [(a, b, None)]):
+            lum, con, stu = ssim_oracle.components(y, x, ws)
+            pick = (lambda t: t[k]) if batched else (lambda t: t)
+            np.testing.assert_allclose(lum, pick(d[f"lum{ws}"]), rtol=1e-4, atol=1e-5)
+            # variances are E[x^2] - mu^2 in float32 in the reference: on smooth images the cancellation noise
+            # (~1e-7 against variances of ~1e-4) shows in contrast and structure at the 1e-3 level
+            np.testing.assert_allclose(con, pick(d[f"con{ws}"]), rtol=1e-4, atol=5e-3)
+            bad = np.abs(stu - pick(d[f"str{ws}"])) > 5e-3      # ill-conditioned where both variances vanish
+            assert bad.mean() < 5e-3
+
+
+def test_ssim_abi_symbols():
+    from wildgs_slam_blackwell_b200 import loss_utils
+    header = open(os.path.join(ROOT, "include", "wgs_ssim.h")).read()
+    code = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(wgs_[a-z_0-9]+)\s*\(", code))
+    assert declared == set(loss_utils.EXPORTS), declared
+    lib = loss_utils._lib_ssim()
+    for name in declared:
+        assert hasattr(lib, name)
+    body = re.search(r"typedef struct WgsSsimArgs \{(.*?)\} WgsSsimArgs;", code, re.S).group(1)
+    names = [n for d in body.split(";") if d.strip() for n in
+             [x.strip().lstrip("*").strip() for x in re.sub(r"^\s*(const\s+)?\w+\s*\*?", "", d.strip(), count=1).split(",")]]
+    assert names == [f[0] for f in loss_utils.SsimArgs._fields_], names
+    assert lib.wgs_ssim_workspace_bytes(640, 480, 3) >= 40 * 30 * 3 * 8
+    a = loss_utils.SsimArgs(0, 0, 0, 0, 11, None, None, None, None, None, None, None)
+    assert lib.wgs_ssim_forward(C.byref(a), None) == _lib.WGS_ERR_INVALID_ARGUMENT

@@ -23,6 +23,8 @@ __device__ __forceinline__ V3 cross(V3 a, V3 b) {
     return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
 }
 
+__device__ __forceinline__ float rcpf(float x) { return __fdividef(1.f, x); }
+
 // gradient store: overwrite, or add to what the buffer holds (WgsBackwardArgs::accumulate)
 __device__ __forceinline__ void gput(float* __restrict__ ptr, size_t i, float v, bool acc) {
     ptr[i] = acc ? ptr[i] + v : v;
@@ -55,7 +57,7 @@ __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const 
 // its coefficients and leaves its dL_dsh there in place, coalesced write-back (zeros for culled rows).  Per-thread
 // row access to global memory (192-B stride) moved 1.9 GB for 1.2 GB of algorithmic traffic at config 4.
 template <bool STAGED>
-__global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
+__global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
     extern __shared__ float sh_stage[];
     const int gidx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
     const bool live = gidx < p.P;
@@ -92,7 +94,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
             for (int k = 0; k < 3; k++) s3[k] = expf(s3[k]);
             qn = fmaxf(sqrtf(q4[0] * q4[0] + q4[1] * q4[1] + q4[2] * q4[2] + q4[3] * q4[3]), 1e-12f);
 #pragma unroll
-            for (int k = 0; k < 4; k++) q4[k] = q4[k] / qn;
+            for (int k = 0; k < 4; k++) q4[k] = q4[k] * rcpf(qn);
         }
         const uint2 rect = __ldg(p.geom.rect + idx);
         const float4 ra = __ldcg(p.geom.rec + 2 * idx), rb = __ldcg(p.geom.rec + 2 * idx + 1);
@@ -131,13 +133,14 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
             V3 t = {V[0] * m.x + V[4] * m.y + V[8] * m.z + V[12], V[1] * m.x + V[5] * m.y + V[9] * m.z + V[13],
                     V[2] * m.x + V[6] * m.y + V[10] * m.z + V[14]};
             const float limx = 1.3f * p.tanfovx, limy = 1.3f * p.tanfovy;
-            const float txtz = t.x / t.z, tytz = t.y / t.z;
+            const float rz = rcpf(t.z);  // gradients are a tolerance path: MUFU reciprocal instead of IEEE division
+            const float txtz = t.x * rz, tytz = t.y * rz;
             t.x = fminf(limx, fmaxf(-limx, txtz)) * t.z;
             t.y = fminf(limy, fmaxf(-limy, tytz)) * t.z;
             const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
             const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
             const float hx = p.focal_x, hy = p.focal_y;
-            const float J00 = hx / t.z, J02 = -(hx * t.x) / (t.z * t.z), J11 = hy / t.z, J12 = -(hy * t.y) / (t.z * t.z);
+            const float J00 = hx * rz, J02 = -(hx * t.x) * (rz * rz), J11 = hy * rz, J12 = -(hy * t.y) * (rz * rz);
             // T = W*J, T[c][r]; W[c][r] with W = mat3(V0,V4,V8, V1,V5,V9, V2,V6,V10)
             const float T00 = V[0] * J00 + V[2] * J02, T01 = V[4] * J00 + V[6] * J02, T02 = V[8] * J00 + V[10] * J02;
             const float T10 = V[1] * J11 + V[2] * J12, T11 = V[5] * J11 + V[6] * J12, T12 = V[9] * J11 + V[10] * J12;
@@ -150,7 +153,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
             const float b = T00 * B0 + T01 * B1 + T02 * B2;
             const float c = T10 * B0 + T11 * B1 + T12 * B2 + 0.3f;
             const float denom = a * c - b * b;
-            const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+            const float denom2inv = rcpf((denom * denom) + 0.0000001f);
             float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
             if (denom2inv != 0.f) {
                 dL_da = denom2inv * (-c * c * dcx + 2.f * b * c * dcy + (denom - a * c) * dcz);
@@ -173,7 +176,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
             const float dJ02 = V[2] * dT00 + V[6] * dT01 + V[10] * dT02;
             const float dJ11 = V[1] * dT10 + V[5] * dT11 + V[9] * dT12;
             const float dJ12 = V[2] * dT10 + V[6] * dT11 + V[10] * dT12;
-            const float tz = 1.f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
+            const float tz = rz, tz2 = tz * tz, tz3 = tz2 * tz;
             const float dtx = x_grad_mul * -hx * tz2 * dJ02;
             const float dty = y_grad_mul * -hy * tz2 * dJ12;
             const float dtz = -hx * tz2 * dJ00 - hy * tz2 * dJ11 + (2.f * hx * t.x) * tz3 * dJ02 + (2.f * hy * t.y) * tz3 * dJ12;
@@ -199,7 +202,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
             const float mhx = Pm[0] * m.x + Pm[4] * m.y + Pm[8] * m.z + Pm[12];
             const float mhy = Pm[1] * m.x + Pm[5] * m.y + Pm[9] * m.z + Pm[13];
             const float mhw = Pm[3] * m.x + Pm[7] * m.y + Pm[11] * m.z + Pm[15];
-            const float m_w = 1.0f / (mhw + 0.0000001f);
+            const float m_w = rcpf(mhw + 0.0000001f);
             const float mul1 = mhx * m_w * m_w, mul2 = mhy * m_w * m_w;
             dmean.x += (Pm[0] * m_w - Pm[3] * mul1) * dm2x + (Pm[1] * m_w - Pm[3] * mul2) * dm2y;
             dmean.y += (Pm[4] * m_w - Pm[7] * mul1) * dm2x + (Pm[5] * m_w - Pm[7] * mul2) * dm2y;
@@ -227,7 +230,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
                 const uint8_t cb = p.geom.clamped[idx];
                 const V3 dRGB = {(cb & 1) ? 0.f : dcol[0], (cb & 2) ? 0.f : dcol[1], (cb & 4) ? 0.f : dcol[2]};
                 const V3 dir_orig = {m.x - __ldg(p.campos), m.y - __ldg(p.campos + 1), m.z - __ldg(p.campos + 2)};
-                const float il = 1.f / sqrtf(dot(dir_orig, dir_orig));
+                const float il = rsqrtf(dot(dir_orig, dir_orig));
                 const float x = dir_orig.x * il, y = dir_orig.y * il, z = dir_orig.z * il;
                 // STAGED: coefficient k of this thread's row sits at srow + 3 (k + koff); dL_dsh replaces it in place,
                 // so every band reads its coefficients before it puts its gradients
@@ -280,7 +283,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
                 // dnormvdv (auxiliary.h:107-117)
                 const V3 v = dir_orig;
                 const float sum2 = dot(v, v);
-                const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+                const float invsum32 = il * il * il;  // 1 / |v|^3
                 const V3 dms = {((sum2 - v.x * v.x) * ddir.x - v.y * v.x * ddir.y - v.z * v.x * ddir.z) * invsum32,
                                 (-v.x * v.y * ddir.x + (sum2 - v.y * v.y) * ddir.y - v.z * v.y * ddir.z) * invsum32,
                                 (-v.x * v.z * ddir.x - v.y * v.z * ddir.y + (sum2 - v.z * v.z) * ddir.z) * invsum32};
@@ -346,7 +349,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
             for (int k = 0; k < 3; k++) dscale[k] *= s3[k];
             const float qd = q4[0] * drot[0] + q4[1] * drot[1] + q4[2] * drot[2] + q4[3] * drot[3];
 #pragma unroll
-            for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q4[k] * qd) / qn;
+            for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q4[k] * qd) * rcpf(qn);
         }
         if (live) {
         if (p.dL_dmeans3D) { gput(p.dL_dmeans3D, 3 * idx, dmean.x, accm); gput(p.dL_dmeans3D, 3 * idx + 1, dmean.y, accm); gput(p.dL_dmeans3D, 3 * idx + 2, dmean.z, accm); }
@@ -407,18 +410,18 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 3) preprocess_bwd_kernel(
     }
 }
 
-static_assert(WGS_PRE_BWD_THREADS == SH_STAGE_THREADS, "staging helpers assume 256-thread blocks");
-
 int configure_preprocess_bwd() {
     return (int)cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)sh_stage_bytes(SH_STAGE_MAX_M));
+                                     (int)sh_stage_bytes(SH_STAGE_MAX_M, WGS_PRE_BWD_THREADS));
 }
+
+static_assert(WGS_PRE_BWD_THREADS >= 6 * 32, "the last block sums the six pose components with one warp each");
 
 void launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
     if (p.P <= 0) return;
     const int blocks = (p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS;
     if (p.sh && p.M > 1 && p.M <= SH_STAGE_MAX_M)
-        preprocess_bwd_kernel<true><<<blocks, WGS_PRE_BWD_THREADS, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M), s>>>(p);
+        preprocess_bwd_kernel<true><<<blocks, WGS_PRE_BWD_THREADS, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M, WGS_PRE_BWD_THREADS), s>>>(p);
     else
         preprocess_bwd_kernel<false><<<blocks, WGS_PRE_BWD_THREADS, 0, s>>>(p);
 }

@@ -258,13 +258,13 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 
 int configure_preprocess_fwd() {
     return (int)cudaFuncSetAttribute(preprocess_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)sh_stage_bytes(SH_STAGE_MAX_M));
+                                     (int)sh_stage_bytes(SH_STAGE_MAX_M, 256));
 }
 
 void launch_preprocess_fwd(const PreFwdParams& p, cudaStream_t s) {
     if (p.P <= 0) return;
     if (p.sh && !p.colors_precomp && p.M > 1 && p.M <= SH_STAGE_MAX_M)
-        preprocess_fwd_kernel<true><<<(p.P + 255) / 256, 256, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M), s>>>(p);
+        preprocess_fwd_kernel<true><<<(p.P + 255) / 256, 256, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M, 256), s>>>(p);
     else
         preprocess_fwd_kernel<false><<<(p.P + 255) / 256, 256, 0, s>>>(p);
 }

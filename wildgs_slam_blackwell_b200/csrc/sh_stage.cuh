@@ -11,9 +11,8 @@
 namespace wgs {
 
 constexpr int SH_STAGE_MAX_M = 16;        // rows of at most 48 words: two requests per row
-constexpr int SH_STAGE_THREADS = 256;
 __host__ __device__ inline int sh_row_stride(int row_words) { return row_words | 1; }
-inline size_t sh_stage_bytes(int M) { return (size_t)SH_STAGE_THREADS * sh_row_stride(3 * M) * sizeof(float); }
+inline size_t sh_stage_bytes(int M, int threads) { return (size_t)threads * sh_row_stride(3 * M) * sizeof(float); }
 
 __device__ __forceinline__ void sh_cp_async4(float* smem_dst, const float* gsrc) {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
