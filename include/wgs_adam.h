@@ -24,8 +24,14 @@ typedef struct WgsAdamTensor {
   float* exp_avg;          /* (n) updated in place */
   float* exp_avg_sq;       /* (n) updated in place */
   uint64_t n;
-  float step_size;         /* lr / (1 - beta1^step) */
-  float bias_correction2_sqrt; /* sqrt(1 - beta2^step) */
+  float step_size;         /* lr / (1 - beta1^step); with step_dev: the learning rate itself (unless lr_dev is given) */
+  float bias_correction2_sqrt; /* sqrt(1 - beta2^step); ignored with step_dev */
+  /* Graph-capturable mode (torch's `capturable=True`): the step count lives on the device, so a captured launch
+   * advances it on every replay.  step_dev: 1 float, the number of steps taken so far -- the kernel forms both bias
+   * corrections from step_dev[0] + 1 in double and a second launch increments the counters.  lr_dev (optional):
+   * 1 float read at run time, for learning-rate schedules under a captured graph.  Both null: host-side mode. */
+  float* step_dev;
+  const float* lr_dev;
 } WgsAdamTensor;
 
 /* tensors: HOST array of `count` (<= WGS_ADAM_MAX_TENSORS) descriptors with DEVICE pointers */

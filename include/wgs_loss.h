@@ -5,7 +5,9 @@
  * the chain of ~25 elementwise/reduction torch kernels (forward + autograd backward) of the
  * reference's
  *   get_loss_tracking / get_loss_tracking_rgb   (src/utils/slam_utils.py:47-87)
- *   get_loss_mapping  / get_loss_mapping_rgbd   (src/utils/slam_utils.py:107-143, ssim_loss off)
+ *   get_loss_mapping  / get_loss_mapping_rgbd   (src/utils/slam_utils.py:107-143; the SSIM term: wgs_ssim.h)
+ *   the L1 colour and depth terms of get_loss_mapping_uncertainty (src/utils/slam_utils.py:146-258,
+ *   src/utils/dyn_uncertainty/mapping_utils.py:257-268)
  * and writes dL/dcolor and dL/ddepth in exactly the layout wgs_backward() consumes
  * (WgsBackwardArgs::dL_dout_color / dL_dout_depth), plus dL/d(exposure_a, exposure_b).
  *
@@ -13,7 +15,9 @@
  *   m        = (sum_c gt_color > rgb_boundary_threshold) * pixel_mask
  *   w        = 0.5 / uncertainty^2, set to 0 where < 0.1           (1 if uncertainty null)
  *   l_rgb    = opacity * | image_ab*m - gt_color*m | * w           (opacity = 1 if null)
- *   l_depth  = | depth*dm - gt_depth*dm |,  dm = gt_depth > depth_min
+ *   l_depth  = | depth*dm - gt_depth*dm |,  dm = gt_depth > depth_min  [and gt_depth < depth_max if depth_max > 0]
+ *   if depth_weighted:  l_depth *= w  where gt_depth < depth + depth_margin      (get_loss_mapping_uncertainty,
+ *                                                                                 src/utils/slam_utils.py:238-242)
  *   loss     = color_weight * mean_{3HW}(l_rgb) + depth_weight * mean_{HW}(l_depth)
  *
  * The gradient w.r.t. the rendered opacity is not produced: the reference rasterizer ignores
@@ -37,6 +41,9 @@ typedef struct WgsLossArgs {
   float depth_min;              /* 0.01 in the reference (slam_utils.py:140) */
   float color_weight;           /* alpha (mapping) or 1 (tracking) */
   float depth_weight;           /* 1 - alpha (mapping) or 0 (tracking) */
+  float depth_max;              /* > 0: the depth mask also needs gt_depth < depth_max (mapping_utils.py:262-266); 0: off */
+  float depth_margin;           /* used when depth_weighted: 1.0 in the reference (slam_utils.py:241) */
+  int32_t depth_weighted;       /* != 0: multiply l_depth by w where gt_depth < depth + depth_margin (needs uncertainty) */
   const float* color;           /* (3,H,W) rendered colour */
   const float* depth;           /* (1,H,W) rendered depth; may be null iff depth_weight == 0 */
   const float* opacity;         /* (1,H,W) rendered opacity or null */

@@ -66,6 +66,45 @@ def test_matches_torch_adam_over_steps_with_state_surgery():
         assert int(sg["step"]) == int(sc["step"])
 
 
+def test_capturable_step_replays_from_a_cuda_graph():
+    """capturable=True: the step count lives on the device and a tensor lr is read at run time, so ONE captured
+    wgs_adam_step launch replayed 9 times equals 9 torch.optim.Adam steps (bias corrections and the lr schedule
+    advance inside the graph)."""
+    g = torch.Generator().manual_seed(4)
+    w0 = torch.randn(3001, 3, generator=g)
+    grads = [torch.randn(3001, 3, generator=g) for _ in range(9)]
+    pc = w0.clone().requires_grad_(True)
+    oc = torch.optim.Adam([{"params": [pc], "lr": 1e-2}], lr=0.0, eps=1e-15)
+    pg = w0.to(DEV).requires_grad_(True)
+    lr = torch.tensor(1e-2, device=DEV)
+    og = FusedAdam([{"params": [pg], "lr": lr}], lr=0.0, eps=1e-15, capturable=True)
+    gbuf = torch.zeros(3001, 3, device=DEV)
+    pg.grad = gbuf
+    graph = None
+    for it, gr in enumerate(grads):
+        oc.param_groups[0]["lr"] = 1e-2 * 0.9 ** it
+        pc.grad = gr.clone()
+        oc.step()
+        gbuf.copy_(gr.to(DEV))
+        lr.fill_(1e-2 * 0.9 ** it)
+        if it < 2:
+            og.step()                                    # eager steps create the state
+        elif graph is None:
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                og.step()
+            graph.replay()                               # capture does not execute
+        else:
+            graph.replay()
+    st = og.state[pg]
+    assert st["step"].is_cuda and float(st["step"]) == 9.0
+    np.testing.assert_allclose(pg.detach().cpu().numpy(), pc.detach().numpy(), rtol=2e-5, atol=1e-3 * 1e-2 * 9)
+    m, v = oc.state[pc]["exp_avg"].numpy(), oc.state[pc]["exp_avg_sq"].numpy()
+    np.testing.assert_allclose(st["exp_avg"].cpu().numpy(), m, rtol=1e-5, atol=1e-6 * np.abs(m).max())
+    np.testing.assert_allclose(st["exp_avg_sq"].cpu().numpy(), v, rtol=1e-5, atol=1e-6 * np.abs(v).max())
+
+
 def test_errors():
     with pytest.raises(NotImplementedError):
         FusedAdam([torch.zeros(3, device=DEV, requires_grad=True)], amsgrad=True)

@@ -92,6 +92,8 @@ def test_argument_errors():
         loss.photometric_loss(c, c, exposure_a=torch.zeros(1, device=DEV))
     with pytest.raises(RuntimeError, match=r"\(3, H, W\)"):
         loss.photometric_loss(torch.zeros(8, 8, device=DEV), c)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(KeyError):      # ssim_loss on needs opt_params.lambda_dssim, as in the reference (slam_utils.py:135)
         loss.get_loss_mapping({"Training": {"rgb_boundary_threshold": 0.01, "ssim_loss": True}}, c, c[:1], View(),
                               initialization=True)
+    with pytest.raises(RuntimeError, match="depth_weighted needs"):
+        loss.photometric_loss(c, c, depth=c[:1], gt_depth=c[:1], depth_weight=0.5, depth_weighted=True)

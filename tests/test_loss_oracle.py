@@ -184,3 +184,44 @@ def test_ssim_abi_symbols():
     assert lib.wgs_ssim_workspace_bytes(640, 480, 3) >= 40 * 30 * 3 * 8
     a = loss_utils.SsimArgs(0, 0, 0, 0, 11, None, None, None, None, None, None, None)
     assert lib.wgs_ssim_forward(C.byref(a), None) == _lib.WGS_ERR_INVALID_ARGUMENT
+
+
+def _make_net(seed, fd=12):
+    import torch
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(fd, 16), torch.nn.ReLU(), torch.nn.Linear(16, 1), torch.nn.Softplus(),
+                               torch.nn.Flatten(-2, -1))
+
+
+def test_mapping_ssim_oracle_matches_reference_golden():
+    d = np.load(os.path.join(ROOT, "tests", "golden", "mapping_ssim.npz"))
+    o = loss_oracle.mapping_rgbd(d["image"], d["gt"], d["depth"], d["gt_depth"], d["a"], d["b"], alpha=0.5, lam=0.2)
+    np.testing.assert_allclose(o["loss"], d["loss"], rtol=1e-5)
+    for k in ("g_image", "g_depth"):
+        np.testing.assert_allclose(o[k], d[k], rtol=2e-3, atol=2e-4 * np.abs(d[k]).max())
+    np.testing.assert_allclose([o["g_a"], o["g_b"]], [d["g_a"][0], d["g_b"][0]], rtol=2e-3)
+
+
+@pytest.mark.parametrize("name,tf,sf,init,freeze", [("mapping_uncertainty", 0.3, 0.6, False, False),
+                                                    ("mapping_uncertainty_init", 0.9, 0.1, True, True)])
+def test_mapping_uncertainty_oracle_matches_reference_golden(name, tf, sf, init, freeze):
+    import torch
+    d = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    cfg = dict(alpha=0.5, lam=0.2, thr=0.01, window=7, median=5, opacity_th=0.9, ssim_mult=0.5, depth_mult=0.2, freeze=freeze)
+    a, b = (None, None) if init else (d["a"], d["b"])
+    o = loss_oracle.mapping_uncertainty(d["image"], d["gt"], d["depth"], d["gt_depth"], d["opacity"], d["uncertainty"],
+                                        cfg, tf, sf, a, b)
+    np.testing.assert_allclose(o["loss"], d["loss"], rtol=2e-4)      # the uncertainty term carries the float32 SSIM components
+    for k in ("g_image", "g_depth"):
+        np.testing.assert_allclose(o[k], d[k], rtol=2e-3, atol=2e-4 * np.abs(d[k]).max())
+    if not init:
+        np.testing.assert_allclose([o["g_a"], o["g_b"]], [d["g_a"][0], d["g_b"][0]], rtol=2e-3)
+    # gradient w.r.t. the uncertainty map, pushed through the same stand-in network as the generator used
+    net = _make_net(7)
+    unc = net(torch.from_numpy(d["features"]))
+    np.testing.assert_allclose(unc.detach().numpy(), d["uncertainty"], rtol=1e-5, atol=1e-6)
+    unc.backward(torch.from_numpy(o["g_unc"]).float())
+    for i, p in enumerate(net.parameters()):
+        want = d[f"g_net{i}"]
+        got = np.zeros_like(want) if p.grad is None else p.grad.numpy()
+        np.testing.assert_allclose(got, want, rtol=1e-2, atol=2e-3 * max(np.abs(want).max(), 1e-12))

@@ -18,7 +18,8 @@ MAX_TENSORS = 16
 
 class AdamTensor(C.Structure):
     _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
-                ("n", C.c_uint64), ("step_size", C.c_float), ("bias_correction2_sqrt", C.c_float)]
+                ("n", C.c_uint64), ("step_size", C.c_float), ("bias_correction2_sqrt", C.c_float),
+                ("step_dev", C.c_void_p), ("lr_dev", C.c_void_p)]
 
 
 _proto_done = False
@@ -40,7 +41,10 @@ class FusedAdam(torch.optim.Adam):
                 raise NotImplementedError(f"FusedAdam: {k} is not fused")
         if kw.get("weight_decay", 0):
             raise NotImplementedError("FusedAdam: weight_decay is not fused")
-        super().__init__(params, lr=lr, betas=betas, eps=eps, foreach=False, fused=False)
+        # capturable=True (torch's meaning): state['step'] is a float tensor on the device, advanced by the launch
+        # itself, and a group's lr may be a device tensor -- the step then replays from a CUDA graph (graph.py)
+        super().__init__(params, lr=lr, betas=betas, eps=eps, foreach=False, fused=False,
+                         capturable=bool(kw.get("capturable", False)))
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -57,18 +61,34 @@ class FusedAdam(torch.optim.Adam):
                 if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
                     raise RuntimeError("FusedAdam: parameters must be contiguous float32 CUDA tensors")
                 st = self.state[p]
+                capt = bool(group.get("capturable", False))
                 if len(st) == 0 or "exp_avg" not in st:
-                    st["step"] = 0
+                    st["step"] = torch.zeros((), dtype=torch.float32, device=p.device) if capt else 0
                     st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                     st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
-                step = int(st.get("step", 0)) + 1
-                st["step"] = step
+                if capt:
+                    if not torch.is_tensor(st["step"]) or not st["step"].is_cuda:   # state made before the switch
+                        st["step"] = torch.full((), float(st["step"]), dtype=torch.float32, device=p.device)
+                    step = 1   # unused: the kernel reads the device counter
+                else:
+                    step = int(st.get("step", 0)) + 1
+                    st["step"] = step
                 g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
                 t = AdamTensor()
                 t.param, t.grad = p.data_ptr(), g.data_ptr()
                 t.exp_avg, t.exp_avg_sq, t.n = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), p.numel()
-                t.step_size = group["lr"] / (1.0 - beta1 ** step)
-                t.bias_correction2_sqrt = math.sqrt(1.0 - beta2 ** step)
+                lr = group["lr"]
+                if capt:
+                    t.step_dev = st["step"].data_ptr()
+                    if torch.is_tensor(lr):
+                        if not lr.is_cuda or lr.dtype != torch.float32:
+                            raise RuntimeError("FusedAdam(capturable): a tensor lr must be a float32 CUDA tensor")
+                        t.lr_dev, t.step_size = lr.data_ptr(), 0.0
+                    else:
+                        t.step_size = float(lr)
+                else:
+                    t.step_size = float(lr) / (1.0 - beta1 ** step)
+                    t.bias_correction2_sqrt = math.sqrt(1.0 - beta2 ** step)
                 batches.setdefault((p.device, beta1, beta2, group["eps"]), []).append((t, g))
         lib = _lib_adam()
         for (device, beta1, beta2, eps), items in batches.items():

@@ -14,6 +14,7 @@ struct AdamParams {
     uint32_t first_block[WGS_ADAM_MAX_TENSORS + 1];
     int count;
     float beta2, w1, w2, eps;   // w = 1 - beta, formed in double on the host
+    double beta1d, beta2d;
 };
 
 __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const __grid_constant__ AdamParams p) {
@@ -22,6 +23,18 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const __grid_constan
     const WgsAdamTensor& t = p.t[e];
     const size_t base = ((size_t)(blockIdx.x - p.first_block[e]) * ADAM_THREADS + threadIdx.x) * ADAM_EPT;
     const float w1 = p.w1, w2 = p.w2;
+    float step_size = t.step_size, bc2s = t.bias_correction2_sqrt;
+    if (t.step_dev) {   // capturable: corrections from the device-side step count (one thread per block, double like torch)
+        __shared__ float s_corr[2];
+        if (threadIdx.x == 0) {
+            const double step = (double)(*t.step_dev) + 1.0;
+            const float lr = t.lr_dev ? *t.lr_dev : t.step_size;
+            s_corr[0] = (float)((double)lr / (1.0 - pow(p.beta1d, step)));
+            s_corr[1] = (float)sqrt(1.0 - pow(p.beta2d, step));
+        }
+        __syncthreads();
+        step_size = s_corr[0]; bc2s = s_corr[1];
+    }
 #pragma unroll
     for (int k = 0; k < ADAM_EPT; k++) {
         const size_t i = base + k;
@@ -30,12 +43,18 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const __grid_constan
             float m = t.exp_avg[i], v = t.exp_avg_sq[i];
             m = m + w1 * (g - m);                       // exp_avg.lerp_(grad, 1 - beta1)
             v = v * p.beta2 + w2 * g * g;               // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
-            const float denom = sqrtf(v) / t.bias_correction2_sqrt + p.eps;
+            const float denom = sqrtf(v) / bc2s + p.eps;
             t.exp_avg[i] = m;
             t.exp_avg_sq[i] = v;
-            t.param[i] = t.param[i] - t.step_size * (m / denom);   // param.addcdiv_(exp_avg, denom, value=-step_size)
+            t.param[i] = t.param[i] - step_size * (m / denom);   // param.addcdiv_(exp_avg, denom, value=-step_size)
         }
     }
+}
+
+// after the update: advance the device-side step counters of the capturable tensors
+__global__ void adam_advance_kernel(const __grid_constant__ AdamParams p) {
+    const int e = threadIdx.x;
+    if (e < p.count && p.t[e].step_dev) *p.t[e].step_dev += 1.f;
 }
 
 }  // namespace wgs
@@ -52,6 +71,8 @@ int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, double beta1, dou
     }
     AdamParams p;
     p.count = 0; p.beta2 = (float)beta2; p.w1 = (float)(1.0 - beta1); p.w2 = (float)(1.0 - beta2); p.eps = (float)eps;
+    p.beta1d = beta1; p.beta2d = beta2;
+    bool capturable = false;
     uint32_t blocks = 0;
     for (int i = 0; i < count; i++) {
         const WgsAdamTensor& t = tensors[i];
@@ -60,6 +81,7 @@ int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, double beta1, dou
             wgs_set_error_message("wgs_adam_step: null tensor pointer");
             return WGS_ERR_INVALID_ARGUMENT;
         }
+        capturable |= t.step_dev != nullptr;
         p.t[p.count] = t;
         p.first_block[p.count] = blocks;
         blocks += (uint32_t)((t.n + (size_t)ADAM_THREADS * ADAM_EPT - 1) / ((size_t)ADAM_THREADS * ADAM_EPT));
@@ -68,6 +90,7 @@ int wgs_adam_step(const WgsAdamTensor* tensors, int32_t count, double beta1, dou
     p.first_block[p.count] = blocks;
     if (blocks == 0) return WGS_OK;
     adam_kernel<<<blocks, ADAM_THREADS, 0, (cudaStream_t)cuda_stream>>>(p);
+    if (capturable) adam_advance_kernel<<<1, 32, 0, (cudaStream_t)cuda_stream>>>(p);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         wgs_set_error_message(cudaGetErrorString(e));

@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
             v = a.uncertainty ? ld4(a.uncertainty, i0, N, 1.f) : make_float4(1.f, 1.f, 1.f, 1.f);
             un[0] = v.x; un[1] = v.y; un[2] = v.z; un[3] = v.w;
         }
-        float dc[3][4];
+        float dc[3][4], wj[4];
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             const bool in = i0 + j < N;
@@ -75,6 +75,7 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
                 w = 0.5f / (un[j] * un[j]);
                 w = w < 0.1f ? 0.f : w;
             }
+            wj[j] = w;
             const float scale = in ? op[j] * w : 0.f;
 #pragma unroll
             for (int ch = 0; ch < 3; ch++) {
@@ -97,10 +98,13 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
                 const float d[4] = {dv.x, dv.y, dv.z, dv.w}, gd[4] = {gv.x, gv.y, gv.z, gv.w};
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    const float dm = gd[j] > a.depth_min ? 1.f : 0.f;  // slam_utils.py:140-141
+                    // slam_utils.py:140-141; mapping_utils.py:262-266 adds the upper bound
+                    const float dm = (gd[j] > a.depth_min && !(a.depth_max > 0.f && !(gd[j] < a.depth_max))) ? 1.f : 0.f;
                     const float r = d[j] * dm - gd[j] * dm;
-                    s_dep += fabsf(r);
-                    dd[j] = kd * sgn(r) * dm;
+                    // slam_utils.py:238-242: weighted only where the reference depth is in front of the rendered one (+ margin)
+                    const float wd = (a.depth_weighted && gd[j] < d[j] + a.depth_margin) ? wj[j] : 1.f;
+                    s_dep += wd * fabsf(r);
+                    dd[j] = kd * wd * sgn(r) * dm;
                 }
             }
             st4(a.dL_ddepth, i0, N, make_float4(dd[0], dd[1], dd[2], dd[3]));
@@ -167,6 +171,10 @@ int wgs_photometric_loss(const WgsLossArgs* a, void* cuda_stream) {
     if (!a || a->width <= 0 || a->height <= 0 || !a->color || !a->gt_color || !a->loss || !a->dL_dcolor ||
         !a->workspace || ((uintptr_t)a->workspace & 255u)) {
         wgs_set_error_message("wgs_photometric_loss: null/misaligned required pointer or bad size");
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    if (a->depth_weighted && !a->uncertainty) {
+        wgs_set_error_message("wgs_photometric_loss: depth_weighted needs the uncertainty map");
         return WGS_ERR_INVALID_ARGUMENT;
     }
     if (a->depth_weight != 0.f && (!a->depth || !a->gt_depth || !a->dL_ddepth)) {

@@ -41,10 +41,12 @@ __device__ __forceinline__ void load_patch(float (*a)[SN + 1], const float* __re
 }
 
 // windowed moments of one plane at this thread's pixel: m = {mu1, mu2, s11, s22, s12}
+// RT >= 0: radius known at compile time (tap loops unrolled; 11- and 7-tap windows are the reference's), else p.R
+template <int RT>
 __device__ __forceinline__ void moments(const SsimParams& p, float (*a)[SN + 1], float (*b)[SN + 1],
                                         float (*h)[SN][ST + 1], const float* __restrict__ x1,
                                         const float* __restrict__ x2, float m[5]) {
-    const int R = p.R, n = ST + 2 * R, taps = 2 * R + 1;
+    const int R = RT >= 0 ? RT : p.R, n = ST + 2 * R, taps = 2 * R + 1;
     const int x0 = blockIdx.x * ST - R, y0 = blockIdx.y * ST - R;
     __syncthreads();   // previous user of the buffers is done
     load_patch(a, x1, p.W, p.H, x0, y0, n);
@@ -53,6 +55,7 @@ __device__ __forceinline__ void moments(const SsimParams& p, float (*a)[SN + 1],
     for (int i = threadIdx.x; i < n * ST; i += 256) {
         const int r = i / ST, c = i - r * ST;
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f, s4 = 0.f;
+#pragma unroll
         for (int k = 0; k < taps; k++) {
             const float w = p.w[k], u = a[r][c + k], v = b[r][c + k];
             s0 = fmaf(w, u, s0); s1 = fmaf(w, v, s1); s2 = fmaf(w, u * u, s2); s3 = fmaf(w, v * v, s3);
@@ -64,6 +67,7 @@ __device__ __forceinline__ void moments(const SsimParams& p, float (*a)[SN + 1],
     const int tx = threadIdx.x & (ST - 1), ty = threadIdx.x / ST;
 #pragma unroll
     for (int q = 0; q < 5; q++) m[q] = 0.f;
+#pragma unroll
     for (int k = 0; k < taps; k++) {
         const float w = p.w[k];
 #pragma unroll
@@ -71,6 +75,7 @@ __device__ __forceinline__ void moments(const SsimParams& p, float (*a)[SN + 1],
     }
 }
 
+template <int RT>
 __global__ void __launch_bounds__(256) ssim_fwd_kernel(const __grid_constant__ SsimParams p) {
     __shared__ float a[SN][SN + 1], b[SN][SN + 1];
     __shared__ float h[5][SN][ST + 1];
@@ -78,7 +83,7 @@ __global__ void __launch_bounds__(256) ssim_fwd_kernel(const __grid_constant__ S
     const int plane = blockIdx.z;
     const size_t N = (size_t)p.W * p.H;
     float m[5];
-    moments(p, a, b, h, p.x1 + plane * N, p.x2 + plane * N, m);
+    moments<RT>(p, a, b, h, p.x1 + plane * N, p.x2 + plane * N, m);
     const int px = blockIdx.x * ST + (threadIdx.x & (ST - 1)), py = blockIdx.y * ST + threadIdx.x / ST;
     float val = 0.f;
     if (px < p.W && py < p.H) {
@@ -123,10 +128,11 @@ __global__ void __launch_bounds__(256) ssim_mean_kernel(const __grid_constant__ 
     if (threadIdx.x == 0) p.mean[blockIdx.x] = (float)(red[0] / ((double)p.ppm * p.W * p.H));
 }
 
+template <int RT>
 __global__ void __launch_bounds__(256) ssim_bwd_kernel(const __grid_constant__ SsimParams p) {
     __shared__ float a[3][SN][SN + 1];
     __shared__ float h[3][SN][ST + 1];
-    const int plane = blockIdx.z, R = p.R, n = ST + 2 * R, taps = 2 * R + 1;
+    const int plane = blockIdx.z, R = RT >= 0 ? RT : p.R, n = ST + 2 * R, taps = 2 * R + 1;
     const size_t N = (size_t)p.W * p.H, PN = (size_t)p.planes * N;
     const int x0 = blockIdx.x * ST - R, y0 = blockIdx.y * ST - R;
 #pragma unroll
@@ -135,6 +141,7 @@ __global__ void __launch_bounds__(256) ssim_bwd_kernel(const __grid_constant__ S
     for (int i = threadIdx.x; i < n * ST; i += 256) {
         const int r = i / ST, c = i - r * ST;
         float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
         for (int k = 0; k < taps; k++) {
             const float w = p.w[k];
             s0 = fmaf(w, a[0][r][c + k], s0); s1 = fmaf(w, a[1][r][c + k], s1); s2 = fmaf(w, a[2][r][c + k], s2);
@@ -146,6 +153,7 @@ __global__ void __launch_bounds__(256) ssim_bwd_kernel(const __grid_constant__ S
     const int px = blockIdx.x * ST + tx, py = blockIdx.y * ST + ty;
     if (px >= p.W || py >= p.H) return;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
     for (int k = 0; k < taps; k++) {
         const float w = p.w[k];
         s0 = fmaf(w, h[0][ty + k][tx], s0); s1 = fmaf(w, h[1][ty + k][tx], s1); s2 = fmaf(w, h[2][ty + k][tx], s2);
@@ -156,6 +164,7 @@ __global__ void __launch_bounds__(256) ssim_bwd_kernel(const __grid_constant__ S
 }
 
 // compute_ssim_components (mapping_utils.py:125-204): grid.z = batch item, channels looped inside
+template <int RT>
 __global__ void __launch_bounds__(256) ssim_components_kernel(const __grid_constant__ SsimParams p) {
     __shared__ float a[SN][SN + 1], b[SN][SN + 1];
     __shared__ float h[5][SN][ST + 1];
@@ -165,7 +174,7 @@ __global__ void __launch_bounds__(256) ssim_components_kernel(const __grid_const
     for (int ch = 0; ch < p.C; ch++) {
         const size_t plane = (size_t)blockIdx.z * p.C + ch;
         float m[5];
-        moments(p, a, b, h, p.x1 + plane * N, p.x2 + plane * N, m);
+        moments<RT>(p, a, b, h, p.x1 + plane * N, p.x2 + plane * N, m);
         const float mu1 = m[0], mu2 = m[1];
         const float v1 = fmaxf(eps, m[2] - mu1 * mu1), v2 = fmaxf(eps, m[3] - mu2 * mu2);
         float s12 = m[4] - mu1 * mu2;
@@ -232,7 +241,10 @@ int wgs_ssim_forward(const WgsSsimArgs* a, void* cuda_stream) {
         return WGS_ERR_INVALID_ARGUMENT;
     }
     cudaStream_t s = (cudaStream_t)cuda_stream;
-    ssim_fwd_kernel<<<dim3(p.gx, p.gy, p.planes), 256, 0, s>>>(p);
+    const dim3 grid(p.gx, p.gy, p.planes);
+    if (p.R == 5) ssim_fwd_kernel<5><<<grid, 256, 0, s>>>(p);
+    else if (p.R == 3) ssim_fwd_kernel<3><<<grid, 256, 0, s>>>(p);
+    else ssim_fwd_kernel<-1><<<grid, 256, 0, s>>>(p);
     ssim_mean_kernel<<<p.planes / p.ppm, 256, 0, s>>>(p);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { wgs_set_error_message(cudaGetErrorString(e)); return WGS_ERR_CUDA; }
@@ -247,7 +259,11 @@ int wgs_ssim_backward(const WgsSsimArgs* a, void* cuda_stream) {
         wgs_set_error_message("wgs_ssim_backward: maps, dL_dmean and dL_dimg1 are required");
         return WGS_ERR_INVALID_ARGUMENT;
     }
-    ssim_bwd_kernel<<<dim3(p.gx, p.gy, p.planes), 256, 0, (cudaStream_t)cuda_stream>>>(p);
+    const dim3 grid(p.gx, p.gy, p.planes);
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    if (p.R == 5) ssim_bwd_kernel<5><<<grid, 256, 0, s>>>(p);
+    else if (p.R == 3) ssim_bwd_kernel<3><<<grid, 256, 0, s>>>(p);
+    else ssim_bwd_kernel<-1><<<grid, 256, 0, s>>>(p);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { wgs_set_error_message(cudaGetErrorString(e)); return WGS_ERR_CUDA; }
     return WGS_OK;
@@ -266,7 +282,11 @@ int wgs_ssim_components(int32_t width, int32_t height, int32_t batch, int32_t ch
     p.gx = (p.W + ST - 1) / ST; p.gy = (p.H + ST - 1) / ST;
     p.x1 = img1; p.x2 = img2; p.maps = nullptr; p.out = nullptr; p.dmean = nullptr; p.partial = nullptr; p.mean = nullptr;
     p.lum = luminance; p.con = contrast; p.str = structure;
-    ssim_components_kernel<<<dim3(p.gx, p.gy, batch), 256, 0, (cudaStream_t)cuda_stream>>>(p);
+    const dim3 grid(p.gx, p.gy, batch);
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    if (p.R == 5) ssim_components_kernel<5><<<grid, 256, 0, s>>>(p);
+    else if (p.R == 3) ssim_components_kernel<3><<<grid, 256, 0, s>>>(p);
+    else ssim_components_kernel<-1><<<grid, 256, 0, s>>>(p);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { wgs_set_error_message(cudaGetErrorString(e)); return WGS_ERR_CUDA; }
     return WGS_OK;

@@ -21,6 +21,7 @@ import ctypes as C
 
 import numpy as np
 import torch
+import torch.nn.functional as F
 
 from . import _lib
 
@@ -32,6 +33,7 @@ class LossArgs(C.Structure):
         ("width", C.c_int32), ("height", C.c_int32),
         ("rgb_boundary_threshold", C.c_float), ("depth_min", C.c_float),
         ("color_weight", C.c_float), ("depth_weight", C.c_float),
+        ("depth_max", C.c_float), ("depth_margin", C.c_float), ("depth_weighted", C.c_int32),
         ("color", _fp), ("depth", _fp), ("opacity", _fp), ("gt_color", _fp), ("gt_depth", _fp),
         ("pixel_mask", _fp), ("uncertainty", _fp), ("exposure_a", _fp), ("exposure_b", _fp),
         ("loss", _fp), ("dL_dcolor", _fp), ("dL_ddepth", _fp), ("dL_dexposure", _fp), ("workspace", _fp),
@@ -76,7 +78,8 @@ def _f32(t, device, shape=None):
 
 def photometric_loss(color, gt_color, *, depth=None, gt_depth=None, opacity=None, pixel_mask=None,
                      uncertainty=None, exposure_a=None, exposure_b=None, rgb_boundary_threshold=0.01,
-                     depth_min=0.01, color_weight=1.0, depth_weight=0.0):
+                     depth_min=0.01, color_weight=1.0, depth_weight=0.0, depth_max=0.0, depth_weighted=False,
+                     depth_margin=1.0):
     """One launch: returns (loss (1,), dL_dcolor (3,H,W), dL_ddepth (1,H,W), dL_dexposure (2,) or None).
     See include/wgs_loss.h for the exact expression."""
     if color.dim() != 3 or color.shape[0] != 3:
@@ -107,6 +110,7 @@ def photometric_loss(color, gt_color, *, depth=None, gt_depth=None, opacity=None
     a.width, a.height = W, H
     a.rgb_boundary_threshold, a.depth_min = float(rgb_boundary_threshold), float(depth_min)
     a.color_weight, a.depth_weight = float(color_weight), float(depth_weight)
+    a.depth_max, a.depth_margin, a.depth_weighted = float(depth_max), float(depth_margin), int(bool(depth_weighted))
     p = lambda t: None if t is None else t.data_ptr()
     a.color, a.depth, a.opacity, a.gt_color, a.gt_depth = p(color), p(depth), p(opacity), p(gt_color), p(gt_depth)
     a.pixel_mask, a.uncertainty, a.exposure_a, a.exposure_b = p(pixel_mask), p(uncertainty), p(ea), p(eb)
@@ -130,7 +134,9 @@ class _PhotometricLoss(torch.autograd.Function):
                                             uncertainty=kw.get("uncertainty"), exposure_a=exposure_a,
                                             exposure_b=exposure_b,
                                             rgb_boundary_threshold=kw["rgb_boundary_threshold"],
-                                            color_weight=kw["color_weight"], depth_weight=kw["depth_weight"])
+                                            color_weight=kw["color_weight"], depth_weight=kw["depth_weight"],
+                                            depth_max=kw.get("depth_max", 0.0),
+                                            depth_weighted=kw.get("depth_weighted", False))
         ctx.has_depth = depth is not None and kw["depth_weight"] != 0.0
         ctx.has_exp = de is not None
         ctx.save_for_backward(dc, dd, de if de is not None else dc.new_empty(0))
@@ -181,15 +187,112 @@ def get_loss_tracking(config, image, depth, opacity, viewpoint, monocular=True, 
 
 
 def get_loss_mapping_rgbd(config, image, depth, viewpoint, _exposure=(None, None)):
-    if config["Training"].get("ssim_loss", False):
-        raise NotImplementedError("ssim_loss=True is not fused (SURVEY.md §8(f)); use the torch expression")
+    """slam_utils.py:116-143.  alpha * mean((1 - l) * l1_rgb + l * (1 - ssim)) + (1 - alpha) * mean(l1_depth): the L1 terms
+    are one launch (wgs_photometric_loss, exposure applied inside), the SSIM term two (wgs_ssim_forward/backward)."""
+    from . import loss_utils
     alpha = config["Training"]["alpha"] if "alpha" in config["Training"] else 0.95
-    kw = dict(gt_color=_gt_image(viewpoint, image.device), gt_depth=_gt_depth(viewpoint, image.device),
-              rgb_boundary_threshold=config["Training"]["rgb_boundary_threshold"], color_weight=alpha,
+    lam = config["opt_params"]["lambda_dssim"] if config["Training"].get("ssim_loss", False) else 0.0
+    gt = _gt_image(viewpoint, image.device)
+    kw = dict(gt_color=gt, gt_depth=_gt_depth(viewpoint, image.device),
+              rgb_boundary_threshold=config["Training"]["rgb_boundary_threshold"], color_weight=alpha * (1.0 - lam),
               depth_weight=1.0 - alpha)
-    return _PhotometricLoss.apply(image, depth, _exposure[0], _exposure[1], kw)
+    loss = _PhotometricLoss.apply(image, depth, _exposure[0], _exposure[1], kw)
+    if lam:
+        image_ab = image if _exposure[0] is None else torch.exp(_exposure[0]) * image + _exposure[1]
+        loss = loss + (alpha * lam) * (1.0 - loss_utils.ssim(image_ab, gt))
+    return loss
 
 
 def get_loss_mapping(config, image, depth, viewpoint, initialization=False):
     exposure = (None, None) if initialization else (viewpoint.exposure_a, viewpoint.exposure_b)
     return get_loss_mapping_rgbd(config, image, depth, viewpoint, _exposure=exposure)
+
+
+def compute_bias_factor(x, s):
+    """mapping_utils.py:45-57 (the nerf-on-the-go schedule)"""
+    return x / (1 + (1 - x) * (1 / s - 2))
+
+
+def _resample(t, shape, mode="bilinear"):
+    """mapping_utils.resample_tensor_to_shape: (H,W) -> shape"""
+    return F.interpolate(t.reshape((1, 1) + tuple(t.shape[-2:])), size=tuple(shape), mode=mode)[0, 0]
+
+
+def _median_pool_same(x, k):
+    """MedianPool2d(kernel_size=k, stride=1, same=True) of median_filter.py on an (H,W) map: reflect padding, window median"""
+    pl = (k - 1) // 2
+    pr = (k - 1) - pl
+    x = F.pad(x[None, None], (pl, pr, pl, pr), mode="reflect")
+    x = x.unfold(2, k, 1).unfold(3, k, 1)
+    return x.contiguous().view(x.shape[:4] + (-1,)).median(dim=-1)[0][0, 0]
+
+
+def _depth_threshold(viewpoint, ref_depth):
+    """min(10 * median(ref_depth), 50) (mapping_utils.py:262-263): a property of the keyframe's reference depth, so it is
+    computed (one host read) when the depth is first seen instead of on every iteration."""
+    cache = getattr(viewpoint, "_wgs_depth_thr", None)
+    if cache is None or cache[0] is not viewpoint.depth:
+        cache = (viewpoint.depth, min(float(10 * ref_depth.median()), 50.0))   # float32 product, as the reference
+        try:
+            viewpoint._wgs_depth_thr = cache
+        except AttributeError:
+            pass
+    return cache[1]
+
+
+def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint, opacity, uncertainty_network,
+                                 train_frac, ssim_frac, initialization=False, freeze_uncertainty_loss=False):
+    """slam_utils.get_loss_mapping_uncertainty (slam_utils.py:146-258) with compute_mapping_loss_components
+    (mapping_utils.py:207-323): same arguments, returns (uncertainty, total_loss).
+
+    The full-resolution work is fused: the uncertainty-weighted L1 colour and depth terms and their cotangents are
+    ONE launch (wgs_photometric_loss: exposure, rgb mask, weights 0.5/u^2 with the 0.1 cut, depth mask with the
+    10x-median bound, depth weighted where the reference depth lies in front), the SSIM term two launches, the
+    luminance/contrast/structure maps of the uncertainty loss one.  What stays in torch is the uncertainty MLP and the
+    patch-resolution part of the uncertainty loss (resampling, 5x5 median, log) -- a few thousand elements."""
+    from . import loss_utils
+    dev = rendered_img.device
+    tr, ucfg = config["Training"], config["uncertainty_params"]
+    ea, eb = (None, None) if initialization else (viewpoint.exposure_a, viewpoint.exposure_b)
+    alpha = tr.get("alpha", 0.95)
+    lam = config["opt_params"]["lambda_dssim"] if tr["ssim_loss"] else 0.0
+    gt = _gt_image(viewpoint, dev)
+    ref_depth = _gt_depth(viewpoint, dev)
+    _, h, w = gt.shape
+    if config.get("full_resolution", False) and tuple(rendered_depth.shape[-2:]) != (h, w):
+        raise NotImplementedError("full_resolution with a depth map of another size than the image")
+    depth_thr = _depth_threshold(viewpoint, ref_depth)
+    image_ab = rendered_img if initialization else torch.exp(ea) * rendered_img + eb
+
+    uncertainty = uncertainty_network(viewpoint.features.to(device=dev))
+    processed = torch.clip(uncertainty, min=0.1) + 1e-3
+    with torch.no_grad():
+        resized = _resample(processed, (h, w))
+        resized = (resized - 0.1) * (1 + compute_bias_factor(train_frac, 0.8)) + 0.1
+        weights = 0.5 / resized ** 2
+        w_mean = torch.where(weights < 0.1, 0.0, weights).mean()
+        # ---- uncertainty loss inputs (detached in the reference) ----
+        op = opacity.detach().reshape(h, w)
+        small_opacity = _resample(op, uncertainty.shape)
+        lum, con, stu = loss_utils.compute_ssim_components(gt, image_ab, window_size=ucfg["ssim_window_size"])
+        ssim_weight = 100 + 900 * compute_bias_factor(ssim_frac, 0.8)
+        ssim_l = torch.clip(op * ssim_weight * (1 - lum) * (1 - stu) * (1 - con), max=5.0)
+        filtered = _median_pool_same(_resample(ssim_l, uncertainty.shape), ucfg["ssim_median_filter_size"])
+        dmask = ((ref_depth > 0.01) & (ref_depth < depth_thr)).reshape(rendered_depth.shape)
+        depth_l1 = torch.abs(rendered_depth * dmask - ref_depth * dmask)
+        small_depth_loss = _resample(torch.clip(depth_l1.reshape(h, w), max=5.0), uncertainty.shape, "bicubic")
+        small_depth = _resample(ref_depth.reshape(h, w), uncertainty.shape, "bicubic")
+        small_depth_loss = torch.where(small_depth > depth_thr, 0.0, small_depth_loss)
+    uncer_loss = (filtered / processed ** 2 + 0.5 * torch.log(processed)
+                  + ucfg["uncer_depth_mult"] * small_depth_loss / processed ** 2)
+    uncer_loss = torch.where(small_opacity < ucfg["opacity_th_for_uncer_loss"], 0.0, uncer_loss)
+    if freeze_uncertainty_loss:
+        uncer_loss = uncer_loss.detach()
+
+    kw = dict(gt_color=gt, gt_depth=ref_depth, uncertainty=resized, rgb_boundary_threshold=tr["rgb_boundary_threshold"],
+              color_weight=alpha * (1.0 - lam), depth_weight=1.0 - alpha, depth_max=depth_thr, depth_weighted=True)
+    total = _PhotometricLoss.apply(rendered_img, rendered_depth, ea, eb, kw)
+    if lam:
+        total = total + (alpha * lam) * w_mean * (1.0 - loss_utils.ssim(image_ab, gt))
+    total = total + ucfg["ssim_mult"] * uncer_loss.mean()
+    return uncertainty, total
