@@ -17,6 +17,8 @@ python scripts/bench_window.py --workload config5 --steps 5 --warmup 2 --graph 2
 python scripts/bench_compact.py 2>> gpurun_out/extra.err | tail -1 > gpurun_out/compact.json; cat gpurun_out/compact.json
 python scripts/bench_iteration.py 2>> gpurun_out/extra.err | tail -1 > gpurun_out/iteration.json; cut -c1-400 gpurun_out/iteration.json
 python scripts/bench_iteration.py mapping 2>> gpurun_out/extra.err | tail -1 > gpurun_out/mapping_iteration.json; cut -c1-400 gpurun_out/mapping_iteration.json
+python scripts/bench_iteration.py mapping_uncertainty 2>> gpurun_out/extra.err | tail -1 > gpurun_out/mapping_uncertainty_iteration.json; cut -c1-500 gpurun_out/mapping_uncertainty_iteration.json
+python scripts/bench_ssim.py 2>> gpurun_out/extra.err | tail -1 > gpurun_out/ssim.json; cat gpurun_out/ssim.json
 fi
 if [ -n "$NCU" ]; then
 python bench.py --steps 3 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/plain.log 2>&1 && \
