@@ -42,10 +42,16 @@ typedef struct WgsSsimArgs {
   float* maps;             /* (3,planes,H,W): written by forward (may be null: no backward wanted), read by backward */
   const float* dL_dmean;   /* backward: planes / planes_per_mean floats */
   float* dL_dimg1;         /* backward out: (planes,H,W) */
-  void* workspace;         /* wgs_ssim_workspace_bytes() bytes, 256-B aligned (forward only) */
+  void* workspace;         /* wgs_ssim_workspace_bytes() bytes, 256-B aligned (forward; backward when dL_dexposure is set) */
+  /* Exposure compensation fused in (slam_utils.py:111, :185-187): img1 is replaced by exp(a) * img1 + b before the
+   * windows are applied (zero padding stays zero).  exposure_a / exposure_b: 1 float each, or both null.  The backward
+   * then returns dL/dimg1 of the UNCOMPENSATED image and, if dL_dexposure is given, {dL/da, dL/db} (2 floats). */
+  const float* exposure_a;
+  const float* exposure_b;
+  float* dL_dexposure;
 } WgsSsimArgs;
 
-size_t wgs_ssim_workspace_bytes(int32_t width, int32_t height, int32_t planes);
+size_t wgs_ssim_workspace_bytes(int32_t width, int32_t height, int32_t planes);   /* covers forward and backward */
 /* return WGS_OK or a negative status of wgs_rasterizer.h; message via wgs_last_error() */
 int wgs_ssim_forward(const WgsSsimArgs* args, void* cuda_stream);
 int wgs_ssim_backward(const WgsSsimArgs* args, void* cuda_stream);
@@ -53,9 +59,10 @@ int wgs_ssim_backward(const WgsSsimArgs* args, void* cuda_stream);
 /* compute_ssim_components: img1, img2 (batch, channels, H, W); luminance / contrast / structure (batch, H, W), each the
  * mean over the channels of the clipped components (mapping_utils.py:166-204: sigma^2 >= eps, |s12| <= sqrt(s11 s22),
  * contrast and structure clamped at 0.98).  Forward only (the reference detaches them). */
+/* exposure_a / exposure_b (1 float each, or both null) compensate img2 -- the reference passes (gt, rendered) */
 int wgs_ssim_components(int32_t width, int32_t height, int32_t batch, int32_t channels, int32_t window,
-                        const float* img1, const float* img2, float* luminance, float* contrast, float* structure,
-                        void* cuda_stream);
+                        const float* img1, const float* img2, const float* exposure_a, const float* exposure_b,
+                        float* luminance, float* contrast, float* structure, void* cuda_stream);
 
 #ifdef __cplusplus
 }

@@ -151,6 +151,8 @@ def main():
     ref_dir = os.path.join(ROOT, "oracle", "_ref")
     if os.path.exists(os.path.join(ref_dir, "diff_gaussian_rasterization", "_C.so")):
         arms.append("reference")
+    if os.environ.get("ARMS"):
+        arms = [a for a in arms if a in os.environ["ARMS"].split(",")]
     for arm in arms:
         pc, cam = Model(g, 1), Cam(cam_d)
         cam.original_image = torch.from_numpy(rng.uniform(0, 1, (3, H, W)).astype(np.float32)).to(DEV)

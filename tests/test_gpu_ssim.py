@@ -88,3 +88,27 @@ def test_errors():
         loss_utils.ssim(a.cpu(), a.cpu())
     with pytest.raises(IndexError):
         loss_utils.ssim(a, a, size_average=False)
+
+
+def test_fused_exposure_matches_the_composition():
+    """ssim(img, gt, exposure=(a, b)) == ssim(exp(a) * img + b, gt) incl. the gradients w.r.t. img, a and b (the
+    composition runs the affine map and its backward in torch around the same kernels)."""
+    g = torch.Generator().manual_seed(9)
+    x0, y = torch.rand(3, 70, 90, generator=g).to(DEV), torch.rand(3, 70, 90, generator=g).to(DEV)
+    outs = []
+    for fused in (False, True):
+        x = x0.clone().requires_grad_(True)
+        a = torch.tensor([0.11], device=DEV, requires_grad=True)
+        b = torch.tensor([-0.03], device=DEV, requires_grad=True)
+        v = loss_utils.ssim(x, y, exposure=(a, b)) if fused else loss_utils.ssim(torch.exp(a) * x + b, y)
+        (3.0 * v).backward()
+        outs.append((v.item(), x.grad.clone(), a.grad.item(), b.grad.item()))
+    assert abs(outs[0][0] - outs[1][0]) < 1e-6
+    torch.testing.assert_close(outs[1][1], outs[0][1], rtol=1e-4, atol=1e-9)
+    assert abs(outs[0][2] - outs[1][2]) < 1e-4 * abs(outs[0][2]) + 1e-7
+    assert abs(outs[0][3] - outs[1][3]) < 1e-4 * abs(outs[0][3]) + 1e-7
+    lum0, con0, stu0 = loss_utils.compute_ssim_components(y, float(np.exp(0.11)) * x0 - 0.03, 7)
+    lum1, con1, stu1 = loss_utils.compute_ssim_components(y, x0, 7, exposure=(torch.tensor([0.11]), torch.tensor([-0.03])))
+    torch.testing.assert_close(lum1, lum0, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(con1, con0, rtol=1e-4, atol=1e-4)
+    assert ((stu1 - stu0).abs() > 1e-3).float().mean().item() < 1e-3

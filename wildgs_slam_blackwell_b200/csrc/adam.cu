@@ -35,18 +35,33 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const __grid_constan
         __syncthreads();
         step_size = s_corr[0]; bc2s = s_corr[1];
     }
+    auto update = [&](float g, float& m, float& v, float& w) {
+        m = m + w1 * (g - m);                       // exp_avg.lerp_(grad, 1 - beta1)
+        v = v * p.beta2 + w2 * g * g;               // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
+        const float denom = sqrtf(v) / bc2s + p.eps;
+        w = w - step_size * (m / denom);            // param.addcdiv_(exp_avg, denom, value=-step_size)
+    };
+    const bool vec = base + ADAM_EPT <= t.n &&
+                     (((uintptr_t)t.param | (uintptr_t)t.grad | (uintptr_t)t.exp_avg | (uintptr_t)t.exp_avg_sq) & 15u) == 0;
+    if (vec) {   // one 16-byte access per array
+        const float4 g = __ldg(reinterpret_cast<const float4*>(t.grad + base));
+        float4 m = *reinterpret_cast<float4*>(t.exp_avg + base), v = *reinterpret_cast<float4*>(t.exp_avg_sq + base);
+        float4 w = *reinterpret_cast<float4*>(t.param + base);
+        update(g.x, m.x, v.x, w.x); update(g.y, m.y, v.y, w.y); update(g.z, m.z, v.z, w.z); update(g.w, m.w, v.w, w.w);
+        *reinterpret_cast<float4*>(t.exp_avg + base) = m;
+        *reinterpret_cast<float4*>(t.exp_avg_sq + base) = v;
+        *reinterpret_cast<float4*>(t.param + base) = w;
+        return;
+    }
 #pragma unroll
     for (int k = 0; k < ADAM_EPT; k++) {
         const size_t i = base + k;
         if (i < t.n) {
-            const float g = __ldg(t.grad + i);
-            float m = t.exp_avg[i], v = t.exp_avg_sq[i];
-            m = m + w1 * (g - m);                       // exp_avg.lerp_(grad, 1 - beta1)
-            v = v * p.beta2 + w2 * g * g;               // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
-            const float denom = sqrtf(v) / bc2s + p.eps;
+            float m = t.exp_avg[i], v = t.exp_avg_sq[i], w = t.param[i];
+            update(__ldg(t.grad + i), m, v, w);
             t.exp_avg[i] = m;
             t.exp_avg_sq[i] = v;
-            t.param[i] = t.param[i] - step_size * (m / denom);   // param.addcdiv_(exp_avg, denom, value=-step_size)
+            t.param[i] = w;
         }
     }
 }

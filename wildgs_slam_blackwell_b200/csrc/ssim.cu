@@ -30,13 +30,17 @@ struct SsimParams {
     double* partial;   // [planes][gy*gx]
     float* mean;
     float* lum; float* con; float* str;
+    const float* ea; const float* eb;   // exposure (device scalars) or null
+    int exp_on;                         // which image is compensated: 1 = x1, 2 = x2, 0 = none
+    float* dexp;                        // backward: {dL/da, dL/db} or null
 };
 
+// gain/bias: exposure compensation of the pixels inside the image; the zero padding stays zero
 __device__ __forceinline__ void load_patch(float (*a)[SN + 1], const float* __restrict__ src, int W, int H, int x0,
-                                           int y0, int n) {
+                                           int y0, int n, float gain = 1.f, float bias = 0.f) {
     for (int i = threadIdx.x; i < n * n; i += 256) {
         const int r = i / n, c = i - r * n, gx = x0 + c, gy = y0 + r;
-        a[r][c] = (gx >= 0 && gx < W && gy >= 0 && gy < H) ? __ldg(src + (size_t)gy * W + gx) : 0.f;
+        a[r][c] = (gx >= 0 && gx < W && gy >= 0 && gy < H) ? fmaf(gain, __ldg(src + (size_t)gy * W + gx), bias) : 0.f;
     }
 }
 
@@ -49,8 +53,9 @@ __device__ __forceinline__ void moments(const SsimParams& p, float (*a)[SN + 1],
     const int R = RT >= 0 ? RT : p.R, n = ST + 2 * R, taps = 2 * R + 1;
     const int x0 = blockIdx.x * ST - R, y0 = blockIdx.y * ST - R;
     __syncthreads();   // previous user of the buffers is done
-    load_patch(a, x1, p.W, p.H, x0, y0, n);
-    load_patch(b, x2, p.W, p.H, x0, y0, n);
+    const float gain = p.exp_on ? expf(__ldg(p.ea)) : 1.f, bias = p.exp_on ? __ldg(p.eb) : 0.f;
+    load_patch(a, x1, p.W, p.H, x0, y0, n, p.exp_on == 1 ? gain : 1.f, p.exp_on == 1 ? bias : 0.f);
+    load_patch(b, x2, p.W, p.H, x0, y0, n, p.exp_on == 2 ? gain : 1.f, p.exp_on == 2 ? bias : 0.f);
     __syncthreads();
     for (int i = threadIdx.x; i < n * ST; i += 256) {
         const int r = i / ST, c = i - r * ST;
@@ -151,16 +156,48 @@ __global__ void __launch_bounds__(256) ssim_bwd_kernel(const __grid_constant__ S
     __syncthreads();
     const int tx = threadIdx.x & (ST - 1), ty = threadIdx.x / ST;
     const int px = blockIdx.x * ST + tx, py = blockIdx.y * ST + ty;
-    if (px >= p.W || py >= p.H) return;
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+    float ga = 0.f, gb = 0.f;   // this pixel's share of dL/da, dL/db
+    if (px < p.W && py < p.H) {
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f;
 #pragma unroll
-    for (int k = 0; k < taps; k++) {
-        const float w = p.w[k];
-        s0 = fmaf(w, h[0][ty + k][tx], s0); s1 = fmaf(w, h[1][ty + k][tx], s1); s2 = fmaf(w, h[2][ty + k][tx], s2);
+        for (int k = 0; k < taps; k++) {
+            const float w = p.w[k];
+            s0 = fmaf(w, h[0][ty + k][tx], s0); s1 = fmaf(w, h[1][ty + k][tx], s1); s2 = fmaf(w, h[2][ty + k][tx], s2);
+        }
+        const size_t o = plane * N + (size_t)py * p.W + px;
+        const float k = __ldg(p.dmean + plane / p.ppm) / ((float)p.ppm * (float)p.W * (float)p.H);
+        const float gain = p.exp_on ? expf(__ldg(p.ea)) : 1.f, bias = p.exp_on ? __ldg(p.eb) : 0.f;
+        const float x = __ldg(p.x1 + o), xc = fmaf(gain, x, bias);
+        const float g = k * (s0 + 2.f * xc * s1 + __ldg(p.x2 + o) * s2);   // dL / d(compensated img1)
+        p.out[o] = gain * g;
+        ga = g * gain * x; gb = g;
     }
-    const size_t o = plane * N + (size_t)py * p.W + px;
-    const float k = __ldg(p.dmean + plane / p.ppm) / ((float)p.ppm * (float)p.W * (float)p.H);
-    p.out[o] = k * (s0 + 2.f * __ldg(p.x1 + o) * s1 + __ldg(p.x2 + o) * s2);
+    if (p.dexp) {   // block partials; ssim_exposure_kernel sums them in a fixed order
+        __shared__ float red[2][8];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { ga += __shfl_xor_sync(0xffffffffu, ga, o); gb += __shfl_xor_sync(0xffffffffu, gb, o); }
+        if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = ga; red[1][threadIdx.x >> 5] = gb; }
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            double s = 0.0;
+            for (int i = 0; i < 8; i++) s += (double)red[threadIdx.x][i];
+            p.partial[2 * ((size_t)plane * (p.gx * p.gy) + blockIdx.y * p.gx + blockIdx.x) + threadIdx.x] = s;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) ssim_exposure_kernel(const __grid_constant__ SsimParams p) {
+    __shared__ double red[256];
+    const size_t n = (size_t)p.planes * p.gx * p.gy;
+    double s = 0.0;
+    for (size_t i = threadIdx.x; i < n; i += 256) s += p.partial[2 * i + blockIdx.x];
+    red[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) p.dexp[blockIdx.x] = (float)red[0];
 }
 
 // compute_ssim_components (mapping_utils.py:125-204): grid.z = batch item, channels looped inside
@@ -216,7 +253,7 @@ void wgs_set_error_message(const char* msg);
 size_t wgs_ssim_workspace_bytes(int32_t width, int32_t height, int32_t planes) {
     if (width <= 0 || height <= 0 || planes <= 0) return 256;
     const size_t blocks = (size_t)((width + ST - 1) / ST) * ((height + ST - 1) / ST) * planes;
-    return align_up(blocks * sizeof(double));
+    return align_up(2 * blocks * sizeof(double));
 }
 
 static int ssim_setup(const WgsSsimArgs* a, SsimParams& p, const char* who) {
@@ -229,6 +266,11 @@ static int ssim_setup(const WgsSsimArgs* a, SsimParams& p, const char* who) {
     p.gx = (p.W + ST - 1) / ST; p.gy = (p.H + ST - 1) / ST; p.C = 0;
     p.x1 = a->img1; p.x2 = a->img2; p.maps = a->maps; p.out = a->dL_dimg1; p.dmean = a->dL_dmean;
     p.partial = (double*)a->workspace; p.mean = a->mean; p.lum = p.con = p.str = nullptr;
+    if ((a->exposure_a == nullptr) != (a->exposure_b == nullptr)) {
+        wgs_set_error_message("wgs_ssim: exposure_a and exposure_b go together");
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    p.ea = a->exposure_a; p.eb = a->exposure_b; p.exp_on = a->exposure_a ? 1 : 0; p.dexp = nullptr;
     return WGS_OK;
 }
 
@@ -259,22 +301,30 @@ int wgs_ssim_backward(const WgsSsimArgs* a, void* cuda_stream) {
         wgs_set_error_message("wgs_ssim_backward: maps, dL_dmean and dL_dimg1 are required");
         return WGS_ERR_INVALID_ARGUMENT;
     }
+    if (a->dL_dexposure) {
+        if (!p.exp_on || !a->workspace || ((uintptr_t)a->workspace & 255u)) {
+            wgs_set_error_message("wgs_ssim_backward: dL_dexposure needs exposure_a/b and the workspace");
+            return WGS_ERR_INVALID_ARGUMENT;
+        }
+        p.dexp = a->dL_dexposure;
+    }
     const dim3 grid(p.gx, p.gy, p.planes);
     cudaStream_t s = (cudaStream_t)cuda_stream;
     if (p.R == 5) ssim_bwd_kernel<5><<<grid, 256, 0, s>>>(p);
     else if (p.R == 3) ssim_bwd_kernel<3><<<grid, 256, 0, s>>>(p);
     else ssim_bwd_kernel<-1><<<grid, 256, 0, s>>>(p);
+    if (p.dexp) ssim_exposure_kernel<<<2, 256, 0, s>>>(p);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { wgs_set_error_message(cudaGetErrorString(e)); return WGS_ERR_CUDA; }
     return WGS_OK;
 }
 
 int wgs_ssim_components(int32_t width, int32_t height, int32_t batch, int32_t channels, int32_t window,
-                        const float* img1, const float* img2, float* luminance, float* contrast, float* structure,
-                        void* cuda_stream) {
+                        const float* img1, const float* img2, const float* exposure_a, const float* exposure_b,
+                        float* luminance, float* contrast, float* structure, void* cuda_stream) {
     SsimParams p;
     if (width <= 0 || height <= 0 || batch <= 0 || batch > 65535 || channels <= 0 || !img1 || !img2 || !luminance ||
-        !contrast || !structure || !fill_window(p, window)) {
+        !contrast || !structure || (exposure_a == nullptr) != (exposure_b == nullptr) || !fill_window(p, window)) {
         wgs_set_error_message("wgs_ssim_components: bad size, window (odd, <= 11) or null pointer");
         return WGS_ERR_INVALID_ARGUMENT;
     }
@@ -282,6 +332,7 @@ int wgs_ssim_components(int32_t width, int32_t height, int32_t batch, int32_t ch
     p.gx = (p.W + ST - 1) / ST; p.gy = (p.H + ST - 1) / ST;
     p.x1 = img1; p.x2 = img2; p.maps = nullptr; p.out = nullptr; p.dmean = nullptr; p.partial = nullptr; p.mean = nullptr;
     p.lum = luminance; p.con = contrast; p.str = structure;
+    p.ea = exposure_a; p.eb = exposure_b; p.exp_on = exposure_a ? 2 : 0; p.dexp = nullptr;
     const dim3 grid(p.gx, p.gy, batch);
     cudaStream_t s = (cudaStream_t)cuda_stream;
     if (p.R == 5) ssim_components_kernel<5><<<grid, 256, 0, s>>>(p);

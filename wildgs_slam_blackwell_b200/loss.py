@@ -198,8 +198,7 @@ def get_loss_mapping_rgbd(config, image, depth, viewpoint, _exposure=(None, None
               depth_weight=1.0 - alpha)
     loss = _PhotometricLoss.apply(image, depth, _exposure[0], _exposure[1], kw)
     if lam:
-        image_ab = image if _exposure[0] is None else torch.exp(_exposure[0]) * image + _exposure[1]
-        loss = loss + (alpha * lam) * (1.0 - loss_utils.ssim(image_ab, gt))
+        loss = loss + (alpha * lam) * (1.0 - loss_utils.ssim(image, gt, exposure=_exposure))
     return loss
 
 
@@ -262,7 +261,6 @@ def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint
     if config.get("full_resolution", False) and tuple(rendered_depth.shape[-2:]) != (h, w):
         raise NotImplementedError("full_resolution with a depth map of another size than the image")
     depth_thr = _depth_threshold(viewpoint, ref_depth)
-    image_ab = rendered_img if initialization else torch.exp(ea) * rendered_img + eb
 
     uncertainty = uncertainty_network(viewpoint.features.to(device=dev))
     processed = torch.clip(uncertainty, min=0.1) + 1e-3
@@ -274,7 +272,8 @@ def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint
         # ---- uncertainty loss inputs (detached in the reference) ----
         op = opacity.detach().reshape(h, w)
         small_opacity = _resample(op, uncertainty.shape)
-        lum, con, stu = loss_utils.compute_ssim_components(gt, image_ab, window_size=ucfg["ssim_window_size"])
+        lum, con, stu = loss_utils.compute_ssim_components(gt, rendered_img, window_size=ucfg["ssim_window_size"],
+                                                            exposure=(ea, eb))
         ssim_weight = 100 + 900 * compute_bias_factor(ssim_frac, 0.8)
         ssim_l = torch.clip(op * ssim_weight * (1 - lum) * (1 - stu) * (1 - con), max=5.0)
         filtered = _median_pool_same(_resample(ssim_l, uncertainty.shape), ucfg["ssim_median_filter_size"])
@@ -293,6 +292,6 @@ def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint
               color_weight=alpha * (1.0 - lam), depth_weight=1.0 - alpha, depth_max=depth_thr, depth_weighted=True)
     total = _PhotometricLoss.apply(rendered_img, rendered_depth, ea, eb, kw)
     if lam:
-        total = total + (alpha * lam) * w_mean * (1.0 - loss_utils.ssim(image_ab, gt))
+        total = total + (alpha * lam) * w_mean * (1.0 - loss_utils.ssim(rendered_img, gt, exposure=(ea, eb)))
     total = total + ucfg["ssim_mult"] * uncer_loss.mean()
     return uncertainty, total
