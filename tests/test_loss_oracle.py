@@ -225,3 +225,20 @@ def test_mapping_uncertainty_oracle_matches_reference_golden(name, tf, sf, init,
         want = d[f"g_net{i}"]
         got = np.zeros_like(want) if p.grad is None else p.grad.numpy()
         np.testing.assert_allclose(got, want, rtol=1e-2, atol=2e-3 * max(np.abs(want).max(), 1e-12))
+
+
+def test_uncertainty_abi_symbols():
+    header = open(os.path.join(ROOT, "include", "wgs_uncertainty.h")).read()
+    code = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(wgs_[a-z_0-9]+)\s*\(", code))
+    assert declared == set(loss.EXPORTS_UNCERTAINTY), declared
+    lib = loss._lib_loss()
+    for name in declared:
+        assert hasattr(lib, name)
+    body = re.search(r"typedef struct WgsUncertaintyLossArgs \{(.*?)\} WgsUncertaintyLossArgs;", code, re.S).group(1)
+    names = [n for d in body.split(";") if d.strip() for n in
+             [x.strip().lstrip("*").strip() for x in re.sub(r"^\s*(const\s+)?\w+\s*\*?", "", d.strip(), count=1).split(",")]]
+    assert names == [f[0] for f in loss.UncertaintyLossArgs._fields_], names
+    assert lib.wgs_uncertainty_workspace_bytes(45, 34) >= 4 * 45 * 34 * 4
+    a = loss.UncertaintyLossArgs()
+    assert lib.wgs_uncertainty_loss(C.byref(a), None) == _lib.WGS_ERR_INVALID_ARGUMENT

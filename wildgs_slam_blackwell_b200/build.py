@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_build")
 LIB = os.path.join(HERE, "libwgs_rasterizer.so")
 SOURCES = ["api.cu", "preprocess_fwd.cu", "binning.cu", "render_fwd.cu", "render_bwd.cu", "preprocess_bwd.cu",
-           "loss.cu", "camera.cu", "peer_allreduce.cu", "knn.cu", "adam.cu", "pose.cu", "compact.cu", "ssim.cu"]
+           "loss.cu", "camera.cu", "peer_allreduce.cu", "knn.cu", "adam.cu", "pose.cu", "compact.cu", "ssim.cu", "uncertainty.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
          "--expt-relaxed-constexpr"]

@@ -40,7 +40,16 @@ class LossArgs(C.Structure):
     ]
 
 
+class UncertaintyLossArgs(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("patch_w", C.c_int32), ("patch_h", C.c_int32),
+                ("median", C.c_int32), ("ssim_weight", C.c_float), ("depth_threshold", C.c_float),
+                ("depth_mult", C.c_float), ("opacity_th", C.c_float), ("weight", C.c_float),
+                ("uncertainty", _fp), ("luminance", _fp), ("contrast", _fp), ("structure", _fp), ("opacity", _fp),
+                ("depth", _fp), ("ref_depth", _fp), ("loss", _fp), ("dL_duncertainty", _fp), ("workspace", _fp)]
+
+
 EXPORTS = ("wgs_loss_workspace_bytes", "wgs_photometric_loss")
+EXPORTS_UNCERTAINTY = ("wgs_uncertainty_workspace_bytes", "wgs_uncertainty_loss")
 _ws = {}
 _proto_done = False
 
@@ -52,6 +61,9 @@ def _lib_loss():
         lib.wgs_loss_workspace_bytes.restype = C.c_size_t
         lib.wgs_loss_workspace_bytes.argtypes = [C.c_int32, C.c_int32]
         lib.wgs_photometric_loss.argtypes = [C.POINTER(LossArgs), C.c_void_p]
+        lib.wgs_uncertainty_workspace_bytes.restype = C.c_size_t
+        lib.wgs_uncertainty_workspace_bytes.argtypes = [C.c_int32, C.c_int32]
+        lib.wgs_uncertainty_loss.argtypes = [C.POINTER(UncertaintyLossArgs), C.c_void_p]
         _proto_done = True
     return lib
 
@@ -217,15 +229,6 @@ def _resample(t, shape, mode="bilinear"):
     return F.interpolate(t.reshape((1, 1) + tuple(t.shape[-2:])), size=tuple(shape), mode=mode)[0, 0]
 
 
-def _median_pool_same(x, k):
-    """MedianPool2d(kernel_size=k, stride=1, same=True) of median_filter.py on an (H,W) map: reflect padding, window median"""
-    pl = (k - 1) // 2
-    pr = (k - 1) - pl
-    x = F.pad(x[None, None], (pl, pr, pl, pr), mode="reflect")
-    x = x.unfold(2, k, 1).unfold(3, k, 1)
-    return x.contiguous().view(x.shape[:4] + (-1,)).median(dim=-1)[0][0, 0]
-
-
 def _depth_threshold(viewpoint, ref_depth):
     """min(10 * median(ref_depth), 50) (mapping_utils.py:262-263): a property of the keyframe's reference depth, so it is
     computed (one host read) when the depth is first seen instead of on every iteration."""
@@ -239,6 +242,40 @@ def _depth_threshold(viewpoint, ref_depth):
     return cache[1]
 
 
+class _UncertaintyLoss(torch.autograd.Function):
+    """weight * mean(uncertainty loss) of mapping_utils.py:270-321 as a function of the network's uncertainty map; every
+    other input is detached in the reference.  Two launches (wgs_uncertainty_loss); the gradient is made in forward."""
+
+    @staticmethod
+    def forward(ctx, uncertainty, lum, con, stu, opacity, depth, ref_depth, kw):
+        dev = uncertainty.device
+        hp, wp = uncertainty.shape
+        h, w = lum.shape[-2:]
+        f = lambda t: _f32(t.detach(), dev, (h, w))
+        unc = _f32(uncertainty.detach(), dev)
+        ins = [f(t) for t in (lum, con, stu, opacity, depth, ref_depth)]
+        lib = _lib_loss()
+        out = torch.empty(hp * wp + 1, device=dev)
+        need = uncertainty.requires_grad and not kw["freeze"]
+        ws = torch.empty(int(lib.wgs_uncertainty_workspace_bytes(wp, hp)), dtype=torch.uint8, device=dev)
+        a = UncertaintyLossArgs(w, h, wp, hp, int(kw["median"]), float(kw["ssim_weight"]), float(kw["depth_threshold"]),
+                                float(kw["depth_mult"]), float(kw["opacity_th"]), float(kw["weight"]), unc.data_ptr(),
+                                *[t.data_ptr() for t in ins], out[hp * wp:].data_ptr(),
+                                out.data_ptr() if need else None, ws.data_ptr())
+        with torch.cuda.device(dev):
+            rc = lib.wgs_uncertainty_loss(C.byref(a), C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+        if rc != _lib.WGS_OK:
+            raise RuntimeError(f"wgs_uncertainty_loss failed ({rc}): {_lib.last_error()}")
+        ctx.need = need
+        if need:
+            ctx.save_for_backward(out[:hp * wp].view(hp, wp))
+        return out[hp * wp:].reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        return (ctx.saved_tensors[0] * g if ctx.need else None,) + (None,) * 7
+
+
 def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint, opacity, uncertainty_network,
                                  train_frac, ssim_frac, initialization=False, freeze_uncertainty_loss=False):
     """slam_utils.get_loss_mapping_uncertainty (slam_utils.py:146-258) with compute_mapping_loss_components
@@ -247,8 +284,9 @@ def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint
     The full-resolution work is fused: the uncertainty-weighted L1 colour and depth terms and their cotangents are
     ONE launch (wgs_photometric_loss: exposure, rgb mask, weights 0.5/u^2 with the 0.1 cut, depth mask with the
     10x-median bound, depth weighted where the reference depth lies in front), the SSIM term two launches, the
-    luminance/contrast/structure maps of the uncertainty loss one.  What stays in torch is the uncertainty MLP and the
-    patch-resolution part of the uncertainty loss (resampling, 5x5 median, log) -- a few thousand elements."""
+    luminance/contrast/structure maps of the uncertainty loss one, the patch-resolution uncertainty loss and its
+    gradient (resampling, 5x5 median, log) two (wgs_uncertainty_loss).  What stays in torch is the uncertainty MLP and
+    the up-sampling of its output to the per-pixel weights."""
     from . import loss_utils
     dev = rendered_img.device
     tr, ucfg = config["Training"], config["uncertainty_params"]
@@ -263,35 +301,22 @@ def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint
     depth_thr = _depth_threshold(viewpoint, ref_depth)
 
     uncertainty = uncertainty_network(viewpoint.features.to(device=dev))
-    processed = torch.clip(uncertainty, min=0.1) + 1e-3
     with torch.no_grad():
-        resized = _resample(processed, (h, w))
+        resized = _resample(torch.clip(uncertainty, min=0.1) + 1e-3, (h, w))
         resized = (resized - 0.1) * (1 + compute_bias_factor(train_frac, 0.8)) + 0.1
         weights = 0.5 / resized ** 2
         w_mean = torch.where(weights < 0.1, 0.0, weights).mean()
-        # ---- uncertainty loss inputs (detached in the reference) ----
-        op = opacity.detach().reshape(h, w)
-        small_opacity = _resample(op, uncertainty.shape)
         lum, con, stu = loss_utils.compute_ssim_components(gt, rendered_img, window_size=ucfg["ssim_window_size"],
                                                             exposure=(ea, eb))
-        ssim_weight = 100 + 900 * compute_bias_factor(ssim_frac, 0.8)
-        ssim_l = torch.clip(op * ssim_weight * (1 - lum) * (1 - stu) * (1 - con), max=5.0)
-        filtered = _median_pool_same(_resample(ssim_l, uncertainty.shape), ucfg["ssim_median_filter_size"])
-        dmask = ((ref_depth > 0.01) & (ref_depth < depth_thr)).reshape(rendered_depth.shape)
-        depth_l1 = torch.abs(rendered_depth * dmask - ref_depth * dmask)
-        small_depth_loss = _resample(torch.clip(depth_l1.reshape(h, w), max=5.0), uncertainty.shape, "bicubic")
-        small_depth = _resample(ref_depth.reshape(h, w), uncertainty.shape, "bicubic")
-        small_depth_loss = torch.where(small_depth > depth_thr, 0.0, small_depth_loss)
-    uncer_loss = (filtered / processed ** 2 + 0.5 * torch.log(processed)
-                  + ucfg["uncer_depth_mult"] * small_depth_loss / processed ** 2)
-    uncer_loss = torch.where(small_opacity < ucfg["opacity_th_for_uncer_loss"], 0.0, uncer_loss)
-    if freeze_uncertainty_loss:
-        uncer_loss = uncer_loss.detach()
+    uncer = _UncertaintyLoss.apply(uncertainty, lum, con, stu, opacity, rendered_depth, ref_depth, dict(
+        median=ucfg["ssim_median_filter_size"], ssim_weight=100 + 900 * compute_bias_factor(ssim_frac, 0.8),
+        depth_threshold=depth_thr, depth_mult=ucfg["uncer_depth_mult"], opacity_th=ucfg["opacity_th_for_uncer_loss"],
+        weight=ucfg["ssim_mult"], freeze=freeze_uncertainty_loss))
 
     kw = dict(gt_color=gt, gt_depth=ref_depth, uncertainty=resized, rgb_boundary_threshold=tr["rgb_boundary_threshold"],
               color_weight=alpha * (1.0 - lam), depth_weight=1.0 - alpha, depth_max=depth_thr, depth_weighted=True)
     total = _PhotometricLoss.apply(rendered_img, rendered_depth, ea, eb, kw)
     if lam:
         total = total + (alpha * lam) * w_mean * (1.0 - loss_utils.ssim(rendered_img, gt, exposure=(ea, eb)))
-    total = total + ucfg["ssim_mult"] * uncer_loss.mean()
+    total = total + uncer
     return uncertainty, total
