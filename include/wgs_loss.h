@@ -44,6 +44,10 @@ typedef struct WgsLossArgs {
   float depth_max;              /* > 0: the depth mask also needs gt_depth < depth_max (mapping_utils.py:262-266); 0: off */
   float depth_margin;           /* used when depth_weighted: 1.0 in the reference (slam_utils.py:241) */
   int32_t depth_weighted;       /* != 0: multiply l_depth by w where gt_depth < depth + depth_margin (needs uncertainty) */
+  int32_t patch_w, patch_h;     /* both > 0: `uncertainty` is the (patch_h, patch_w) network output and the per-pixel value
+                                   is made here (mapping_utils.py:270-277): bilinear(clip(u, 0.1) + 1e-3) to (H, W),
+                                   then (r - 0.1) * uncertainty_rate + 0.1.  Both 0: `uncertainty` is (H, W) as given */
+  float uncertainty_rate;       /* 1 + compute_bias_factor(train_frac, 0.8); used with patch_w / patch_h */
   const float* color;           /* (3,H,W) rendered colour */
   const float* depth;           /* (1,H,W) rendered depth; may be null iff depth_weight == 0 */
   const float* opacity;         /* (1,H,W) rendered opacity or null */
@@ -57,6 +61,7 @@ typedef struct WgsLossArgs {
   float* dL_dcolor;             /* out: (3,H,W) */
   float* dL_ddepth;             /* out: (1,H,W); may be null iff depth_weight == 0 */
   float* dL_dexposure;          /* out: 2 floats {dL/da, dL/db}; may be null iff exposure_a is null */
+  float* weight_mean;           /* out (optional): mean over (H, W) of w -- the factor of the SSIM term (slam_utils.py:226-230) */
   void* workspace;              /* wgs_loss_workspace_bytes(width, height) bytes, 256-B aligned; must be zero before
                                    the first call (the kernel leaves it zero again) */
 } WgsLossArgs;

@@ -17,7 +17,7 @@ struct LossParams {
     WgsLossArgs a;
     size_t N;
     int blocks;
-    double* partials;    // [blocks][4]: sum l_rgb, sum l_depth, dL/da, dL/db (unscaled by 1/(3N), 1/N)
+    double* partials;    // [blocks][5]: sum l_rgb, sum l_depth, dL/da, dL/db (unscaled by 1/(3N), 1/N), sum w
     unsigned int* ticket;
 };
 
@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
     float ea = 1.f, eb = 0.f;
     if (a.exposure_a) { ea = expf(__ldg(a.exposure_a)); eb = __ldg(a.exposure_b); }
     const float kc = a.color_weight / (3.0f * (float)N), kd = a.depth_weight / (float)N;
-    float s_rgb = 0.f, s_dep = 0.f, s_da = 0.f, s_db = 0.f;
+    float s_rgb = 0.f, s_dep = 0.f, s_da = 0.f, s_db = 0.f, s_w = 0.f;
     if (i0 < N) {
         float c[3][4], g[3][4], op[4], pm[4], un[4];
         {
@@ -61,8 +61,26 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
             op[0] = v.x; op[1] = v.y; op[2] = v.z; op[3] = v.w;
             v = a.pixel_mask ? ld4(a.pixel_mask, i0, N, 0.f) : make_float4(1.f, 1.f, 1.f, 1.f);
             pm[0] = v.x; pm[1] = v.y; pm[2] = v.z; pm[3] = v.w;
-            v = a.uncertainty ? ld4(a.uncertainty, i0, N, 1.f) : make_float4(1.f, 1.f, 1.f, 1.f);
-            un[0] = v.x; un[1] = v.y; un[2] = v.z; un[3] = v.w;
+            if (a.uncertainty && a.patch_w > 0) {
+                // patch-resolution network output -> per-pixel uncertainty (mapping_utils.py:270-277):
+                // bilinear(clip(u, 0.1) + 1e-3) (torch's align_corners=False formulas), then (r - 0.1) * rate + 0.1
+                const float sy = (float)a.patch_h / (float)a.height, sx = (float)a.patch_w / (float)a.width;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const size_t i = min(i0 + j, N - 1);
+                    const int py = (int)(i / a.width), px = (int)(i - (size_t)py * a.width);
+                    const float fy = fmaxf(sy * ((float)py + 0.5f) - 0.5f, 0.f), fx = fmaxf(sx * ((float)px + 0.5f) - 0.5f, 0.f);
+                    const int y0 = min((int)fy, a.patch_h - 1), y1 = min(y0 + 1, a.patch_h - 1);
+                    const int x0 = min((int)fx, a.patch_w - 1), x1 = min(x0 + 1, a.patch_w - 1);
+                    const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), lx = fminf(fmaxf(fx - (float)x0, 0.f), 1.f);
+                    auto u = [&](int y, int x) { return fmaxf(__ldg(a.uncertainty + y * a.patch_w + x), 0.1f) + 1e-3f; };
+                    const float r = (1.f - ly) * ((1.f - lx) * u(y0, x0) + lx * u(y0, x1)) + ly * ((1.f - lx) * u(y1, x0) + lx * u(y1, x1));
+                    un[j] = (r - 0.1f) * a.uncertainty_rate + 0.1f;
+                }
+            } else {
+                v = a.uncertainty ? ld4(a.uncertainty, i0, N, 1.f) : make_float4(1.f, 1.f, 1.f, 1.f);
+                un[0] = v.x; un[1] = v.y; un[2] = v.z; un[3] = v.w;
+            }
         }
         float dc[3][4], wj[4];
 #pragma unroll
@@ -76,6 +94,7 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
                 w = w < 0.1f ? 0.f : w;
             }
             wj[j] = w;
+            if (in) s_w += w;
             const float scale = in ? op[j] * w : 0.f;
 #pragma unroll
             for (int ch = 0; ch < 3; ch++) {
@@ -111,22 +130,22 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
         }
     }
     // block reduction (fixed order) -> partials; the last block sums the partials in block order
-    __shared__ double red[4][LOSS_THREADS / 32];
+    __shared__ double red[5][LOSS_THREADS / 32];
     __shared__ bool last;
-    double v[4] = {(double)s_rgb, (double)s_dep, (double)s_da, (double)s_db};
+    double v[5] = {(double)s_rgb, (double)s_dep, (double)s_da, (double)s_db, (double)s_w};
 #pragma unroll
-    for (int k = 0; k < 4; k++)
+    for (int k = 0; k < 5; k++)
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(0xffffffffu, v[k], o);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0)
 #pragma unroll
-        for (int k = 0; k < 4; k++) red[k][warp] = v[k];
+        for (int k = 0; k < 5; k++) red[k][warp] = v[k];
     __syncthreads();
-    if (threadIdx.x < 4) {
+    if (threadIdx.x < 5) {
         double s = 0.0;
         for (int wq = 0; wq < LOSS_THREADS / 32; wq++) s += red[threadIdx.x][wq];
-        p.partials[(size_t)blockIdx.x * 4 + threadIdx.x] = s;
+        p.partials[(size_t)blockIdx.x * 5 + threadIdx.x] = s;
     }
     __threadfence();
     __syncthreads();
@@ -134,9 +153,9 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
     __syncthreads();
     if (!last) return;
     __threadfence();
-    if (warp < 4) {
+    if (warp < 5) {
         double s = 0.0;
-        for (int b = lane; b < p.blocks; b += 32) s += __ldcg(p.partials + (size_t)b * 4 + warp);
+        for (int b = lane; b < p.blocks; b += 32) s += __ldcg(p.partials + (size_t)b * 5 + warp);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
         if (lane == 0) red[warp][0] = s;
@@ -146,6 +165,7 @@ __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __
         const double l = (double)a.color_weight * red[0][0] / (3.0 * (double)N) + (double)a.depth_weight * red[1][0] / (double)N;
         *a.loss = (float)l;
         if (a.dL_dexposure) { a.dL_dexposure[0] = (float)red[2][0]; a.dL_dexposure[1] = (float)red[3][0]; }
+        if (a.weight_mean) *a.weight_mean = (float)(red[4][0] / (double)N);
         *p.ticket = 0u;  // leave the workspace ready for the next call
     }
 }
@@ -162,7 +182,7 @@ static int loss_blocks(size_t N) {
 
 size_t wgs_loss_workspace_bytes(int32_t width, int32_t height) {
     if (width <= 0 || height <= 0) return 0;
-    return align_up(256 + (size_t)loss_blocks((size_t)width * height) * 4 * sizeof(double));
+    return align_up(256 + (size_t)loss_blocks((size_t)width * height) * 5 * sizeof(double));
 }
 
 void wgs_set_error_message(const char* msg);  // api.cu
@@ -171,6 +191,10 @@ int wgs_photometric_loss(const WgsLossArgs* a, void* cuda_stream) {
     if (!a || a->width <= 0 || a->height <= 0 || !a->color || !a->gt_color || !a->loss || !a->dL_dcolor ||
         !a->workspace || ((uintptr_t)a->workspace & 255u)) {
         wgs_set_error_message("wgs_photometric_loss: null/misaligned required pointer or bad size");
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    if (a->patch_w < 0 || a->patch_h < 0 || (a->patch_w > 0) != (a->patch_h > 0) || (a->patch_w > 0 && !a->uncertainty)) {
+        wgs_set_error_message("wgs_photometric_loss: patch_w / patch_h describe the uncertainty map: both > 0 or both 0");
         return WGS_ERR_INVALID_ARGUMENT;
     }
     if (a->depth_weighted && !a->uncertainty) {

@@ -21,7 +21,6 @@ import ctypes as C
 
 import numpy as np
 import torch
-import torch.nn.functional as F
 
 from . import _lib
 
@@ -34,9 +33,11 @@ class LossArgs(C.Structure):
         ("rgb_boundary_threshold", C.c_float), ("depth_min", C.c_float),
         ("color_weight", C.c_float), ("depth_weight", C.c_float),
         ("depth_max", C.c_float), ("depth_margin", C.c_float), ("depth_weighted", C.c_int32),
+        ("patch_w", C.c_int32), ("patch_h", C.c_int32), ("uncertainty_rate", C.c_float),
         ("color", _fp), ("depth", _fp), ("opacity", _fp), ("gt_color", _fp), ("gt_depth", _fp),
         ("pixel_mask", _fp), ("uncertainty", _fp), ("exposure_a", _fp), ("exposure_b", _fp),
-        ("loss", _fp), ("dL_dcolor", _fp), ("dL_ddepth", _fp), ("dL_dexposure", _fp), ("workspace", _fp),
+        ("loss", _fp), ("dL_dcolor", _fp), ("dL_ddepth", _fp), ("dL_dexposure", _fp), ("weight_mean", _fp),
+        ("workspace", _fp),
     ]
 
 
@@ -91,9 +92,10 @@ def _f32(t, device, shape=None):
 def photometric_loss(color, gt_color, *, depth=None, gt_depth=None, opacity=None, pixel_mask=None,
                      uncertainty=None, exposure_a=None, exposure_b=None, rgb_boundary_threshold=0.01,
                      depth_min=0.01, color_weight=1.0, depth_weight=0.0, depth_max=0.0, depth_weighted=False,
-                     depth_margin=1.0):
+                     depth_margin=1.0, uncertainty_rate=None, weight_mean=None):
     """One launch: returns (loss (1,), dL_dcolor (3,H,W), dL_ddepth (1,H,W), dL_dexposure (2,) or None).
-    See include/wgs_loss.h for the exact expression."""
+    See include/wgs_loss.h for the exact expression.  uncertainty_rate given: `uncertainty` is the patch-resolution
+    network output, up-sampled inside; weight_mean: a (1,) float tensor that receives mean(w)."""
     if color.dim() != 3 or color.shape[0] != 3:
         raise RuntimeError("color must have dimensions (3, H, W)")
     device = color.device
@@ -106,7 +108,12 @@ def photometric_loss(color, gt_color, *, depth=None, gt_depth=None, opacity=None
     gt_depth = _f32(gt_depth, device, (1, H, W))
     opacity = _f32(None if opacity is None else opacity.detach(), device, (1, H, W))
     pixel_mask = _f32(pixel_mask, device, (1, H, W))
-    uncertainty = _f32(uncertainty, device, (H, W))
+    patch = (0, 0)
+    if uncertainty_rate is not None:
+        patch = (int(uncertainty.shape[-1]), int(uncertainty.shape[-2]))
+        uncertainty = _f32(uncertainty.detach(), device)
+    else:
+        uncertainty = _f32(uncertainty, device, (H, W))
     ea = _f32(None if exposure_a is None else exposure_a.detach(), device, (1,))
     eb = _f32(None if exposure_b is None else exposure_b.detach(), device, (1,))
     if (ea is None) != (eb is None):
@@ -123,6 +130,9 @@ def photometric_loss(color, gt_color, *, depth=None, gt_depth=None, opacity=None
     a.rgb_boundary_threshold, a.depth_min = float(rgb_boundary_threshold), float(depth_min)
     a.color_weight, a.depth_weight = float(color_weight), float(depth_weight)
     a.depth_max, a.depth_margin, a.depth_weighted = float(depth_max), float(depth_margin), int(bool(depth_weighted))
+    a.patch_w, a.patch_h = patch
+    a.uncertainty_rate = float(uncertainty_rate) if uncertainty_rate is not None else 1.0
+    a.weight_mean = None if weight_mean is None else weight_mean.data_ptr()
     p = lambda t: None if t is None else t.data_ptr()
     a.color, a.depth, a.opacity, a.gt_color, a.gt_depth = p(color), p(depth), p(opacity), p(gt_color), p(gt_depth)
     a.pixel_mask, a.uncertainty, a.exposure_a, a.exposure_b = p(pixel_mask), p(uncertainty), p(ea), p(eb)
@@ -148,7 +158,9 @@ class _PhotometricLoss(torch.autograd.Function):
                                             rgb_boundary_threshold=kw["rgb_boundary_threshold"],
                                             color_weight=kw["color_weight"], depth_weight=kw["depth_weight"],
                                             depth_max=kw.get("depth_max", 0.0),
-                                            depth_weighted=kw.get("depth_weighted", False))
+                                            depth_weighted=kw.get("depth_weighted", False),
+                                            uncertainty_rate=kw.get("uncertainty_rate"),
+                                            weight_mean=kw.get("weight_mean"))
         ctx.has_depth = depth is not None and kw["depth_weight"] != 0.0
         ctx.has_exp = de is not None
         ctx.save_for_backward(dc, dd, de if de is not None else dc.new_empty(0))
@@ -224,11 +236,6 @@ def compute_bias_factor(x, s):
     return x / (1 + (1 - x) * (1 / s - 2))
 
 
-def _resample(t, shape, mode="bilinear"):
-    """mapping_utils.resample_tensor_to_shape: (H,W) -> shape"""
-    return F.interpolate(t.reshape((1, 1) + tuple(t.shape[-2:])), size=tuple(shape), mode=mode)[0, 0]
-
-
 def _depth_threshold(viewpoint, ref_depth):
     """min(10 * median(ref_depth), 50) (mapping_utils.py:262-263): a property of the keyframe's reference depth, so it is
     computed (one host read) when the depth is first seen instead of on every iteration."""
@@ -285,8 +292,8 @@ def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint
     ONE launch (wgs_photometric_loss: exposure, rgb mask, weights 0.5/u^2 with the 0.1 cut, depth mask with the
     10x-median bound, depth weighted where the reference depth lies in front), the SSIM term two launches, the
     luminance/contrast/structure maps of the uncertainty loss one, the patch-resolution uncertainty loss and its
-    gradient (resampling, 5x5 median, log) two (wgs_uncertainty_loss).  What stays in torch is the uncertainty MLP and
-    the up-sampling of its output to the per-pixel weights."""
+    gradient (resampling, 5x5 median, log) two (wgs_uncertainty_loss); the network's patch-resolution output is
+    up-sampled to the per-pixel weights inside the L1 launch.  What stays in torch is the uncertainty MLP."""
     from . import loss_utils
     dev = rendered_img.device
     tr, ucfg = config["Training"], config["uncertainty_params"]
@@ -302,10 +309,6 @@ def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint
 
     uncertainty = uncertainty_network(viewpoint.features.to(device=dev))
     with torch.no_grad():
-        resized = _resample(torch.clip(uncertainty, min=0.1) + 1e-3, (h, w))
-        resized = (resized - 0.1) * (1 + compute_bias_factor(train_frac, 0.8)) + 0.1
-        weights = 0.5 / resized ** 2
-        w_mean = torch.where(weights < 0.1, 0.0, weights).mean()
         lum, con, stu = loss_utils.compute_ssim_components(gt, rendered_img, window_size=ucfg["ssim_window_size"],
                                                             exposure=(ea, eb))
     uncer = _UncertaintyLoss.apply(uncertainty, lum, con, stu, opacity, rendered_depth, ref_depth, dict(
@@ -313,10 +316,12 @@ def get_loss_mapping_uncertainty(config, rendered_img, rendered_depth, viewpoint
         depth_threshold=depth_thr, depth_mult=ucfg["uncer_depth_mult"], opacity_th=ucfg["opacity_th_for_uncer_loss"],
         weight=ucfg["ssim_mult"], freeze=freeze_uncertainty_loss))
 
-    kw = dict(gt_color=gt, gt_depth=ref_depth, uncertainty=resized, rgb_boundary_threshold=tr["rgb_boundary_threshold"],
-              color_weight=alpha * (1.0 - lam), depth_weight=1.0 - alpha, depth_max=depth_thr, depth_weighted=True)
+    w_mean = torch.empty(1, device=dev)     # mean of the per-pixel weights, written by the L1 launch
+    kw = dict(gt_color=gt, gt_depth=ref_depth, uncertainty=uncertainty, rgb_boundary_threshold=tr["rgb_boundary_threshold"],
+              color_weight=alpha * (1.0 - lam), depth_weight=1.0 - alpha, depth_max=depth_thr, depth_weighted=True,
+              uncertainty_rate=1 + compute_bias_factor(train_frac, 0.8), weight_mean=w_mean)
     total = _PhotometricLoss.apply(rendered_img, rendered_depth, ea, eb, kw)
     if lam:
-        total = total + (alpha * lam) * w_mean * (1.0 - loss_utils.ssim(rendered_img, gt, exposure=(ea, eb)))
+        total = total + (alpha * lam) * w_mean[0] * (1.0 - loss_utils.ssim(rendered_img, gt, exposure=(ea, eb)))
     total = total + uncer
     return uncertainty, total
