@@ -16,7 +16,7 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-@pytest.mark.parametrize("P,frac", [(100_003, 0.7), (1, 1.0), (1, 0.0), (5000, 0.0), (5000, 1.0), (1025, 0.5), (2_000_000, 0.9)])
+@pytest.mark.parametrize("P,frac", [(100_003, 0.7), (0, 0.5), (1, 1.0), (1, 0.0), (5000, 0.0), (5000, 1.0), (1025, 0.5), (2_000_000, 0.9)])
 def test_compact_rows_equals_boolean_indexing(P, frac):
     g = torch.Generator(device=DEV).manual_seed(P)
     keep = torch.rand(P, device=DEV, generator=g) < frac
