@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define WGS_ABI_VERSION 8
+#define WGS_ABI_VERSION 9
 
 /* status codes (negative = error) */
 #define WGS_OK 0
@@ -155,6 +155,16 @@ typedef struct WgsBackwardArgs {
   int32_t activations;
   const float* sh_rest;
   float* dL_dsh_rest;
+  /* Densification statistics fused into the per-Gaussian backward (any may be null).  For every Gaussian with
+   * radii > 0 -- the visibility_filter of the callers -- this backward does what the mapper runs after it
+   * (src/mapper.py:1176-1182, gaussian_model.py:745-749):
+   *   stat_grad_accum[i] += || dL_dmeans2D[i, :2] ||      (xyz_gradient_accum, (P,1))
+   *   stat_denom[i]      += 1                             (denom, (P,1))
+   *   stat_max_radii[i]   = max(stat_max_radii[i], radii[i])   (max_radii2D, (P,) float)
+   * Whole-image backward only (tile_row_begin/end covering all rows): the norm is per view. */
+  float* stat_grad_accum;
+  float* stat_denom;
+  float* stat_max_radii;
 } WgsBackwardArgs;
 
 /* library / device */

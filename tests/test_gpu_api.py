@@ -358,3 +358,37 @@ def test_staged_sh_rows_match_cpu_oracle(P, deg, active):
         with rasterizer.grad_sink(bufs, accumulate=k > 0):
             ((color * dc).sum() + (depth * dd).sum()).backward()
         util.assert_grad_close("sh", bufs["sh"].cpu().numpy(), (k + 1.0) * ours["g_dL_dsh"])
+
+
+def test_fused_densification_statistics_match_the_mapper_procedure():
+    """rasterizer.densification_stats / WindowTrainer(densify_stats=True): the per-Gaussian backward kernel accumulates
+    what the mapper computes after each view's backward (mapper.py:1176-1182, gaussian_model.py:745-749):
+    sum over views of ||dL_dmeans2D[:, :2]|| and of the visibility counts, running max of the radii."""
+    from wildgs_slam_blackwell_b200.window import WindowTrainer
+    P = 4000
+    g, cams, cots = scenes.make_scene(P, 160, 112, 0, seed=43, n_views=3)
+    singles = [util.run_ours(g, cams[k], cots[k], export=False) for k in range(3)]
+    accum, denom, maxr = np.zeros((P, 1), np.float32), np.zeros((P, 1), np.float32), np.zeros(P, np.float32)
+    for s in singles:                                   # the reference's procedure, view by view
+        vis = s["radii"] > 0
+        accum[vis] += np.linalg.norm(s["g_dL_dmeans2D"][vis, :2], axis=-1, keepdims=True)
+        denom[vis] += 1
+        maxr[vis] = np.maximum(maxr[vis], s["radii"][vis])
+    params = {k: util.to_dev(g[k]).requires_grad_(True) for k in ("means3D", "sh", "opacities", "scales", "rotations")}
+    tr = WindowTrainer(params, sink_names={"means3D": "means3D", "sh": "sh", "opacities": "opacity", "scales": "scales",
+                                           "rotations": "rotations"}, densify_stats=True)
+    m2 = torch.zeros(P, 3, device=DEV, requires_grad=True)
+
+    def render_loss(v):
+        rast = rasterizer.GaussianRasterizer(util.settings_from_cam(cams[v], 0))
+        color, radii, depth, opacity, n_touched = rast(params["means3D"], m2, params["opacities"], shs=params["sh"],
+                                                       scales=params["scales"], rotations=params["rotations"])
+        return (color * util.to_dev(cots[v][0])).sum() + (depth * util.to_dev(cots[v][1])).sum(), None
+    for _ in range(2):                                  # per-window sums: the second step must not carry over
+        tr.step(3, render_loss)
+    util.assert_grad_close("xyz_gradient_accum", tr.grad_accum.cpu().numpy(), accum)
+    np.testing.assert_array_equal(tr.denom.cpu().numpy(), denom)
+    np.testing.assert_array_equal(tr.reduce_max_radii().cpu().numpy(), maxr)
+    with pytest.raises(RuntimeError, match="whole-image"):
+        with rasterizer.tile_rows(0, 2), rasterizer.densification_stats(tr.grad_accum, tr.denom, tr.max_radii):
+            render_loss(0)[0].backward()

@@ -195,3 +195,57 @@ def test_grad_bucket_layout_and_accumulation():
     assert b.matches(params) and not b.matches({"means3D": params["means3D"]})
     with pytest.raises(TypeError):
         GradBucket({"x": torch.zeros(3, dtype=torch.float64)})
+
+
+def _stats_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from wildgs_slam_blackwell_b200 import rasterizer
+        params = _params()
+        tr = WindowTrainer(params, densify_stats=True)
+        base = _make_render(params)
+
+        def render_loss(v):     # stand-in for the backward kernel: it fills whatever densification_stats holds
+            acc, den, mx = rasterizer.densification_stats._active.bufs if rasterizer.densification_stats._active else (None,) * 3
+            assert acc is None                                  # only active around backward(), not around the forward
+            loss, pg = base(v)
+
+            class Fill(torch.autograd.Function):
+                @staticmethod
+                def forward(ctx, x):
+                    return x.clone()
+
+                @staticmethod
+                def backward(ctx, g):
+                    a, d, m = rasterizer.densification_stats._active.bufs
+                    a += float(v + 1); d += 1.0; m.copy_(torch.maximum(m, torch.full_like(m, float(10 * v + rank))))
+                    return g
+            return Fill.apply(loss), pg
+        for _ in range(2):
+            tr.step(N_VIEWS, render_loss)
+        torch.save((tr.grad_accum.clone(), tr.denom.clone(), tr.reduce_max_radii().clone(), tr.bucket.nbytes),
+                   os.path.join(q, f"stats{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_window_densification_statistics_world2(tmp_path):
+    """the statistics segment rides in the gradient allreduce (SUM over ranks = over all views), per step; the radius
+    maximum is a MAX reduction on demand"""
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_stats_worker, args=(r, 2, port, str(tmp_path))) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    for r in range(2):
+        acc, den, mx, nbytes = torch.load(tmp_path / f"stats{r}.pt")
+        assert acc.shape == (P, 1) and bool((acc == sum(v + 1 for v in range(N_VIEWS))).all())
+        assert bool((den == N_VIEWS).all())
+        want = max(10 * max(views) + rk for rk, views in enumerate(assign_views([1.0] * N_VIEWS, 2)))
+        assert bool((mx == want).all())                         # identical on both ranks: MAX across ranks
+        assert nbytes == 4 * P * 7                              # nbytes counts the gradients only

@@ -5,7 +5,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libwgs_rasterizer.so")
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 WGS_OK = 0
 WGS_ERR_INVALID_ARGUMENT = -1
@@ -50,6 +50,7 @@ class BackwardArgs(C.Structure):
         ("geom", _fp), ("tile", _fp), ("binning", _fp), ("image", _fp), ("grad", _fp),
         ("capacity", C.c_int64), ("tile_row_begin", C.c_int32), ("tile_row_end", C.c_int32),
         ("activations", C.c_int32), ("sh_rest", _fp), ("dL_dsh_rest", _fp),
+        ("stat_grad_accum", _fp), ("stat_denom", _fp), ("stat_max_radii", _fp),
     ]
 
 

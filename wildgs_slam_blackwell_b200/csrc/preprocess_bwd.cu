@@ -351,6 +351,11 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
 #pragma unroll
             for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q4[k] * qd) * rcpf(qn);
         }
+        if (live && rad > 0) {   // mapper.py:1176-1182 + add_densification_stats (gaussian_model.py:745-749), visibility = radii > 0
+            if (p.stat_grad_accum) p.stat_grad_accum[idx] += sqrtf(dm2x * dm2x + dm2y * dm2y);
+            if (p.stat_denom) p.stat_denom[idx] += 1.f;
+            if (p.stat_max_radii) p.stat_max_radii[idx] = fmaxf(p.stat_max_radii[idx], (float)rad);
+        }
         if (live) {
         if (p.dL_dmeans3D) { gput(p.dL_dmeans3D, 3 * idx, dmean.x, accm); gput(p.dL_dmeans3D, 3 * idx + 1, dmean.y, accm); gput(p.dL_dmeans3D, 3 * idx + 2, dmean.z, accm); }
         if (p.dL_dmeans2D) { gput(p.dL_dmeans2D, 3 * idx, dm2x, accm); gput(p.dL_dmeans2D, 3 * idx + 1, dm2y, accm); gput(p.dL_dmeans2D, 3 * idx + 2, 0.f, accm); }

@@ -228,6 +228,27 @@ class grad_sink:
         return False
 
 
+class densification_stats:
+    """Context manager: while active, every backward also does what the mapper runs after it on the same view
+    (src/mapper.py:1176-1182, GaussianModel.add_densification_stats): for the Gaussians with radii > 0,
+    `xyz_gradient_accum += ||dL_dmeans2D[:, :2]||`, `denom += 1`, `max_radii2D = max(max_radii2D, radii)` -- inside
+    the per-Gaussian backward kernel, so the window needs neither the (P,3) dL_dmeans2D tensor nor the ~12 indexing
+    kernels per view.  Tensors: float32 CUDA, P elements each (any may be None).  Whole-image backward only."""
+    _active = None
+
+    def __init__(self, xyz_gradient_accum=None, denom=None, max_radii2D=None):
+        self.bufs = (xyz_gradient_accum, denom, max_radii2D)
+
+    def __enter__(self):
+        self._prev = densification_stats._active
+        densification_stats._active = self
+        return self
+
+    def __exit__(self, *exc):
+        densification_stats._active = self._prev
+        return False
+
+
 def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii,
                  grad_out_color, grad_out_depth, sink=None):
     """Runs the backward through the C ABI.  Returns dict of gradient tensors (+ 'tau' (6,))."""
@@ -281,6 +302,12 @@ def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_p
         b.capacity = fa.capacity
         b.tile_row_begin, b.tile_row_end = fa.tile_row_begin, fa.tile_row_end
         b.activations, b.sh_rest, b.dL_dsh_rest = fa.activations, fa.sh_rest, _ptr(g["sh_rest"])
+        stats = densification_stats._active
+        if stats is not None:
+            for t in stats.bufs:
+                if t is not None and (t.numel() != P or t.dtype != torch.float32 or t.device != device or not t.is_contiguous()):
+                    raise RuntimeError(f"densification_stats buffers must be contiguous float32 tensors of {P} elements on {device}")
+            b.stat_grad_accum, b.stat_denom, b.stat_max_radii = (_ptr(t) for t in stats.bufs)
         if P > 0:
             b.grad = _grad_workspace(device, P).data_ptr()
         rc = lib.wgs_backward(ctx, C.byref(b), _stream_ptr(device))

@@ -65,8 +65,11 @@ class GradBucket:
     per-leaf views into it.  Installing the views as `.grad` makes autograd accumulate straight into
     the buffer, so the allreduce needs no packing copy."""
 
-    def __init__(self, params: Dict[str, torch.Tensor], peer_group=None, peer_mode: str = "auto", side_floats: int = 0):
-        """side_floats: extra floats behind the gradients (`self.side`) that ride in the same allreduce -- the window's
+    def __init__(self, params: Dict[str, torch.Tensor], peer_group=None, peer_mode: str = "auto", side_floats: int = 0,
+                 stat_floats: int = 0):
+        """stat_floats: floats between the gradients and the side block (`self.stats`), summed by the same allreduce --
+        the window's densification statistics.
+        side_floats: extra floats behind the gradients (`self.side`) that ride in the same allreduce -- the window's
         per-view losses / costs / pose gradients, so that a step is ONE collective.
         peer_group: a process group whose ranks share one NVLink domain -> the buffer is allocated in
         symmetric peer memory (peer.PeerBucket) and all_reduce() runs the library's own kernel instead of
@@ -80,11 +83,11 @@ class GradBucket:
             from .peer import PeerBucket
             world = dist.get_world_size(peer_group)
             mc = peer_mode == "nvls" or (peer_mode == "auto" and world >= 4)
-            self.peer = PeerBucket(n + side_floats, first.device, peer_group, use_multicast=mc)
+            self.peer = PeerBucket(n + side_floats + stat_floats, first.device, peer_group, use_multicast=mc)
             self._all = self.peer.flat
         else:
-            self._all = torch.zeros(n + side_floats, dtype=torch.float32, device=first.device)
-        self.flat, self.side = self._all[:n], self._all[n:]
+            self._all = torch.zeros(n + side_floats + stat_floats, dtype=torch.float32, device=first.device)
+        self.flat, self.stats, self.side = self._all[:n], self._all[n:n + stat_floats], self._all[n + stat_floats:]
         self.views: Dict[str, torch.Tensor] = {}
         off = 0
         for k, p in params.items():
@@ -126,6 +129,10 @@ class WindowTrainer:
     either None or a callable returning that view's pose gradient (6,) AFTER backward.  After step():
     every leaf's .grad holds the gradient summed over ALL views of the window (identical on every
     rank), `out["losses"]` (n_views,), `out["pose_grads"]` (n_views, 6), `out["assignment"]`.
+    With densify_stats=True the backward kernels also accumulate the densification statistics of the window
+    (rasterizer.densification_stats): after step(), `trainer.grad_accum` / `trainer.denom` (P,1) hold the sums over ALL
+    views of ||dL_dmeans2D[:, :2]|| and of the visibility counts (add them to GaussianModel.xyz_gradient_accum / denom),
+    `trainer.max_radii` the running maximum of this rank's views (reduce_max_radii() before it is used).
     """
 
     SIDE_FLOATS = 8 * 64   # (loss, cost, pose gradient) of up to 64 views ride behind the gradients in the bucket
@@ -152,7 +159,8 @@ class WindowTrainer:
         return {"losses": side[:, 0], "pose_grads": side[:, 2:8], "assignment": assignment, "bucket_bytes": b.nbytes}
 
     def __init__(self, params: Dict[str, torch.Tensor], group: Optional[dist.ProcessGroup] = None,
-                 sink_names: Optional[Dict[str, str]] = None, peer: bool = False, peer_mode: str = "auto"):
+                 sink_names: Optional[Dict[str, str]] = None, peer: bool = False, peer_mode: str = "auto",
+                 densify_stats: bool = False):
         """`sink_names` (optional): leaf name -> rasterizer gradient name ('means3D', 'sh', 'opacity',
         'scales', 'rotations', ...).  When given, the rasterizer's backward kernel writes / accumulates
         straight into the bucket (rasterizer.grad_sink) instead of autograd allocating per-view
@@ -166,13 +174,36 @@ class WindowTrainer:
         # peer=True: bucket in NVLink peer memory, summed by wgs_peer_allreduce (single node, CUDA only)
         self._peer_group = (group if group is not None else dist.group.WORLD) if (peer and self.world > 1) else None
         self._peer_mode = peer_mode
-        self.bucket = GradBucket(params, self._peer_group, peer_mode, self.SIDE_FLOATS)
+        self._stats = bool(densify_stats)
+        self.bucket = self._make_bucket(params)
         self.costs: List[float] = []
+
+    def _make_bucket(self, params):
+        P = next(iter(params.values())).shape[0]
+        b = GradBucket(params, self._peer_group, self._peer_mode, self.SIDE_FLOATS, 2 * P if self._stats else 0)
+        if self._stats:
+            # window sums of ||dL_dmeans2D[:, :2]|| and of the visibility counts ride in the bucket; the
+            # screen-space radius needs a MAX: kept per rank, reduced on demand (reduce_max_radii)
+            self.grad_accum, self.denom = b.stats[:P].view(P, 1), b.stats[P:].view(P, 1)
+            self.max_radii = torch.zeros(P, dtype=torch.float32, device=b.flat.device)
+        return b
+
+    def _stats_ctx(self):
+        if not self._stats:
+            return _null()
+        from . import rasterizer
+        return rasterizer.densification_stats(self.grad_accum, self.denom, self.max_radii)
+
+    def reduce_max_radii(self):
+        """max over the ranks of the running screen-space radius (GaussianModel.max_radii2D's update, mapper.py:1176-1179)"""
+        if self.world > 1:
+            dist.all_reduce(self.max_radii, op=dist.ReduceOp.MAX, group=self.group)
+        return self.max_radii
 
     def rebind(self, params: Dict[str, torch.Tensor]):
         """Call after densify/prune changed the number of Gaussians."""
         if not self.bucket.matches(params):
-            self.bucket = GradBucket(params, self._peer_group, self._peer_mode, self.SIDE_FLOATS)
+            self.bucket = self._make_bucket(params)
         else:
             self.bucket.params = params
 
@@ -198,13 +229,16 @@ class WindowTrainer:
         else:
             b.install()
         side, fused = self._side(n_views)  # loss, cost, pose grad (6)
+        if self._stats:
+            b.stats.zero_()
         for n_done, v in enumerate(mine):
             loss, pose_grad_fn = render_loss(v)
-            if use_sink:
-                with rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0):
+            with self._stats_ctx():
+                if use_sink:
+                    with rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0):
+                        loss.backward()
+                else:
                     loss.backward()
-            else:
-                loss.backward()
             side[v, 0] = loss.detach()
             side[v, 1].fill_(float(cost_fn(v)) if cost_fn is not None else 1.0)  # fill_: no H2D copy (graph capture)
             if pose_grad_fn is not None:
@@ -215,6 +249,8 @@ class WindowTrainer:
 
     def _step_strips(self, n_views, render_loss, cost_fn, tile_rows):
         from . import rasterizer
+        if self._stats:
+            raise RuntimeError("densify_stats needs whole views (the gradient norm is per view): call step() without tile_rows")
         plan = assign_strips(self.costs, self.world, tile_rows)
         mine = plan[self.rank]
         b = self.bucket
