@@ -93,3 +93,50 @@ def test_empty_scene_is_background():
         np.testing.assert_array_equal(o["color"][ch], np.full_like(o["color"][ch], cam["bg"][ch]))
     assert int(o["num_rendered"]) == 0 and not o["opacity"].any()
     np.testing.assert_array_equal(o["dL_dtau"], np.zeros(6, np.float32))
+
+
+def test_pose_and_parameter_gradients_are_derivatives_of_the_rendered_loss():
+    """Correctness, not agreement: central finite differences of L = <color, dc> + <depth, dd> through the
+    oracle's own forward -- along the six pose directions (left perturbation W2C <- SE3_exp(h e_i) W2C, the consumer's
+    convention, pose_utils.py:81-98) and along random directions of means3D / opacity / sh / scales -- against the
+    analytic dL_dtau and parameter gradients.  The forward is discontinuous where the analytic gradient is not (pixels
+    enter or leave a footprint at alpha = 1/255, tile rectangles are rounded), so the scene is smooth (large,
+    translucent Gaussians) and the cotangents vary slowly over the image; the remaining gap (2-5 %, always the finite
+    difference slightly larger) is those boundary terms.  With white-noise cotangents they reach 20 %."""
+    from wildgs_slam_blackwell_b200 import scenes
+    W, H, P = 64, 48, 250
+    cam = scenes.make_camera(W, H, 77)
+    g = scenes.make_gaussians(P, W, H, 1, 77, cam)
+    g = dict(g, scales=(g["scales"] * 8.0).astype(np.float32), opacities=np.clip(g["opacities"] * 0.5, 0.05, 0.3).astype(np.float32))
+    yy, xx = np.mgrid[0:H, 0:W]
+    smooth = (np.sin(xx / 9.0) + np.cos(yy / 7.0)).astype(np.float32)
+    dc = (np.stack([smooth, 0.5 * smooth + 0.3, -smooth]) / (3 * H * W)).astype(np.float32)
+    dd = (smooth[None] / (H * W)).astype(np.float32)
+    rng = np.random.default_rng(5)
+
+    def loss(gg, cc):
+        o = cpu_oracle.forward_backward(gg, cc)
+        return float((o["color"].astype(np.float64) * dc).sum() + (o["depth"].astype(np.float64) * dd).sum())
+
+    def moved(tau_h):
+        w2c = scenes.se3_exp(tau_h) @ cam["w2c"]
+        view = w2c.T.astype(np.float32)
+        return dict(cam, w2c=w2c, viewmatrix=np.ascontiguousarray(view), campos=np.linalg.inv(w2c)[:3, 3].astype(np.float32),
+                    projmatrix=np.ascontiguousarray((view.astype(np.float64) @ cam["projmatrix_raw"].astype(np.float64)).astype(np.float32)))
+
+    o = cpu_oracle.forward_backward(g, cam, (dc, dd))
+    tau = o["dL_dtau"].astype(np.float64)
+    num, h = np.zeros(6), 5e-4
+    for i in range(6):
+        e = np.zeros(6)
+        e[i] = h
+        num[i] = (loss(g, moved(e)) - loss(g, moved(-e))) / (2 * h)
+    assert np.linalg.norm(num - tau) < 0.06 * np.linalg.norm(tau), (num, tau)
+    for name, key, h in (("means3D", "g_dL_dmeans3D", 1e-3), ("opacities", "g_dL_dopacity", 2e-3), ("sh", "g_dL_dsh", 5e-3),
+                         ("scales", "g_dL_dscales", 1e-3)):
+        d = rng.normal(0, 1, g[name].shape)
+        gp, gm = dict(g), dict(g)
+        gp[name], gm[name] = (g[name] + h * d).astype(np.float32), (g[name] - h * d).astype(np.float32)
+        fd = (loss(gp, cam) - loss(gm, cam)) / (2 * h)
+        ana = float((o[key].astype(np.float64) * d).sum())
+        assert abs(fd - ana) < 0.06 * abs(ana) + 1e-7, (name, fd, ana)
