@@ -203,8 +203,11 @@ def _stats_worker(rank, world, port, q):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from wildgs_slam_blackwell_b200 import rasterizer
-        params = _params()
+        params = _params(seed=rank)                             # ranks start apart ...
         tr = WindowTrainer(params, densify_stats=True)
+        tr.broadcast_params(0)                                  # ... and are replicated from rank 0
+        same = _params(seed=0)
+        assert all(torch.equal(params[k], same[k]) for k in params)
         base = _make_render(params)
 
         def render_loss(v):     # stand-in for the backward kernel: it fills whatever densification_stats holds

@@ -200,6 +200,12 @@ class WindowTrainer:
             dist.all_reduce(self.max_radii, op=dist.ReduceOp.MAX, group=self.group)
         return self.max_radii
 
+    def broadcast_params(self, src: int = 0):
+        """Replicate the parameter tensors from rank `src` (after densify / prune changed them there)."""
+        if self.world > 1:
+            for p in self.bucket.params.values():
+                dist.broadcast(p.data, src=src, group=self.group)
+
     def rebind(self, params: Dict[str, torch.Tensor]):
         """Call after densify/prune changed the number of Gaussians."""
         if not self.bucket.matches(params):
