@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
     unsigned vmask = 0;
     {
         // Issue every load this Gaussian can need before looking at radii, so that the latencies
-        // overlap (the kernel is latency-bound: 108 registers, 2 CTAs/SM).  Accumulator records of
+        // overlap (the kernel is latency-bound: 80 registers, 3 CTAs/SM).  Accumulator records of
         // culled Gaussians are never written, so they read as zero.
         const int rad = __ldg(p.radii + idx);
         float4 g0 = __ldcg(p.grad.acc + 3 * idx), g1 = __ldcg(p.grad.acc + 3 * idx + 1), g2 = __ldcg(p.grad.acc + 3 * idx + 2);
