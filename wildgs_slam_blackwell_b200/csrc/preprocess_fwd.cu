@@ -10,13 +10,11 @@
 
 namespace wgs {
 
-__device__ __forceinline__ void cov3d_from_scale_rot(const float* __restrict__ scales,
-                                                     const float* __restrict__ rots, int idx, float mod,
-                                                     bool act, float c[6]) {
+// sq = {scale xyz, quaternion rxyz}, loaded by the caller (all loads of a Gaussian are issued up front)
+__device__ __forceinline__ void cov3d_from_scale_rot(const float sq[7], float mod, bool act, float c[6]) {
     // reference computeCov3D (forward.cu:120-154); quaternion (r,x,y,z) is NOT normalised
-    float s0 = __ldg(scales + 3 * idx), s1 = __ldg(scales + 3 * idx + 1), s2 = __ldg(scales + 3 * idx + 2);
-    float r = __ldg(rots + 4 * idx), x = __ldg(rots + 4 * idx + 1), y = __ldg(rots + 4 * idx + 2),
-          z = __ldg(rots + 4 * idx + 3);
+    float s0 = sq[0], s1 = sq[1], s2 = sq[2];
+    float r = sq[3], x = sq[4], y = sq[5], z = sq[6];
     if (act) {
         // raw-parameter mode: GaussianModel.get_scaling = exp(_scaling), get_rotation =
         // F.normalize(_rotation) = q / max(|q|, 1e-12)  (gaussian_model.py:54-63,77-83)
@@ -124,13 +122,24 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
     const int lane = threadIdx.x & 31;
     uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
     bool visible = false;
-    float px = 0.f, py = 0.f, pz = 0.f, depth = 0.f;
+    float px = 0.f, py = 0.f, pz = 0.f, depth = 0.f, opac_raw = 0.f;
     float mx = 0.f, my = 0.f, cnx = 0.f, cny = 0.f, cnz = 0.f;
     if (idx < p.P) {
         const float* __restrict__ V = p.viewmatrix;
         const float* __restrict__ Pm = p.projmatrix;
         px = __ldg(p.means3D + 3 * idx); py = __ldg(p.means3D + 3 * idx + 1);
         pz = __ldg(p.means3D + 3 * idx + 2);
+        // Issue every load this Gaussian can need before the frustum test, so that the DRAM round trips overlap
+        // instead of chaining means -> (depth test) -> scales/rotation -> (visible) -> opacity (the kernel is
+        // latency-bound); culled Gaussians pay 32 B of extra traffic.
+        float sq[7] = {0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f};
+        if (!p.cov3D_precomp) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) sq[k] = __ldg(p.scales + 3 * idx + k);
+#pragma unroll
+            for (int k = 0; k < 4; k++) sq[3 + k] = __ldg(p.rotations + 4 * idx + k);
+        }
+        opac_raw = __ldg(p.opacities + idx);
         depth = dot3p(px, py, pz, V[2], V[6], V[10], V[14]);
         int radius = 0;
         if (depth <= 0.2f) {  // in_frustum (auxiliary.h:139-164)
@@ -146,7 +155,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
 #pragma unroll
                 for (int k = 0; k < 6; k++) c[k] = __ldg(p.cov3D_precomp + 6 * idx + k);
             } else {
-                cov3d_from_scale_rot(p.scales, p.rotations, idx, p.scale_modifier, p.act != 0, c);
+                cov3d_from_scale_rot(sq, p.scale_modifier, p.act != 0, c);
             }
             // computeCov2D (forward.cu:76-115)
             const float tx = dot3p(px, py, pz, V[0], V[4], V[8], V[12]);
@@ -216,7 +225,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_consta
                     rgb = sh_to_rgb<false>(sh0, shr, p.D, px, py, pz, p.campos, cb);
                 }
             }
-            float o = __ldg(p.opacities + idx);
+            float o = opac_raw;
             if (p.act) o = DIV(1.f, ADD(1.f, expf(-o)));  // torch.sigmoid (gaussian_model.py:59,95-97)
             p.geom.rec[2 * idx] = make_float4(mx, my, cnx, cny);
             p.geom.rec[2 * idx + 1] = make_float4(cnz, o, depth, logf(255.f * o));
