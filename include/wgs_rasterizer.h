@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define WGS_ABI_VERSION 9
+#define WGS_ABI_VERSION 10
 
 /* status codes (negative = error) */
 #define WGS_OK 0
@@ -55,6 +55,9 @@ typedef struct WgsWorkspaceSizes {
  * (RAST/cuda_rasterizer/rasterizer.h:32-58, rasterizer_impl.cu:198-344).
  * A null pointer means "absent", as the reference's empty tensors do. */
 typedef struct WgsForwardArgs {
+  uint32_t struct_size; /* = sizeof(WgsForwardArgs) of the header the caller was built against; a binding made
+                           for an older (shorter) layout is rejected with WGS_ERR_INVALID_ARGUMENT instead of
+                           being read past its end */
   int32_t P;          /* number of Gaussians (0 is legal: outputs are background-only) */
   int32_t sh_degree;  /* active SH degree D (0..3) */
   int32_t M;          /* SH coefficients stored per Gaussian (sh is (P,M,3)); 0 if sh absent */
@@ -110,6 +113,7 @@ typedef struct WgsForwardArgs {
  * (rasterizer.h:60-91, rasterizer_impl.cu:348-455) + the torch.sum over dL_dtau in
  * RAST/diff_gaussian_rasterization/__init__.py:152-154 (folded into the kernel). */
 typedef struct WgsBackwardArgs {
+  uint32_t struct_size; /* = sizeof(WgsBackwardArgs), checked like WgsForwardArgs::struct_size */
   int32_t P, sh_degree, M, width, height;
   float tanfovx, tanfovy, scale_modifier;
   int32_t debug;
@@ -190,12 +194,23 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* args, void* cuda_stream
 /* No-wait operation.  The reference blocks the host once per forward on a D2H copy of R
  * (rasterizer_impl.cu:283-284); wgs_forward waits on a 4-byte pinned word instead.  When the stream is
  * being captured into a CUDA graph, or after wgs_set_async(ctx, 1), wgs_forward does not wait at all:
- * *num_rendered is -1, kernels whose instance count exceeds `capacity` exit without touching memory
- * (outputs are then undefined), and the caller checks wgs_last_num_rendered() after synchronising the
- * stream (or after a graph replay): it returns WGS_ERR_CAPACITY if the most recent forward on this
- * context overflowed, with the needed size in *num_rendered. */
+ * *num_rendered is -1.  A forward whose instance count exceeds `capacity` then writes the background
+ * colour / zero depth and opacity (its backward produces zero gradients) and records the overflow in a
+ * STICKY per-context device word: wgs_overflow_status() reports, after the caller has synchronised, how
+ * many forwards on this context overflowed since the word was last cleared and the largest instance count
+ * any of them needed -- so one check after 100 graph replays, or after a window of several views per
+ * replay, sees an overflow of ANY of them (wgs_last_num_rendered only knows the most recent forward).
+ * Returns WGS_ERR_CAPACITY when the count is non-zero; `clear` != 0 resets the word. */
 int wgs_set_async(WgsContext* ctx, int enable);
 int wgs_last_num_rendered(WgsContext* ctx, int64_t* num_rendered, int64_t* capacity);
+int wgs_overflow_status(WgsContext* ctx, int64_t* overflowed_forwards, int64_t* max_num_rendered, int clear);
+
+/* Debug counting pass for the roofline report (no reference counterpart): replays the
+ * compositing of the forward that `args` describes and returns, in two device u64 words,
+ *   counts[0] = N_eval  = sum over pixels of n_contrib (list entries a pixel must visit)
+ *   counts[1] = N_blend = (pixel, Gaussian) pairs that pass both alpha tests and are composited.
+ * Not part of any timed path. */
+int wgs_count_pairs(const WgsForwardArgs* args, uint64_t* counts, void* cuda_stream);
 
 /* Replaces markVisible (RAST/rasterize_points.cu:213-232, rasterizer_impl.cu:54-66,141-153):
  * present[i] = view-space z > 0.2.  `present` is (P,) bytes (torch.bool). */

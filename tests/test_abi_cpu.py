@@ -104,3 +104,72 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.replace("the oracle", ""), f
     assert "oracle" not in open(os.path.join(ROOT, "diff_gaussian_rasterization", "__init__.py")).read()
+
+
+def _integration_block(marker):
+    """The fenced python block of INTEGRATION.md that starts with `# --- <marker>`."""
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    for block in re.findall(r"```python\n(.*?)```", doc, re.S):
+        if block.startswith("# --- " + marker):
+            return block
+    raise AssertionError(f"INTEGRATION.md has no '{marker}' block")
+
+
+def test_integration_md_structs_match_the_library():
+    """The reference-side binding INTEGRATION.md section 3 prints is the layout the library reads: same field names,
+    offsets, sizes as the package's own ctypes mirror (which test_ctypes_structs_mirror_header ties to the header)."""
+    ns = {}
+    exec(_integration_block("wgs-abi-structs"), ns)
+    for doc_name, cls in (("WgsForwardArgs", _lib.ForwardArgs), ("WgsBackwardArgs", _lib.BackwardArgs),
+                          ("WgsWorkspaceSizes", _lib.WorkspaceSizes)):
+        doc_cls = ns[doc_name]
+        assert C.sizeof(doc_cls) == C.sizeof(cls), doc_name
+        assert [f[0] for f in doc_cls._fields_] == [f[0] for f in cls._fields_], doc_name
+        for name, _ in cls._fields_:
+            assert getattr(doc_cls, name).offset == getattr(cls, name).offset, (doc_name, name)
+            assert getattr(doc_cls, name).size == getattr(cls, name).size, (doc_name, name)
+    compile(_integration_block("wgs-abi-calls"), "INTEGRATION.md", "exec")      # at least syntactically valid here
+
+
+def test_stale_struct_layout_is_rejected():
+    """ABI v10: a binding built for an older, shorter WgsForwardArgs is refused instead of read past its end."""
+    lib = _lib.load()
+    a = _lib.ForwardArgs()
+    assert a.struct_size == C.sizeof(_lib.ForwardArgs)
+    a.struct_size -= 24                                   # the ABI-v8 layout INTEGRATION.md used to print
+    n = C.c_int64(0)
+    fake_ctx = C.c_void_p(1)                              # never dereferenced: the size check comes first
+    assert lib.wgs_forward(fake_ctx, C.byref(a), None, C.byref(n)) == _lib.WGS_ERR_INVALID_ARGUMENT
+    assert b"struct_size" in lib.wgs_last_error()
+    b = _lib.BackwardArgs()
+    b.struct_size = 8
+    assert lib.wgs_backward(fake_ctx, C.byref(b), None) == _lib.WGS_ERR_INVALID_ARGUMENT
+    assert b"struct_size" in lib.wgs_last_error()
+
+
+def test_scoped_contexts_are_per_thread_on_the_forward_side():
+    """tile_rows / grad_sink / densification_stats: what a forward sees is per thread (contextvars); a backward that
+    was not bound by its forward falls back to the innermost instance of the process."""
+    import threading
+    seen = {}
+
+    def worker(name, rows):
+        with rasterizer.tile_rows(*rows):
+            barrier.wait()
+            seen[name] = (rasterizer.tile_rows.current().begin, rasterizer.tile_rows.current().end)
+            barrier.wait()
+
+    barrier = threading.Barrier(2)
+    ts = [threading.Thread(target=worker, args=("a", (0, 3))), threading.Thread(target=worker, args=("b", (5, 9)))]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert seen == {"a": (0, 3), "b": (5, 9)}
+    assert rasterizer.tile_rows.current() is None
+    sink = rasterizer.grad_sink({})
+    assert rasterizer.grad_sink.current_for_backward(None) is None
+    with sink:
+        assert rasterizer.grad_sink.current() is sink
+        assert rasterizer.grad_sink.current_for_backward(None) is sink      # backward-only wrapping
+        other = rasterizer.grad_sink({})
+        assert rasterizer.grad_sink.current_for_backward(other) is other    # the forward's binding wins
+    assert rasterizer.grad_sink.current_for_backward(None) is None

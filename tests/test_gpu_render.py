@@ -241,3 +241,45 @@ def test_async_forward_reports_overflow():
         assert out[-1].num_rendered == -1
     assert graph.check_overflow(DEV) == ref[-1].num_rendered
     assert torch.equal(out[0], ref[0])
+
+
+def test_sticky_overflow_record_covers_every_no_wait_forward():
+    """No-wait mode: a forward that needs more instances than its capacity renders the background only (zero gradients),
+    and the STICKY record reports it even when later forwards on the device were fine; the check raises the capacity
+    floor so that the rerun fits."""
+    from wildgs_slam_blackwell_b200 import graph, rasterizer
+    W, H, P = 200, 120, 3000
+    cam_d = scenes.make_camera(W, H, 21, bg=(0.2, 0.4, 0.6))
+    g = scenes.make_gaussians(P, W, H, 0, 21, cam_d)
+    big = dict(g, scales=g["scales"] * 12.0)                 # R >> max(4 P, 65536): the default capacity
+    s = util.settings_from_cam(cam_d, 0, DEV)
+    mk = lambda gg: [util.to_dev(gg[k], DEV) for k in ("means3D", "sh")] + [torch.Tensor([])] + \
+        [util.to_dev(gg[k], DEV) for k in ("opacities", "scales", "rotations")] + [torch.Tensor([]), s]
+    rasterizer._capacity_hint.clear()
+    rasterizer._capacity_floor.clear()
+    graph.overflow_status(DEV, clear=True)
+    ref = rasterizer.forward_raw(*mk(big))                   # blocking forward: grows and retries
+    R_big = ref[-1].num_rendered
+    assert R_big > max(4 * P, 1 << 16)
+    rasterizer._capacity_hint.clear()
+    with graph.async_forward(DEV):
+        with graph.async_forward(DEV):                        # nests: the inner exit must not switch the mode off
+            pass
+        out_big = rasterizer.forward_raw(*mk(big))            # overflows silently ...
+        assert out_big[-1].num_rendered == -1
+        out_small = rasterizer.forward_raw(*mk(g))            # ... and is followed by a forward that is fine
+    torch.cuda.synchronize()
+    for c in range(3):
+        assert torch.all(out_big[0][c] == float(cam_d["bg"][c]))
+    assert not out_big[2].any() and not out_big[3].any()
+    n, cap = graph.last_num_rendered(DEV)
+    assert n <= cap                                           # the most recent forward alone looks healthy
+    with pytest.raises(RuntimeError, match="instance capacity exceeded by 1 forward") as ei:
+        graph.check_overflow(DEV)
+    assert ei.value.needed == R_big
+    assert graph.overflow_status(DEV) == (0, 0)               # cleared by the check
+    with graph.async_forward(DEV):
+        again = rasterizer.forward_raw(*mk(big))              # the floor was raised: fits now
+    assert graph.check_overflow(DEV) == R_big
+    assert torch.equal(again[0], ref[0])
+    rasterizer._capacity_floor.clear()

@@ -49,7 +49,7 @@ def _make_strip_render(params, rows):
     poses = [torch.zeros(6, requires_grad=True) for _ in range(N_VIEWS)]
 
     def render_loss(v):
-        act = rasterizer.tile_rows._active
+        act = rasterizer.tile_rows.current()
         b, e = (0, rows) if act is None else (act.begin, act.end)
         poses[v].grad = None
         loss = 0.0
@@ -211,8 +211,7 @@ def _stats_worker(rank, world, port, q):
         base = _make_render(params)
 
         def render_loss(v):     # stand-in for the backward kernel: it fills whatever densification_stats holds
-            acc, den, mx = rasterizer.densification_stats._active.bufs if rasterizer.densification_stats._active else (None,) * 3
-            assert acc is None                                  # only active around backward(), not around the forward
+            acc, den, mx = rasterizer.densification_stats.current_for_backward(None).bufs if rasterizer.densification_stats.current_for_backward(None) else (None,) * 3
             loss, pg = base(v)
 
             class Fill(torch.autograd.Function):
@@ -222,7 +221,7 @@ def _stats_worker(rank, world, port, q):
 
                 @staticmethod
                 def backward(ctx, g):
-                    a, d, m = rasterizer.densification_stats._active.bufs
+                    a, d, m = rasterizer.densification_stats.current_for_backward(None).bufs
                     a += float(v + 1); d += 1.0; m.copy_(torch.maximum(m, torch.full_like(m, float(10 * v + rank))))
                     return g
             return Fill.apply(loss), pg

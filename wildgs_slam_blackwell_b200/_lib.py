@@ -5,7 +5,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libwgs_rasterizer.so")
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 WGS_OK = 0
 WGS_ERR_INVALID_ARGUMENT = -1
@@ -21,9 +21,17 @@ class WorkspaceSizes(C.Structure):
     _fields_ = [(n, C.c_size_t) for n in ("geom_bytes", "tile_bytes", "binning_bytes", "image_bytes", "grad_bytes")]
 
 
-class ForwardArgs(C.Structure):
+class _SizedStructure(C.Structure):
+    """Fills the leading `struct_size` member (ABI v10: the library rejects a struct of another size)."""
+
+    def __init__(self, *args, **kw):
+        super().__init__(*args, **kw)
+        self.struct_size = C.sizeof(self)
+
+
+class ForwardArgs(_SizedStructure):
     _fields_ = [
-        ("P", C.c_int32), ("sh_degree", C.c_int32), ("M", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
+        ("struct_size", C.c_uint32), ("P", C.c_int32), ("sh_degree", C.c_int32), ("M", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
         ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float),
         ("prefiltered", C.c_int32), ("debug", C.c_int32),
         ("background", _fp), ("means3D", _fp), ("sh", _fp), ("colors_precomp", _fp), ("opacities", _fp),
@@ -36,9 +44,9 @@ class ForwardArgs(C.Structure):
     ]
 
 
-class BackwardArgs(C.Structure):
+class BackwardArgs(_SizedStructure):
     _fields_ = [
-        ("P", C.c_int32), ("sh_degree", C.c_int32), ("M", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
+        ("struct_size", C.c_uint32), ("P", C.c_int32), ("sh_degree", C.c_int32), ("M", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
         ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float), ("debug", C.c_int32),
         ("accumulate", C.c_int32),
         ("background", _fp), ("means3D", _fp), ("sh", _fp), ("colors_precomp", _fp), ("scales", _fp),
@@ -57,7 +65,8 @@ class BackwardArgs(C.Structure):
 EXPORTS = ("wgs_abi_version", "wgs_last_error", "wgs_context_create", "wgs_context_destroy",
            "wgs_workspace_sizes", "wgs_forward", "wgs_backward", "wgs_mark_visible", "wgs_export_binning",
            "wgs_export_geometry", "wgs_stage_timing", "wgs_stage_times", "wgs_camera_matrices", "wgs_set_async",
-           "wgs_last_num_rendered", "wgs_peer_flags_bytes", "wgs_peer_allreduce")
+           "wgs_last_num_rendered", "wgs_overflow_status", "wgs_count_pairs", "wgs_peer_flags_bytes",
+           "wgs_peer_allreduce")
 NUM_STAGES = 8
 STAGE_NAMES = ("preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd", "render_bwd", "preprocess_bwd",
                "reserved")
@@ -93,6 +102,8 @@ def load():
                                        C.c_uint64, C.c_void_p]
     lib.wgs_set_async.argtypes = [C.c_void_p, C.c_int]
     lib.wgs_last_num_rendered.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    lib.wgs_overflow_status.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_int]
+    lib.wgs_count_pairs.argtypes = [C.POINTER(ForwardArgs), _fp, C.c_void_p]
     lib.wgs_stage_timing.argtypes = [C.c_void_p, C.c_int]
     lib.wgs_stage_times.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     if lib.wgs_abi_version() != ABI_VERSION:

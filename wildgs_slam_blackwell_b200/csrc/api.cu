@@ -18,6 +18,7 @@ struct WgsContext {
     unsigned int* host_R = nullptr;  // pinned + mapped
     unsigned int* dev_R = nullptr;   // device alias of host_R
     cudaEvent_t ev_R = nullptr;
+    unsigned int* sticky = nullptr;  // device: {forwards that overflowed their capacity, largest R among them}
     // stage timing (wgs_stage_timing): fwd boundaries 0..5, bwd boundaries 6..8
     bool async = false;              // wgs_set_async: wgs_forward never waits for R
     long long last_capacity = 0;     // capacity of the most recent forward (for wgs_last_num_rendered)
@@ -88,6 +89,8 @@ WgsContext* wgs_context_create(int device) {
     cudaError_t e = cudaHostAlloc((void**)&c->host_R, 64, cudaHostAllocMapped);
     if (e == cudaSuccess) e = cudaHostGetDevicePointer((void**)&c->dev_R, c->host_R, 0);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_R, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&c->sticky, 2 * sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMemset(c->sticky, 0, 2 * sizeof(unsigned int));
     if (e == cudaSuccess) e = (cudaError_t)configure_binning();
     if (e == cudaSuccess) e = (cudaError_t)configure_render_bwd();
     if (e == cudaSuccess) e = (cudaError_t)configure_preprocess_bwd();
@@ -106,6 +109,7 @@ void wgs_context_destroy(WgsContext* c) {
     for (cudaEvent_t e : c->ev_stage)
         if (e) cudaEventDestroy(e);
     if (c->host_R) cudaFreeHost(c->host_R);
+    if (c->sticky) cudaFree(c->sticky);
     delete c;
 }
 
@@ -127,6 +131,12 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     if (!ctx || !a || !num_rendered) { set_err("wgs_forward: null argument", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
     cudaStream_t s = (cudaStream_t)cuda_stream;
     *num_rendered = 0;
+    if (a->struct_size != sizeof(WgsForwardArgs)) {
+        snprintf(g_err, sizeof(g_err), "wgs_forward: args->struct_size is %u, this library's WgsForwardArgs has %zu bytes "
+                 "(ABI %d): rebuild the binding against include/wgs_rasterizer.h", a->struct_size, sizeof(WgsForwardArgs),
+                 WGS_ABI_VERSION);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
     // Inside a CUDA-graph capture (or in async mode) the host must not wait on the device: R is not read
     // back here, *num_rendered = -1, and the caller checks wgs_last_num_rendered() after a synchronisation.
     cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
@@ -194,6 +204,7 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     BinParams bp;
     bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.copies = hist_copies((size_t)tiles); bp.capacity = a->capacity;
     bp.geom = geom; bp.tile = tile; bp.bucket = (unsigned long long*)a->binning; bp.host_R = ctx->dev_R;
+    bp.sticky = ctx->sticky;
     launch_tile_scan(bp, s);
     const bool no_wait = capturing || ctx->async;
     if (!no_wait) CK(cudaEventRecord(ctx->ev_R, s));
@@ -235,6 +246,12 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
 
 int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     if (!ctx || !a) { set_err("wgs_backward: null argument", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    if (a->struct_size != sizeof(WgsBackwardArgs)) {
+        snprintf(g_err, sizeof(g_err), "wgs_backward: args->struct_size is %u, this library's WgsBackwardArgs has %zu bytes "
+                 "(ABI %d): rebuild the binding against include/wgs_rasterizer.h", a->struct_size, sizeof(WgsBackwardArgs),
+                 WGS_ABI_VERSION);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
     cudaStream_t s = (cudaStream_t)cuda_stream;
     cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(s, &cap_status) != cudaSuccess) cap_status = cudaStreamCaptureStatusNone;
@@ -323,6 +340,42 @@ int wgs_last_num_rendered(WgsContext* ctx, int64_t* num_rendered, int64_t* capac
     return *num_rendered > ctx->last_capacity ? WGS_ERR_CAPACITY : WGS_OK;
 }
 
+int wgs_overflow_status(WgsContext* ctx, int64_t* overflowed_forwards, int64_t* max_num_rendered, int clear) {
+    if (!ctx) { set_err("wgs_overflow_status: null context", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
+    unsigned int h[2] = {0u, 0u};
+    CK(cudaMemcpy(h, ctx->sticky, sizeof(h), cudaMemcpyDeviceToHost));  // the caller has synchronised its streams
+    if (clear && h[0]) CK(cudaMemset(ctx->sticky, 0, sizeof(h)));
+    if (overflowed_forwards) *overflowed_forwards = (int64_t)h[0];
+    if (max_num_rendered) *max_num_rendered = (int64_t)h[1];
+    if (h[0]) {
+        snprintf(g_err, sizeof(g_err), "%u forward(s) exceeded their instance capacity (largest needed %u)", h[0], h[1]);
+        return WGS_ERR_CAPACITY;
+    }
+    return WGS_OK;
+}
+
+int wgs_count_pairs(const WgsForwardArgs* a, uint64_t* counts, void* cuda_stream) {
+    if (!a || !counts || a->struct_size != sizeof(WgsForwardArgs) || !a->tile || !a->image || (a->P > 0 && (!a->geom || !a->binning))) {
+        set_err("wgs_count_pairs: invalid argument", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    const int gx = (a->width + 15) / 16, gy = (a->height + 15) / 16;
+    int row0, row1;
+    if (!strip_rows(a->tile_row_begin, a->tile_row_end, gy, &row0, &row1)) {
+        set_err("wgs_count_pairs: tile_row_begin/end out of range", cudaSuccess);
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    RenderFwdParams rp = {};
+    rp.W = a->width; rp.H = a->height; rp.gx = gx; rp.gy = gy; rp.tile0 = row0 * gx; rp.ntiles = (row1 - row0) * gx;
+    rp.geom = geom_view(a->geom, (size_t)(a->P > 0 ? a->P : 1));
+    rp.tile = tile_view(a->tile, (size_t)gx * gy);
+    rp.image = image_view(a->image, (size_t)a->width * a->height);
+    rp.bucket = (const unsigned long long*)a->binning;
+    launch_count_pairs(rp, (unsigned long long*)counts, (cudaStream_t)cuda_stream);
+    STAGE(0, (cudaStream_t)cuda_stream, "count_pairs");
+    return WGS_OK;
+}
+
 int wgs_stage_timing(WgsContext* ctx, int enable) {
     if (!ctx) { set_err("wgs_stage_timing: null context", cudaSuccess); return WGS_ERR_INVALID_ARGUMENT; }
     if (enable) {
@@ -365,7 +418,7 @@ int wgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, c
 int wgs_export_binning(const WgsForwardArgs* a, int64_t num_rendered, uint64_t* point_list_keys,
                        uint32_t* point_list, uint32_t* ranges, uint32_t* n_contrib, float* final_T,
                        void* cuda_stream) {
-    if (!a || !a->tile || !a->image || num_rendered > a->capacity) {
+    if (!a || a->struct_size != sizeof(WgsForwardArgs) || !a->tile || !a->image || num_rendered > a->capacity) {
         set_err("wgs_export_binning: invalid argument", cudaSuccess);
         return WGS_ERR_INVALID_ARGUMENT;
     }
@@ -374,7 +427,7 @@ int wgs_export_binning(const WgsForwardArgs* a, int64_t num_rendered, uint64_t* 
     bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.copies = hist_copies((size_t)tiles); bp.capacity = a->capacity;
     bp.geom = geom_view(a->geom, (size_t)(a->P > 0 ? a->P : 1));
     bp.tile = tile_view(a->tile, (size_t)tiles);
-    bp.bucket = (unsigned long long*)a->binning; bp.host_R = nullptr;
+    bp.bucket = (unsigned long long*)a->binning; bp.host_R = nullptr; bp.sticky = nullptr;
     launch_export_binning(bp, image_view(a->image, (size_t)a->width * a->height), a->width, a->height,
                           (unsigned long long*)point_list_keys, point_list, ranges, n_contrib, final_T,
                           (cudaStream_t)cuda_stream);
@@ -384,7 +437,7 @@ int wgs_export_binning(const WgsForwardArgs* a, int64_t num_rendered, uint64_t* 
 
 int wgs_export_geometry(const WgsForwardArgs* a, float* depths, float* means2D, float* conic_opacity, float* rgb,
                         uint8_t* clamped, void* cuda_stream) {
-    if (!a || (a->P > 0 && (!a->geom || !a->radii))) {
+    if (!a || a->struct_size != sizeof(WgsForwardArgs) || (a->P > 0 && (!a->geom || !a->radii))) {
         set_err("wgs_export_geometry: invalid argument", cudaSuccess);
         return WGS_ERR_INVALID_ARGUMENT;
     }

@@ -25,6 +25,20 @@ constexpr int LARGE_MAX = 24576;   // 192 KB of keys, 1024-thread CTA, 1 CTA/SM
 constexpr int SMALL_THREADS = 512;
 constexpr int LARGE_THREADS = 1024;
 
+// R = num_rendered of this forward: to the tile workspace, to the mapped host word the blocking forward waits on,
+// and -- when it exceeds the instance capacity -- to the context's STICKY overflow record, which only
+// wgs_overflow_status() clears (a no-wait / graph-replayed forward has nobody looking at its own R).
+__device__ __forceinline__ void publish_total(const BinParams& p, uint32_t total) {
+    const bool over = (long long)total > p.capacity;
+    p.tile.misc[MISC_NUM_RENDERED] = total;
+    p.tile.misc[MISC_OVERFLOW] = over;
+    if (p.host_R) *(volatile unsigned int*)p.host_R = total;
+    if (over && p.sticky) {
+        atomicAdd(p.sticky, 1u);
+        atomicMax(p.sticky + 1, total);
+    }
+}
+
 // K = number of privatised histogram copies (compile-time so that all K loads are in flight at once)
 template <int K>
 __global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__ BinParams p) {
@@ -71,11 +85,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__
         carry += warp_sums[31];
         __syncthreads();
     }
-    if (tid == 0) {
-        p.tile.misc[MISC_NUM_RENDERED] = carry;
-        p.tile.misc[MISC_OVERFLOW] = (long long)carry > p.capacity;
-        if (p.host_R) *(volatile unsigned int*)p.host_R = carry;
-    }
+    if (tid == 0) publish_total(p, carry);
 }
 
 // Same scan on one 8-CTA thread-block cluster (tiles <= 8 * 1024): every CTA sums the K copies of
@@ -179,11 +189,7 @@ __global__ void __cluster_dims__(SCAN_CLUSTER, 1, 1) __launch_bounds__(1024)
             if (w < cw) off += cls_wsum[w];
         p.tile.order[off] = (uint32_t)t;
     }
-    if (crank == 0 && tid == 0) {
-        p.tile.misc[MISC_NUM_RENDERED] = total;
-        p.tile.misc[MISC_OVERFLOW] = (long long)total > p.capacity;
-        if (p.host_R) *(volatile unsigned int*)p.host_R = total;
-    }
+    if (crank == 0 && tid == 0) publish_total(p, total);
     cluster.sync();  // no CTA may exit while its shared memory can still be read remotely
 }
 

@@ -26,6 +26,7 @@ struct BinParams {
     TileView tile;
     unsigned long long* bucket;
     unsigned int* host_R;  // mapped pinned word (may be null)
+    unsigned int* sticky;  // context-level overflow record {forwards that overflowed, largest R among them} (may be null)
 };
 
 struct RenderFwdParams {
@@ -79,6 +80,7 @@ void launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s);
 void launch_export_binning(const BinParams& p, const ImageView& image, int W, int H, unsigned long long* keys,
                            unsigned int* list, unsigned int* ranges, unsigned int* n_contrib, float* final_T,
                            cudaStream_t s);
+void launch_count_pairs(const RenderFwdParams& p, unsigned long long* counts, cudaStream_t s);
 void launch_export_geometry(int P, const GeomView& g, const int* radii, float* depths, float* means2D,
                             float* conic_opacity, float* rgb, uint8_t* clamped, cudaStream_t s);
 int configure_binning();  // one-time cudaFuncSetAttribute calls; returns cudaError_t

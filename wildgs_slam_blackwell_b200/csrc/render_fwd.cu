@@ -57,7 +57,12 @@ __device__ __forceinline__ void walk_survivors(const FwdStage& s, unsigned m, in
 
 __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__ RenderFwdParams p) {
     __shared__ FwdStage st[2];
-    if (p.tile.misc[MISC_OVERFLOW]) return;
+    // R exceeded the instance capacity (only reachable in no-wait / graph mode, where no host is there to grow the
+    // buffer and retry): every tile composites an EMPTY list, i.e. background colour, zero depth / opacity and
+    // n_contrib = 0, so a missed overflow check never hands uninitialised memory to a loss or an optimiser (the
+    // backward of such a forward finds no contributor and produces zero gradients); tile_scan recorded the event
+    // in the context's sticky overflow word.
+    const bool overflow = p.tile.misc[MISC_OVERFLOW] != 0;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // longest tiles first (tile_scan's order); a tile-row strip skips the tiles outside it
     const int tile = (int)p.tile.order[blockIdx.x];
@@ -73,7 +78,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
     const bool warp_in_image = wx0 < p.W && wy0 < p.H;
 
     const uint2 range = p.tile.ranges[tile];
-    const int total = (int)(range.y - range.x);
+    const int total = overflow ? 0 : (int)(range.y - range.x);
     const int rounds = (total + BATCH - 1) / BATCH;
     const unsigned long long* __restrict__ list = p.bucket + range.x;
 
@@ -146,6 +151,50 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
         p.out_depth[pix] = D;
         p.out_opacity[pix] = SUB(1.f, T);
     }
+}
+
+// Debug counting pass (wgs_count_pairs): one thread per pixel re-walks its tile list up to n_contrib with the
+// forward's arithmetic and counts the pairs that pass both alpha tests (= the pairs the forward composited: the
+// transmittance cut only ever fires behind the last contributor).  counts[0] += n_contrib, counts[1] += blended.
+__global__ void __launch_bounds__(256) count_pairs_kernel(const __grid_constant__ RenderFwdParams p,
+                                                          unsigned long long* __restrict__ counts) {
+    if (p.tile.misc[MISC_OVERFLOW]) return;
+    const int tile = blockIdx.x;
+    if (tile < p.tile0 || tile >= p.tile0 + p.ntiles) return;
+    const int tx = tile % p.gx, ty = tile / p.gx;
+    const int pxi = tx * WGS_TILE + (threadIdx.x & 15), pyi = ty * WGS_TILE + (threadIdx.x >> 4);
+    unsigned long long n_eval = 0, n_blend = 0;
+    if (pxi < p.W && pyi < p.H) {
+        const uint2 range = p.tile.ranges[tile];
+        const unsigned long long* __restrict__ list = p.bucket + range.x;
+        const int last = (int)p.image.n_contrib[(size_t)pyi * p.W + pxi];
+        const float pixx = (float)pxi, pixy = (float)pyi;
+        n_eval = (unsigned long long)last;
+        for (int k = 0; k < last; k++) {
+            const uint32_t id = (uint32_t)list[k];
+            const float4 a = p.geom.rec[2 * (size_t)id], b = p.geom.rec[2 * (size_t)id + 1];
+            const float dx = SUB(a.x, pixx), dy = SUB(a.y, pixy);
+            const float power = FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
+            if (power > 0.f) continue;
+            const float alpha = fminf(MUL(b.y, expf(power)), 0.99f);
+            if (alpha < 1.0f / 255.0f) continue;
+            n_blend++;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        n_eval += __shfl_xor_sync(0xffffffffu, n_eval, o);
+        n_blend += __shfl_xor_sync(0xffffffffu, n_blend, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(counts, n_eval);
+        atomicAdd(counts + 1, n_blend);
+    }
+}
+
+void launch_count_pairs(const RenderFwdParams& p, unsigned long long* counts, cudaStream_t s) {
+    cudaMemsetAsync(counts, 0, 2 * sizeof(unsigned long long), s);
+    count_pairs_kernel<<<p.gx * p.gy, 256, 0, s>>>(p, counts);
 }
 
 void launch_render_fwd(const RenderFwdParams& p, cudaStream_t s) {

@@ -5,7 +5,10 @@ calling libwgs_rasterizer.so through ctypes instead of the pybind `_C` module.
 
 PyTorch is used for device memory, streams and autograd plumbing only.
 """
+import collections
+import contextvars
 import ctypes as C
+import threading
 from typing import NamedTuple
 
 import torch
@@ -34,9 +37,17 @@ def cpu_deep_copy_tuple(input_tuple):
     return tuple(item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple)
 
 
-# ---- per-device host state: instance-capacity hint and the self-cleaning gradient workspace ----
+# ---- host state: instance-capacity hint per (device, W, H, P) and the self-cleaning gradient workspaces ----
 _capacity_hint = {}
-_grad_ws = {}
+_capacity_floor = {}        # device -> instance count a no-wait forward was seen to need (graph.check_overflow)
+# (device, stream, P) -> accumulator workspace.  One per STREAM: two backwards in flight on two streams of a device
+# never share accumulators / the pose ticket; one per P: a masked render or a densified model next to the full one
+# does not evict (and free) a workspace a captured CUDA graph still points at.  Least-recently-used entries beyond
+# _GRAD_WS_KEEP per device are dropped unless a live CapturedIteration pinned them.
+_grad_ws = collections.OrderedDict()
+_GRAD_WS_KEEP = 8
+_grad_ws_lock = threading.Lock()
+_capture_pins = []          # workspaces handed out while a stream capture was active (graph.CapturedIteration takes them)
 
 
 def _ptr(t):
@@ -75,7 +86,7 @@ def _check(rc, what):
 
 class ForwardState:
     """What one forward leaves behind for its backward / for the parity exports."""
-    __slots__ = ("args", "geom", "tile", "binning", "image", "num_rendered", "keep")
+    __slots__ = ("args", "geom", "tile", "binning", "image", "num_rendered", "keep", "sink", "stats")
 
 
 def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, s, sh_rest=None,
@@ -111,7 +122,7 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
                 raise RuntimeError("with sh_rest, sh must be the (P,1,3) DC coefficients")
             M = 1 + int(sh_rest.shape[1])
 
-        strip = tile_rows._active
+        strip = tile_rows.current()
         new_img = torch.zeros if strip is not None else torch.empty   # outside a strip nothing is written
         color = new_img((3, H, W), dtype=torch.float32, device=device)
         depth = new_img((1, H, W), dtype=torch.float32, device=device)
@@ -119,8 +130,8 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
         radii = torch.empty((P,), dtype=torch.int32, device=device)
         n_touched = torch.empty((P,), dtype=torch.int32, device=device)
 
-        key = (device.index, W, H)
-        cap = max(_capacity_hint.get(key, 0), 4 * P, 1 << 16)
+        key = (device.index, W, H, P)
+        cap = max(_capacity_hint.get(key, 0), _capacity_floor.get(device.index, 0), 4 * P, 1 << 16)
         st = ForwardState()
         a = _lib.ForwardArgs()
         a.P, a.sh_degree, a.M, a.width, a.height = P, int(s.sh_degree), M, W, H
@@ -159,6 +170,8 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
                 _capacity_hint[key] = int(R.value * 1.5)
         st.args = a
         st.num_rendered = int(R.value)
+        # what is active around the FORWARD is bound to its backward (the backward runs on autograd's worker thread)
+        st.sink, st.stats = grad_sink.current(), densification_stats.current()
         # Keep every INPUT the argument block points at alive as long as the state lives.  The
         # outputs are deliberately not held: under autograd they carry grad_fn -> ctx -> state, and
         # holding them here would close a reference cycle that only the cyclic GC frees (workspaces
@@ -169,16 +182,78 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
 
 
 def _grad_workspace(device, P):
-    key = device.index
-    ent = _grad_ws.get(key)
-    nbytes = _lib.workspace_sizes(P, 16, 16, 0).grad_bytes
-    if ent is None or ent[0] != P:
-        ent = (P, torch.zeros(int(nbytes), dtype=torch.uint8, device=device))  # zero once; kernels re-zero
-        _grad_ws[key] = ent
-    return ent[1]
+    """The accumulator workspace of (device, current stream, P): zeroed once, the kernels re-zero it."""
+    stream = torch.cuda.current_stream(device)
+    key = (device.index, int(stream.cuda_stream), int(P))
+    with _grad_ws_lock:
+        ws = _grad_ws.get(key)
+        if ws is None:
+            nbytes = _lib.workspace_sizes(P, 16, 16, 0).grad_bytes
+            ws = torch.zeros(int(nbytes), dtype=torch.uint8, device=device)
+            _grad_ws[key] = ws
+            mine = [k for k in _grad_ws if k[0] == device.index]
+            for k in mine[:max(0, len(mine) - _GRAD_WS_KEEP)]:
+                del _grad_ws[k]      # (a pinned tensor stays alive through its CapturedIteration)
+        else:
+            _grad_ws.move_to_end(key)
+        if torch.cuda.is_current_stream_capturing():
+            _capture_pins.append(ws)
+    return ws
 
 
-class tile_rows:
+def raise_capacity_floor(device_index, needed):
+    """Every later forward on the device starts with room for `needed` instances (no-wait forwards cannot retry)."""
+    _capacity_floor[device_index] = max(_capacity_floor.get(device_index, 0), int(needed))
+
+
+def _drop_grad_workspace(device, P):
+    stream = torch.cuda.current_stream(device)
+    with _grad_ws_lock:
+        _grad_ws.pop((device.index, int(stream.cuda_stream), int(P)), None)
+
+
+def take_capture_pins():
+    """Workspaces whose raw pointers went into kernels recorded during a stream capture since the last call; the
+    owner of the graph keeps them so that their lifetime is at least the graph's."""
+    with _grad_ws_lock:
+        pins = list(_capture_pins)
+        del _capture_pins[:]
+    return pins
+
+
+class _Scoped:
+    """Context manager whose innermost active instance is found through a contextvars.ContextVar (per thread / per
+    asyncio task) -- the forward binds what is active around IT to its autograd node -- and, for callers that wrap
+    only `loss.backward()`, through a per-device registry: autograd runs a CUDA node's backward on its own worker
+    thread, which never sees the caller's context variables, so the backward-only form cannot be thread-local; it
+    is safe with one backward at a time per device, the forward-bound form with any number of threads/streams."""
+    _var = None          # ContextVar, one per subclass
+    _stack = None        # process-wide stack of active instances, one list per subclass
+
+    def __enter__(self):
+        self._token = self._var.set(self)
+        self._stack.append(self)
+        return self
+
+    def __exit__(self, *exc):
+        self._var.reset(self._token)
+        self._stack.remove(self)
+        return False
+
+    @classmethod
+    def current(cls):
+        """innermost instance active in the calling context (forward side)"""
+        return cls._var.get()
+
+    @classmethod
+    def current_for_backward(cls, bound):
+        """`bound` (what the forward saw) wins; else the innermost instance entered anywhere in the process"""
+        if bound is not None:
+            return bound
+        return cls._stack[-1] if cls._stack else None
+
+
+class tile_rows(_Scoped):
     """Context manager (new capability: sub-frame sharding of a keyframe window): forwards issued
     while active render only tile rows [begin, end) (rows of 16 pixels).  Output images have the full
     (H, W) shape and are ZERO outside the strip, so images, n_touched and -- after backward --
@@ -187,70 +262,50 @@ class tile_rows:
 
         with tile_rows(0, 15):  color_top, *_ = rasterizer(...)
     """
-    _active = None
+    _var = contextvars.ContextVar("wgs_tile_rows", default=None)
+    _stack = []
 
     def __init__(self, begin, end):
         self.begin, self.end = int(begin), int(end)
 
-    def __enter__(self):
-        self._prev = tile_rows._active
-        tile_rows._active = self
-        return self
 
-    def __exit__(self, *exc):
-        tile_rows._active = self._prev
-        return False
-
-
-class grad_sink:
-    """Context manager (new capability, used by the multi-GPU mapping window): while active, the
-    backward writes the Gaussian-parameter gradients straight into the caller's buffers
+class grad_sink(_Scoped):
+    """Context manager (new capability, used by the multi-GPU mapping window): the backward writes the
+    Gaussian-parameter gradients straight into the caller's buffers
     (`buffers`: any of 'means3D', 'sh', 'colors', 'opacity', 'scales', 'rotations', 'cov3D' ->
     float32 CUDA tensor of the gradient's shape, e.g. slices of one flat allreduce bucket) and
     autograd receives None for them; with accumulate=True the kernel adds to the buffers instead
     of overwriting, so a window of views sums in place.  Pose gradients still flow through autograd.
 
         with grad_sink(bucket_views, accumulate=(k > 0)):
+            loss_k = render_and_loss(k)      # the forward binds the sink to its backward (thread-safe form)
             loss_k.backward()
+
+    Wrapping only `loss.backward()` works too (one backward at a time per process; see _Scoped).
     """
-    _active = None
+    _var = contextvars.ContextVar("wgs_grad_sink", default=None)
+    _stack = []
 
     def __init__(self, buffers, accumulate=False):
         self.buffers, self.accumulate = dict(buffers), bool(accumulate)
 
-    def __enter__(self):
-        self._prev = grad_sink._active
-        grad_sink._active = self
-        return self
 
-    def __exit__(self, *exc):
-        grad_sink._active = self._prev
-        return False
-
-
-class densification_stats:
-    """Context manager: while active, every backward also does what the mapper runs after it on the same view
+class densification_stats(_Scoped):
+    """Context manager: every backward of a forward issued while active (or every backward run while active) also does
+    what the mapper runs after it on the same view
     (src/mapper.py:1176-1182, GaussianModel.add_densification_stats): for the Gaussians with radii > 0,
     `xyz_gradient_accum += ||dL_dmeans2D[:, :2]||`, `denom += 1`, `max_radii2D = max(max_radii2D, radii)` -- inside
     the per-Gaussian backward kernel, so the window needs neither the (P,3) dL_dmeans2D tensor nor the ~12 indexing
     kernels per view.  Tensors: float32 CUDA, P elements each (any may be None).  Whole-image backward only."""
-    _active = None
+    _var = contextvars.ContextVar("wgs_densification_stats", default=None)
+    _stack = []
 
     def __init__(self, xyz_gradient_accum=None, denom=None, max_radii2D=None):
         self.bufs = (xyz_gradient_accum, denom, max_radii2D)
 
-    def __enter__(self):
-        self._prev = densification_stats._active
-        densification_stats._active = self
-        return self
-
-    def __exit__(self, *exc):
-        densification_stats._active = self._prev
-        return False
-
 
 def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii,
-                 grad_out_color, grad_out_depth, sink=None):
+                 grad_out_color, grad_out_depth, sink=None, stats=None):
     """Runs the backward through the C ABI.  Returns dict of gradient tensors (+ 'tau' (6,))."""
     device = means3D.device
     lib = _lib.load()
@@ -302,7 +357,7 @@ def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_p
         b.capacity = fa.capacity
         b.tile_row_begin, b.tile_row_end = fa.tile_row_begin, fa.tile_row_end
         b.activations, b.sh_rest, b.dL_dsh_rest = fa.activations, fa.sh_rest, _ptr(g["sh_rest"])
-        stats = densification_stats._active
+        stats = densification_stats.current_for_backward(stats)
         if stats is not None:
             for t in stats.bufs:
                 if t is not None and (t.numel() != P or t.dtype != torch.float32 or t.device != device or not t.is_contiguous()):
@@ -312,7 +367,7 @@ def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_p
             b.grad = _grad_workspace(device, P).data_ptr()
         rc = lib.wgs_backward(ctx, C.byref(b), _stream_ptr(device))
         if rc != _lib.WGS_OK:
-            _grad_ws.pop(device.index, None)  # accumulators may be dirty
+            _drop_grad_workspace(device, P)  # accumulators may be dirty
         _check(rc, "wgs_backward")
     return g
 
@@ -358,11 +413,11 @@ class _RasterizeGaussians(torch.autograd.Function):
             grad_out_color = torch.zeros((3, s.image_height, s.image_width), device=means3D.device)
         if grad_out_depth is None:
             grad_out_depth = torch.zeros((1, s.image_height, s.image_width), device=means3D.device)
-        sink = grad_sink._active
+        sink = grad_sink.current_for_backward(ctx.state.sink)
         args = (ctx.state, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii, grad_out_color,
-                grad_out_depth, sink)
+                grad_out_depth, sink, ctx.state.stats)
         if s.debug:
-            cpu_args = cpu_deep_copy_tuple(args[2:-1] + tuple(s))
+            cpu_args = cpu_deep_copy_tuple(args[2:-2] + tuple(s))
             try:
                 g = backward_raw(*args)
             except Exception as ex:
@@ -412,10 +467,10 @@ class _RasterizeGaussianModel(torch.autograd.Function):
             grad_out_color = torch.zeros((3, s.image_height, s.image_width), device=xyz.device)
         if grad_out_depth is None:
             grad_out_depth = torch.zeros((1, s.image_height, s.image_width), device=xyz.device)
-        sink = grad_sink._active
+        sink = grad_sink.current_for_backward(ctx.state.sink)
         empty = torch.Tensor([])
         g = backward_raw(ctx.state, s, xyz, f_dc, empty, scaling_raw, rotation_raw, empty, radii, grad_out_color,
-                         grad_out_depth, sink)
+                         grad_out_depth, sink, ctx.state.stats)
         th_shape, rho_shape = ctx.pose_shapes
         grad_rho = g["tau"][:3].view(rho_shape if len(rho_shape) and rho_shape.numel() == 3 else (1, 3))
         grad_theta = g["tau"][3:].view(th_shape if len(th_shape) and th_shape.numel() == 3 else (1, 3))

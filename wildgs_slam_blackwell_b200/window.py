@@ -238,13 +238,11 @@ class WindowTrainer:
         if self._stats:
             b.stats.zero_()
         for n_done, v in enumerate(mine):
-            loss, pose_grad_fn = render_loss(v)
-            with self._stats_ctx():
-                if use_sink:
-                    with rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0):
-                        loss.backward()
-                else:
-                    loss.backward()
+            # the contexts surround the FORWARD as well: the rasterizer binds them to that forward's backward, which
+            # keeps two trainers on two threads / streams of one process apart (rasterizer._Scoped)
+            with self._stats_ctx(), (rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0) if use_sink else _null()):
+                loss, pose_grad_fn = render_loss(v)
+                loss.backward()
             side[v, 0] = loss.detach()
             side[v, 1].fill_(float(cost_fn(v)) if cost_fn is not None else 1.0)  # fill_: no H2D copy (graph capture)
             if pose_grad_fn is not None:
@@ -270,13 +268,10 @@ class WindowTrainer:
         side, fused = self._side(n_views)
         for n_done, (v, r0, r1) in enumerate(mine):
             whole = r0 == 0 and r1 == tile_rows
-            with rasterizer.tile_rows(r0, r1) if not whole else _null():
+            with (rasterizer.tile_rows(r0, r1) if not whole else _null()), \
+                    (rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0) if use_sink else _null()):
                 loss, pose_grad_fn = render_loss(v)
-                if use_sink:
-                    with rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0):
-                        loss.backward()
-                else:
-                    loss.backward()
+                loss.backward()
             side[v, 0] += loss.detach()
             side[v, 1].add_(float(cost_fn(v)) if cost_fn is not None else (r1 - r0) / tile_rows)
             if pose_grad_fn is not None:
