@@ -118,7 +118,9 @@ typedef struct WgsBackwardArgs {
   float tanfovx, tanfovy, scale_modifier;
   int32_t debug;
   int32_t accumulate; /* 0: gradient outputs are overwritten; 1: added to (lets a keyframe window sum the
-                         per-view Gaussian gradients in place; dL_dtau is always overwritten) */
+                         per-view Gaussian gradients in place; dL_dtau is always overwritten); 2: added to with
+                         reduction atomics, so that backwards running concurrently on several streams may share
+                         the output buffers (the caller zeroes them first) */
   const float* background;
   const float* means3D;
   const float* sh;

@@ -476,3 +476,37 @@ def test_fused_densification_statistics_match_the_mapper_procedure():
     with pytest.raises(RuntimeError, match="whole-image"):
         with rasterizer.tile_rows(0, 2), rasterizer.densification_stats(tr.grad_accum, tr.denom, tr.max_radii):
             render_loss(0)[0].backward()
+
+
+@pytest.mark.parametrize("streams", [1, 2])
+def test_window_shares_of_emulated_ranks_sum_to_the_window_gradient(streams):
+    """The work units WindowTrainer hands to each of 4 ranks (whole views + tile-row strips of the remainder, on one or
+    two streams with atomic accumulation, block-compacted preprocess_bwd), run one rank after the other on this GPU, sum
+    to the gradient of the whole 5-view window -- eagerly and with a rank's step captured in one CUDA graph."""
+    sys.path.insert(0, os.path.join(util.ROOT, "scripts"))
+    from window_workload import LEAVES, WindowWorkload
+    scenes.CONFIGS["_w5"] = (40_000, 320, 240, 0, 5)
+    scene = scenes.make_scene(40_000, 320, 240, 0, seed=91, n_views=5)
+    ref_wl = WindowWorkload("_w5", torch.device(DEV), peer="off", streams=1, use_graph=False, scene=scene)
+    ref = {k: torch.zeros_like(p) for k, p in ref_wl.params.items()}
+    for v in range(5):
+        loss, _ = ref_wl.render_loss(v)
+        for k, gk in zip(LEAVES, torch.autograd.grad(loss, [ref_wl.params[k] for k in LEAVES])):
+            ref[k] += gk
+    for plan, use_graph in (("views", False), ("strips", False), ("balanced", False), ("balanced", True)):
+        total = {k: torch.zeros_like(p) for k, p in ref.items()}
+        units = 0
+        for r in range(4):
+            wl = WindowWorkload("_w5", torch.device(DEV), peer="off", plan=plan, streams=streams, use_graph=use_graph,
+                                scene=scene, emulate=(r, 4))
+            out = wl.step()
+            if use_graph:
+                out = wl.step()
+                wl.check()
+            torch.cuda.synchronize()
+            units += len(out["assignment"][r])
+            for k in total:
+                total[k] += wl.params[k].grad
+        assert units == (5 if plan == "views" else 8 if plan == "strips" else 8), (plan, units)
+        for k in ref:
+            util.assert_grad_close(f"{plan}/{k}", total[k].cpu().numpy(), ref[k].cpu().numpy())

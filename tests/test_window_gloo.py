@@ -251,3 +251,43 @@ def test_window_densification_statistics_world2(tmp_path):
         want = max(10 * max(views) + rk for rk, views in enumerate(assign_views([1.0] * N_VIEWS, 2)))
         assert bool((mx == want).all())                         # identical on both ranks: MAX across ranks
         assert nbytes == 4 * P * 7                              # nbytes counts the gradients only
+
+
+def test_assign_balanced_properties():
+    from wildgs_slam_blackwell_b200.window import assign_balanced
+    for costs, world, rows in [([1] * 10, 8, 30), ([1] * 10, 4, 30), ([1.1, 0.9, 1.0, 1.05, 0.95, 1.0, 1.0, 1.02, 0.98, 1.0], 8, 30),
+                               ([3, 1, 2, 5, 1, 1, 2, 2, 4, 1], 8, 30), ([1] * 3, 2, 4), ([1, 1], 4, 30), ([1] * 16, 8, 30)]:
+        plan = assign_balanced(costs, world, rows)
+        seen = set()
+        for units in plan:
+            for v, b, e in units:
+                assert 0 <= b < e <= rows
+                for row in range(b, e):
+                    assert (v, row) not in seen
+                    seen.add((v, row))
+        assert len(seen) == len(costs) * rows                       # every (view, row) exactly once
+        loads = [sum(costs[v] * (e - b) / rows for v, b, e in units) for units in plan]
+        assert max(loads) <= 1.08 * sum(costs) / world + max(costs) / rows + 1e-9
+    plan = assign_balanced([1] * 10, 8, 30)                        # config 3: one whole view + a quarter of another per rank
+    assert all(len(u) == 2 and u[0][1:] == (0, 30) and 7 <= u[1][2] - u[1][1] <= 8 for u in plan)
+    assert sorted(u[1][0] for u in plan) == [8] * 4 + [9] * 4
+    assert all(u == [(i, 0, 30), (8 + i, 0, 30)] for i, u in enumerate(assign_balanced([1] * 16, 8, 30)))   # divides: whole views
+
+
+def test_emulated_rank_runs_that_ranks_units_without_exchange():
+    """WindowTrainer(emulate=(r, N)): rank r's share of an N-rank step in one process; the shares of all ranks sum to the
+    single-process gradients, for every plan."""
+    ref_params = _params()
+    ref = WindowTrainer(ref_params)
+    ref.step(N_VIEWS, _make_strip_render(ref_params, 4), tile_rows=4)
+    for plan in ("views", "strips", "balanced"):
+        total = None
+        for r in range(2):
+            params = _params()
+            tr = WindowTrainer(params, emulate=(r, 2))
+            out = tr.step(N_VIEWS, _make_strip_render(params, 4), tile_rows=4, plan=plan)
+            g = {k: p.grad.clone() for k, p in params.items()}
+            total = g if total is None else {k: total[k] + g[k] for k in g}
+            assert len(out["assignment"]) == 2
+        for k in total:
+            torch.testing.assert_close(total[k], ref_params[k].grad, rtol=1e-5, atol=1e-6)

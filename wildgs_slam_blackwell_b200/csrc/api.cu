@@ -204,9 +204,9 @@ int wgs_forward(WgsContext* ctx, const WgsForwardArgs* a, void* cuda_stream, int
     BinParams bp;
     bp.P = a->P; bp.gx = gx; bp.gy = gy; bp.tiles = tiles; bp.copies = hist_copies((size_t)tiles); bp.capacity = a->capacity;
     bp.geom = geom; bp.tile = tile; bp.bucket = (unsigned long long*)a->binning; bp.host_R = ctx->dev_R;
-    bp.sticky = ctx->sticky;
-    launch_tile_scan(bp, s);
     const bool no_wait = capturing || ctx->async;
+    bp.sticky = no_wait ? ctx->sticky : nullptr;  // a blocking forward reports its overflow itself (and is retried)
+    launch_tile_scan(bp, s);
     if (!no_wait) CK(cudaEventRecord(ctx->ev_R, s));
     ctx->last_capacity = a->capacity;
     STAGE(a->debug, s, "tile_scan");
@@ -256,8 +256,8 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(s, &cap_status) != cudaSuccess) cap_status = cudaStreamCaptureStatusNone;
     const bool capturing = cap_status == cudaStreamCaptureStatusActive;
-    if (a->P < 0 || a->width <= 0 || a->height <= 0) {
-        set_err("wgs_backward: bad P / image size", cudaSuccess);
+    if (a->P < 0 || a->width <= 0 || a->height <= 0 || a->accumulate < 0 || a->accumulate > 2) {
+        set_err("wgs_backward: bad P / image size / accumulate mode", cudaSuccess);
         return WGS_ERR_INVALID_ARGUMENT;
     }
     if (a->P == 0) {

@@ -25,9 +25,12 @@ __device__ __forceinline__ V3 cross(V3 a, V3 b) {
 
 __device__ __forceinline__ float rcpf(float x) { return __fdividef(1.f, x); }
 
-// gradient store: overwrite, or add to what the buffer holds (WgsBackwardArgs::accumulate)
-__device__ __forceinline__ void gput(float* __restrict__ ptr, size_t i, float v, bool acc) {
-    ptr[i] = acc ? ptr[i] + v : v;
+// gradient store (WgsBackwardArgs::accumulate): 0 overwrite, 1 add to what the buffer holds (plain read-modify-write:
+// one backward at a time per buffer), 2 add with a reduction atomic (RED.ADD.F32: backwards on several streams may
+// accumulate into one buffer concurrently; a warp's consecutive words still travel as whole sectors)
+__device__ __forceinline__ void gput(float* __restrict__ ptr, size_t i, float v, int acc) {
+    if (acc == 2) atomicAdd(ptr + i, v);
+    else ptr[i] = acc ? ptr[i] + v : v;
 }
 
 __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const float* q4, float c[6], float R[9],
@@ -60,9 +63,7 @@ template <bool STAGED>
 __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
     extern __shared__ float sh_stage[];
     const int gidx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
-    const bool live = gidx < p.P;
-    const int idx = live ? gidx : p.P - 1;  // dead threads of the last block shadow its last Gaussian, write nothing
-    const bool accm = p.accumulate != 0;
+    const int accm = p.accumulate;
     float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     // staged SH rows of this warp: packed (P,M,3) rows, or the (P,M-1,3) rest rows in raw-parameter mode
     const int sh_rw = STAGED ? (p.sh_rest ? 3 * (p.M - 1) : 3 * p.M) : 1;
@@ -70,11 +71,80 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
     const int wrow0 = blockIdx.x * WGS_PRE_BWD_THREADS + (threadIdx.x & ~31);  // first Gaussian of the warp
     float* const wstage = sh_stage + (threadIdx.x & ~31) * sh_rs;
     unsigned vmask = 0;
-    {
+    // Which Gaussian this thread works on.  STAGED: its own (the SH rows of a warp must stay one contiguous span);
+    // dead threads of the last block shadow its last Gaussian and write nothing.  Otherwise the block first COMPACTS
+    // its visible Gaussians (radii > 0 and a non-empty rectangle inside the rendered strip) onto its leading threads:
+    // the expensive part then runs on full warps and whole warps retire early -- a quarter-image strip of a mapping
+    // window keeps ~1/4 of the Gaussians, a whole view ~3/4.  Invisible Gaussians have nothing to add to an
+    // accumulating backward; an overwriting one zero-fills their outputs here.
+    bool live = gidx < p.P, work = true;
+    int idx = live ? gidx : p.P - 1;
+    int rad = 0;
+    uint2 rect = make_uint2(0u, 0u);
+    if (STAGED) {
+        rad = __ldg(p.radii + idx);
+        rect = __ldg(p.geom.rect + idx);
+    } else {
+        __shared__ uint16_t s_list[WGS_PRE_BWD_THREADS];
+        __shared__ int s_wcount[WGS_PRE_BWD_THREADS / 32];
+        const int lane_ = threadIdx.x & 31, warp_ = threadIdx.x >> 5;
+        bool vis1 = false;
+        if (live) {
+            rad = __ldg(p.radii + gidx);
+            rect = __ldg(p.geom.rect + gidx);
+            vis1 = rad > 0 && rect.x != rect.y;
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, vis1);
+        if (lane_ == 0) s_wcount[warp_] = __popc(bal);
+        if (live && !vis1 && accm == 0) {
+            const size_t i = (size_t)gidx;
+            if (p.dL_dmeans3D) { p.dL_dmeans3D[3 * i] = 0.f; p.dL_dmeans3D[3 * i + 1] = 0.f; p.dL_dmeans3D[3 * i + 2] = 0.f; }
+            if (p.dL_dmeans2D) { p.dL_dmeans2D[3 * i] = 0.f; p.dL_dmeans2D[3 * i + 1] = 0.f; p.dL_dmeans2D[3 * i + 2] = 0.f; }
+            if (p.dL_dopacity) p.dL_dopacity[i] = 0.f;
+            if (p.dL_dcolors) { p.dL_dcolors[3 * i] = 0.f; p.dL_dcolors[3 * i + 1] = 0.f; p.dL_dcolors[3 * i + 2] = 0.f; }
+            if (p.dL_dcov3D) {
+#pragma unroll
+                for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * i + k] = 0.f;
+            }
+            if (p.dL_dscales) { p.dL_dscales[3 * i] = 0.f; p.dL_dscales[3 * i + 1] = 0.f; p.dL_dscales[3 * i + 2] = 0.f; }
+            if (p.dL_drotations) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) p.dL_drotations[4 * i + k] = 0.f;
+            }
+            if (p.sh && p.dL_dsh) {
+                if (p.sh_rest) {
+                    float* __restrict__ d0 = p.dL_dsh + i * 3;
+                    d0[0] = d0[1] = d0[2] = 0.f;
+                    if (p.dL_dsh_rest)
+                        for (int k = 0; k < 3 * (p.M - 1); k++) p.dL_dsh_rest[i * (p.M - 1) * 3 + k] = 0.f;
+                } else {
+                    for (int k = 0; k < 3 * p.M; k++) p.dL_dsh[i * p.M * 3 + k] = 0.f;
+                }
+            }
+        }
+        __syncthreads();
+        int before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < WGS_PRE_BWD_THREADS / 32; w++) {
+            const int c = s_wcount[w];
+            before += w < warp_ ? c : 0;
+            total += c;
+        }
+        if (vis1) s_list[before + __popc(bal & ((1u << lane_) - 1u))] = (uint16_t)threadIdx.x;
+        __syncthreads();
+        work = (int)threadIdx.x < total;
+        live = work;
+        if (work) {
+            idx = blockIdx.x * WGS_PRE_BWD_THREADS + (int)s_list[threadIdx.x];
+            // (radii / rect of the adopted Gaussian: both answered "visible")
+            rad = __ldg(p.radii + idx);
+            rect = __ldg(p.geom.rect + idx);
+        }
+    }
+    if (work) {
         // Issue every load this Gaussian can need before looking at radii, so that the latencies
         // overlap (the kernel is latency-bound: 80 registers, 3 CTAs/SM).  Accumulator records of
         // culled Gaussians are never written, so they read as zero.
-        const int rad = __ldg(p.radii + idx);
         float4 g0 = __ldcg(p.grad.acc + 3 * idx), g1 = __ldcg(p.grad.acc + 3 * idx + 1), g2 = __ldcg(p.grad.acc + 3 * idx + 2);
         const V3 m = {__ldg(p.means3D + 3 * idx), __ldg(p.means3D + 3 * idx + 1), __ldg(p.means3D + 3 * idx + 2)};
         float s3[3] = {0.f, 0.f, 0.f}, q4[4] = {1.f, 0.f, 0.f, 0.f}, c3[6];
@@ -96,7 +166,6 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
 #pragma unroll
             for (int k = 0; k < 4; k++) q4[k] = q4[k] * rcpf(qn);
         }
-        const uint2 rect = __ldg(p.geom.rect + idx);
         const float4 ra = __ldcg(p.geom.rec + 2 * idx), rb = __ldcg(p.geom.rec + 2 * idx + 1);
         const bool vis = live && rad > 0 && rect.x != rect.y;  // rect is empty outside the rendered strip
         if (STAGED) {
@@ -352,9 +421,17 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
             for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q4[k] * qd) * rcpf(qn);
         }
         if (live && rad > 0) {   // mapper.py:1176-1182 + add_densification_stats (gaussian_model.py:745-749), visibility = radii > 0
-            if (p.stat_grad_accum) p.stat_grad_accum[idx] += sqrtf(dm2x * dm2x + dm2y * dm2y);
-            if (p.stat_denom) p.stat_denom[idx] += 1.f;
-            if (p.stat_max_radii) p.stat_max_radii[idx] = fmaxf(p.stat_max_radii[idx], (float)rad);
+            const float gn = sqrtf(dm2x * dm2x + dm2y * dm2y);
+            if (accm == 2) {   // views on several streams update the statistics concurrently
+                if (p.stat_grad_accum) atomicAdd(p.stat_grad_accum + idx, gn);
+                if (p.stat_denom) atomicAdd(p.stat_denom + idx, 1.f);
+                // non-negative floats order like their bit patterns
+                if (p.stat_max_radii) atomicMax((int*)p.stat_max_radii + idx, __float_as_int((float)rad));
+            } else {
+                if (p.stat_grad_accum) p.stat_grad_accum[idx] += gn;
+                if (p.stat_denom) p.stat_denom[idx] += 1.f;
+                if (p.stat_max_radii) p.stat_max_radii[idx] = fmaxf(p.stat_max_radii[idx], (float)rad);
+            }
         }
         if (live) {
         if (p.dL_dmeans3D) { gput(p.dL_dmeans3D, 3 * idx, dmean.x, accm); gput(p.dL_dmeans3D, 3 * idx + 1, dmean.y, accm); gput(p.dL_dmeans3D, 3 * idx + 2, dmean.z, accm); }

@@ -38,7 +38,7 @@ __device__ __forceinline__ void sh_stage_load(float* wstage, const float* __rest
 
 // rows [0, nrows) of the warp: wdst = staged row (0 for culled rows), or += for the visible rows when accumulating
 __device__ __forceinline__ void sh_stage_store(const float* wstage, float* __restrict__ wdst, unsigned vmask,
-                                               uint32_t nrows, uint32_t rw, uint32_t rs, bool accumulate) {
+                                               uint32_t nrows, uint32_t rw, uint32_t rs, int accumulate) {
     const uint32_t lane = threadIdx.x & 31;
     const bool second = lane + 32 < rw, first = lane < rw;
     __syncwarp();
@@ -48,8 +48,13 @@ __device__ __forceinline__ void sh_stage_store(const float* wstage, float* __res
             vmask &= vmask - 1;
             const float* s = wstage + i * rs + lane;
             float* d = wdst + i * rw + lane;
-            if (first) d[0] += s[0];
-            if (second) d[32] += s[32];
+            if (accumulate == 2) {   // several backwards add to this buffer concurrently (WgsBackwardArgs::accumulate)
+                if (first) atomicAdd(d, s[0]);
+                if (second) atomicAdd(d + 32, s[32]);
+            } else {
+                if (first) d[0] += s[0];
+                if (second) d[32] += s[32];
+            }
         }
     } else {
 #pragma unroll 4

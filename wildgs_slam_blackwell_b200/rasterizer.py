@@ -274,7 +274,7 @@ class grad_sink(_Scoped):
     Gaussian-parameter gradients straight into the caller's buffers
     (`buffers`: any of 'means3D', 'sh', 'colors', 'opacity', 'scales', 'rotations', 'cov3D' ->
     float32 CUDA tensor of the gradient's shape, e.g. slices of one flat allreduce bucket) and
-    autograd receives None for them; with accumulate=True the kernel adds to the buffers instead
+    autograd receives None for them; with accumulate=True (or "atomic") the kernel adds to the buffers instead
     of overwriting, so a window of views sums in place.  Pose gradients still flow through autograd.
 
         with grad_sink(bucket_views, accumulate=(k > 0)):
@@ -287,7 +287,10 @@ class grad_sink(_Scoped):
     _stack = []
 
     def __init__(self, buffers, accumulate=False):
-        self.buffers, self.accumulate = dict(buffers), bool(accumulate)
+        """accumulate: False (overwrite), True (add; one backward at a time per buffer) or "atomic" (add with reduction
+        atomics: backwards running concurrently on several streams may share the buffers; zero them first)"""
+        self.buffers = dict(buffers)
+        self.accumulate = 2 if accumulate == "atomic" else int(bool(accumulate))
 
 
 class densification_stats(_Scoped):
@@ -343,7 +346,7 @@ def backward_raw(st, s, means3D, sh, colors_precomp, scales, rotations, cov3Ds_p
         b = _lib.BackwardArgs()
         b.P, b.sh_degree, b.M, b.width, b.height = P, fa.sh_degree, M, W, H
         b.tanfovx, b.tanfovy, b.scale_modifier, b.debug = fa.tanfovx, fa.tanfovy, fa.scale_modifier, fa.debug
-        b.accumulate = int(sink is not None and sink.accumulate)
+        b.accumulate = sink.accumulate if sink is not None else 0
         b.background, b.means3D, b.sh, b.colors_precomp = fa.background, fa.means3D, fa.sh, fa.colors_precomp
         b.scales, b.rotations, b.cov3D_precomp = fa.scales, fa.rotations, fa.cov3D_precomp
         b.viewmatrix, b.projmatrix, b.projmatrix_raw, b.campos = fa.viewmatrix, fa.projmatrix, _ptr(proj_raw), fa.campos

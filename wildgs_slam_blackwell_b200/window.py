@@ -60,6 +60,56 @@ def assign_strips(costs: Sequence[float], world: int, tile_rows: int) -> List[Li
     return out
 
 
+def assign_balanced(costs: Sequence[float], world: int, tile_rows: int) -> List[List[tuple]]:
+    """Whole views first, strips only for the remainder.  With n views on `world` ranks every rank gets
+    floor(n / world) WHOLE views (longest-processing-time first); the n mod world cheapest views are laid end to end
+    and cut at tile-row granularity into one piece per rank, sized so that the ranks' total loads come out equal.
+    Returns per rank a list of (view, row_begin, row_end), whole views first; every (view, row) appears exactly once
+    and every rank computes the same plan.
+
+    Against assign_strips (all views end to end) the number of work units is the same, but the partial units are all
+    SMALL strips (10 keyframes on 8 GPUs: one whole view + a quarter of another per rank) -- the per-Gaussian stages of
+    a small strip reject most Gaussians early (block-local compaction in preprocess_bwd), and a rank can run its strip
+    on a second stream next to its whole view (WindowTrainer(streams=2))."""
+    world = max(int(world), 1)
+    n, rows = len(costs), int(tile_rows)
+    c = [max(float(x), 1e-9) for x in costs]
+    k, r = divmod(n, world)
+    order = sorted(range(n), key=lambda v: (-c[v], v))
+    whole_views, split_views = order[:n - r], sorted(order[n - r:])
+    out: List[List[tuple]] = [[] for _ in range(world)]
+    load = [0.0] * world
+    for v in whole_views:                                   # LPT with exactly k views per rank
+        i = min((i for i in range(world) if len(out[i]) < k), key=lambda i: (load[i], i))
+        out[i].append((v, 0, rows))
+        load[i] += c[v]
+    for lst in out:
+        lst.sort()
+    if r:
+        total = sum(c)
+        target = [max(total / world - load[i], 0.0) for i in range(world)]      # what rank i still has to take
+        scale = sum(c[v] for v in split_views) / max(sum(target), 1e-30)        # (targets sum to the remainder)
+        target = [t * scale for t in target]
+        i, acc = 0, 0.0
+        for v in split_views:
+            begin = 0
+            w = c[v] / rows
+            for row in range(rows):
+                acc += w
+                if i < world - 1 and acc >= target[i] - 1e-12 * total:
+                    out[i].append((v, begin, row + 1))
+                    begin, acc = row + 1, acc - target[i]
+                    i += 1
+                    while i < world - 1 and target[i] <= 1e-12 * total:         # (a rank whose whole views fill its share)
+                        i += 1
+            if begin < rows:
+                out[i].append((v, begin, rows))
+        loads = [sum(c[v] * (e - b) / rows for v, b, e in units) for units in out]
+        if max(loads) > 1.08 * sum(c) / world:              # very uneven views: whole views cannot balance them
+            return assign_strips(costs, world, tile_rows)
+    return out
+
+
 class GradBucket:
     """One flat fp32 buffer holding the gradients of all replicated leaves back to back, plus
     per-leaf views into it.  Installing the views as `.grad` makes autograd accumulate straight into
@@ -147,7 +197,7 @@ class WindowTrainer:
 
     def _finish(self, side, fused, cost_fn, assignment):
         b = self.bucket
-        if self.world > 1:
+        if self._exchange:
             work = b.all_reduce(self.group, async_op=True)
             if not fused:
                 dist.all_reduce(side, group=self.group)
@@ -160,17 +210,30 @@ class WindowTrainer:
 
     def __init__(self, params: Dict[str, torch.Tensor], group: Optional[dist.ProcessGroup] = None,
                  sink_names: Optional[Dict[str, str]] = None, peer: bool = False, peer_mode: str = "auto",
-                 densify_stats: bool = False):
+                 densify_stats: bool = False, streams: int = 1, emulate: Optional[tuple] = None):
         """`sink_names` (optional): leaf name -> rasterizer gradient name ('means3D', 'sh', 'opacity',
         'scales', 'rotations', ...).  When given, the rasterizer's backward kernel writes / accumulates
         straight into the bucket (rasterizer.grad_sink) instead of autograd allocating per-view
         gradient tensors and adding them; requires that the leaves are passed to the rasterizer
         unmodified (no activation in between)."""
+        """streams=2 (needs sink_names): a rank's work units run on two CUDA streams, all of them accumulating
+        into the bucket with reduction atomics -- the small kernels of one unit (scan, sort, per-Gaussian stages) and
+        the tail waves of its compositing kernels overlap the other unit's work; inside a CUDA graph the two branches
+        are scheduled by the device.  The bucket sum is then order-dependent in the last bit.
+        emulate=(rank, world): measurement aid -- run the units rank `rank` of a `world`-rank job would run, in this
+        single process, without the exchange (the per-rank compute time of an N-GPU step on one GPU)."""
         self.sink_names = sink_names
         self.group = group
         self.distributed = dist.is_available() and dist.is_initialized()
         self.world = dist.get_world_size(group) if self.distributed else 1
         self.rank = dist.get_rank(group) if self.distributed else 0
+        self._exchange = self.world > 1
+        if emulate is not None:
+            if self.distributed:
+                raise RuntimeError("emulate=(rank, world) is for a single, non-distributed process")
+            self.rank, self.world = int(emulate[0]), int(emulate[1])
+        self.streams = int(streams) if sink_names is not None else 1
+        self._side_stream = None
         # peer=True: bucket in NVLink peer memory, summed by wgs_peer_allreduce (single node, CUDA only)
         self._peer_group = (group if group is not None else dist.group.WORLD) if (peer and self.world > 1) else None
         self._peer_mode = peer_mode
@@ -213,72 +276,94 @@ class WindowTrainer:
         else:
             self.bucket.params = params
 
-    def step(self, n_views: int, render_loss: Callable, cost_fn: Optional[Callable[[int], float]] = None,
-             tile_rows: Optional[int] = None):
-        """`tile_rows` (= ceil(H/16)), when given and the window does not divide by the world size, switches to
-        sub-frame units (assign_strips): render_loss(v) is then called inside rasterizer.tile_rows(b, e) and
-        must return a loss that is a sum over pixels (images are zero outside the strip); per-view losses,
-        costs and pose gradients are summed over the strips of a view."""
+    def plan(self, n_views: int, tile_rows: Optional[int] = None, plan: Optional[str] = None) -> List[List[tuple]]:
+        """Work units (view, row_begin, row_end) per rank; a whole view is (view, 0, tile_rows) -- or (view, 0, 0) when
+        no tile_rows were given -- and is rendered without a strip.  plan: 'views' (whole views, LPT), 'strips' (all views end to end, cut per rank), 'balanced' (whole
+        views + strips of the remainder); None = 'views', or 'strips' when tile_rows is given and the window does not
+        divide by the world size (the behaviour before `plan` existed)."""
         if len(self.costs) != n_views:
             self.costs = [1.0] * n_views
-        if tile_rows is not None and self.world > 1 and n_views % self.world != 0:
-            return self._step_strips(n_views, render_loss, cost_fn, int(tile_rows))
-        assignment = assign_views(self.costs, self.world)
-        mine = assignment[self.rank]
+        divides = self.world <= 1 or n_views % self.world == 0
+        if plan is None:
+            plan = "views" if (tile_rows is None or divides) else "strips"
+        if plan != "views" and tile_rows is None:
+            raise ValueError(f"plan='{plan}' needs tile_rows (= ceil(H / 16))")
+        rows = int(tile_rows) if tile_rows is not None else 0
+        if plan == "views" or divides:
+            return [[(v, 0, rows) for v in views] for views in assign_views(self.costs, self.world)]
+        return assign_strips(self.costs, self.world, rows) if plan == "strips" else assign_balanced(self.costs, self.world, rows)
+
+    def step(self, n_views: int, render_loss: Callable, cost_fn: Optional[Callable[[int], float]] = None,
+             tile_rows: Optional[int] = None, plan: Optional[str] = None):
+        """`tile_rows` (= ceil(H/16)), when given and the window does not divide by the world size, switches to
+        sub-frame units (see plan()): render_loss(v) is then called inside rasterizer.tile_rows(b, e) and
+        must return a loss that is a sum over pixels (images are zero outside the strip); per-view losses,
+        costs and pose gradients are summed over the strips of a view."""
+        from . import rasterizer
+        units = self.plan(n_views, tile_rows, plan)
+        mine = units[self.rank]
+        rows = int(tile_rows) if tile_rows is not None else 0
+        is_whole = lambda u: u[1] == 0 and u[2] == rows
+        strips = any(not is_whole(u) for lst in units for u in lst)
+        if strips and self._stats:
+            raise RuntimeError("densify_stats needs whole views (the gradient norm is per view): call step() without tile_rows")
         b = self.bucket
         use_sink = self.sink_names is not None and len(mine) > 0
+        two = use_sink and self.streams > 1 and len(mine) > 1
         if use_sink:
-            from . import rasterizer
             sink_bufs = {g: b.views[k] for k, g in self.sink_names.items()}
             for p in b.params.values():
                 p.grad = None
+            if two:
+                b.flat.zero_()                       # every unit adds atomically
         else:
             b.install()
         side, fused = self._side(n_views)  # loss, cost, pose grad (6)
         if self._stats:
             b.stats.zero_()
-        for n_done, v in enumerate(mine):
-            # the contexts surround the FORWARD as well: the rasterizer binds them to that forward's backward, which
-            # keeps two trainers on two threads / streams of one process apart (rasterizer._Scoped)
-            with self._stats_ctx(), (rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0) if use_sink else _null()):
-                loss, pose_grad_fn = render_loss(v)
-                loss.backward()
-            side[v, 0] = loss.detach()
-            side[v, 1].fill_(float(cost_fn(v)) if cost_fn is not None else 1.0)  # fill_: no H2D copy (graph capture)
-            if pose_grad_fn is not None:
-                side[v, 2:8] = pose_grad_fn().reshape(6)
-        if use_sink:
-            b.install(zero=False)
-        return self._finish(side, fused, cost_fn, assignment)
 
-    def _step_strips(self, n_views, render_loss, cost_fn, tile_rows):
-        from . import rasterizer
-        if self._stats:
-            raise RuntimeError("densify_stats needs whole views (the gradient norm is per view): call step() without tile_rows")
-        plan = assign_strips(self.costs, self.world, tile_rows)
-        mine = plan[self.rank]
-        b = self.bucket
-        use_sink = self.sink_names is not None and len(mine) > 0
-        if use_sink:
-            sink_bufs = {g: b.views[k] for k, g in self.sink_names.items()}
-            for p in b.params.values():
-                p.grad = None
-        else:
-            b.install()
-        side, fused = self._side(n_views)
-        for n_done, (v, r0, r1) in enumerate(mine):
-            whole = r0 == 0 and r1 == tile_rows
-            with (rasterizer.tile_rows(r0, r1) if not whole else _null()), \
-                    (rasterizer.grad_sink(sink_bufs, accumulate=n_done > 0) if use_sink else _null()):
+        def run(unit, first):
+            v, r0, r1 = unit
+            whole = is_whole(unit)
+            acc = "atomic" if two else (not first)
+            # the contexts surround the FORWARD as well: the rasterizer binds them to that forward's backward, which
+            # keeps units on two streams (and two trainers on two threads) apart (rasterizer._Scoped)
+            with (rasterizer.tile_rows(r0, r1) if not whole else _null()), self._stats_ctx(), \
+                    (rasterizer.grad_sink(sink_bufs, accumulate=acc) if use_sink else _null()):
                 loss, pose_grad_fn = render_loss(v)
                 loss.backward()
+            frac = 1.0 if whole else (r1 - r0) / rows
+            # (add_/+=: the strips of a view sum; fill-free so that nothing is copied from the host under capture)
             side[v, 0] += loss.detach()
-            side[v, 1].add_(float(cost_fn(v)) if cost_fn is not None else (r1 - r0) / tile_rows)
+            side[v, 1].add_(float(cost_fn(v)) * frac if cost_fn is not None else frac)
             if pose_grad_fn is not None:
                 side[v, 2:8] += pose_grad_fn().reshape(6)
+
+        if two:
+            # longest-processing-time split of the rank's units over the two streams
+            w = lambda u: self.costs[u[0]] * (1.0 if is_whole(u) else (u[2] - u[1]) / rows)
+            lanes, load = ([], []), [0.0, 0.0]
+            for u in sorted(mine, key=lambda u: -w(u)):
+                i = 0 if load[0] <= load[1] else 1
+                lanes[i].append(u)
+                load[i] += w(u)
+            dev = b.flat.device
+            if self._side_stream is None:
+                self._side_stream = torch.cuda.Stream(dev)
+            main = torch.cuda.current_stream(dev)
+            self._side_stream.wait_stream(main)
+            with torch.cuda.stream(self._side_stream):
+                for u in lanes[1]:
+                    run(u, False)
+            for u in lanes[0]:
+                run(u, False)
+            main.wait_stream(self._side_stream)
+        else:
+            for n_done, u in enumerate(mine):
+                run(u, n_done == 0)
         if use_sink:
             b.install(zero=False)
-        return self._finish(side, fused, cost_fn, plan)
+        return self._finish(side, fused, cost_fn, units if strips else [[v for v, _, _ in u] for u in units])
 
 
 class _null:
