@@ -70,7 +70,9 @@ def _lib_loss():
 
 
 def _workspace(device, W, H):
-    key = (device.index, W, H)
+    # per stream: the block partials / ticket of two losses in flight on two streams must not mix (a mapping
+    # window runs its views on two streams)
+    key = (device.index, int(torch.cuda.current_stream(device).cuda_stream), W, H)
     ws = _ws.get(key)
     if ws is None:
         ws = torch.zeros(int(_lib_loss().wgs_loss_workspace_bytes(W, H)), dtype=torch.uint8, device=device)
