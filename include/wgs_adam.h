@@ -28,7 +28,8 @@ typedef struct WgsAdamTensor {
   float bias_correction2_sqrt; /* sqrt(1 - beta2^step); ignored with step_dev */
   /* Graph-capturable mode (torch's `capturable=True`): the step count lives on the device, so a captured launch
    * advances it on every replay.  step_dev: 1 float, the number of steps taken so far -- the kernel forms both bias
-   * corrections from step_dev[0] + 1 in double and a second launch increments the counters.  lr_dev (optional):
+   * corrections from step_dev[0] + 1 in double and a second launch increments the counters (descriptors of one call
+   * may share a counter: it is advanced once).  lr_dev (optional):
    * 1 float read at run time, for learning-rate schedules under a captured graph.  Both null: host-side mode. */
   float* step_dev;
   const float* lr_dev;

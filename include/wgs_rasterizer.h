@@ -260,6 +260,19 @@ int wgs_camera_matrices(const float* R, const float* T, const float* projection_
 size_t wgs_peer_flags_bytes(void);
 int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
                        int32_t world, uint64_t n_floats, void* cuda_stream);
+/* The general form.  The exchanged data are `n_segments` (<= 12) pieces of the buffer, seg_offsets[k] / seg_lengths[k]
+ * in floats (multiples of 4) -- a capacity-headroom arena keeps every leaf's gradient in its own segment and only the
+ * used rows travel -- laid end to end as one virtual array of which rank r owns the r-th 1/world slice.
+ *   mode 0  allreduce       every copy ends up holding the sum
+ *   mode 1  reduce-scatter  this rank's copy of ITS slice receives the sum over all ranks (the other slices are untouched):
+ *                           the first half of a sharded optimiser step -- Adam then runs on 1/world of the model per rank
+ *   mode 2  allgather       this rank's copy of its slice is written into every rank's copy (on another buffer of the same
+ *                           layout, the updated parameters return to all ranks)
+ * Every call is bracketed by the block-level peer barriers of wgs_peer_allreduce; flag_ptrs may belong to a different
+ * allocation than buffer_ptrs (one flag area serves all buffers exchanged in stream order). */
+int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
+                      int32_t world, const uint64_t* seg_offsets, const uint64_t* seg_lengths, int32_t n_segments,
+                      int32_t mode, void* cuda_stream);
 
 int wgs_stage_timing(WgsContext* ctx, int enable);
 int wgs_stage_times(WgsContext* ctx, float* ms_out /* WGS_NUM_STAGES floats, host */);

@@ -132,3 +132,104 @@ def test_window_trainer_two_gpus_real_rasterizer(tmp_path):
             assert v["ok"], (name, v)
             if "plans" in v:
                 assert set(v["plans"]) == {"views", "strips", "balanced"} and v["max_rel_err"] <= 1e-3, (name, v)
+
+
+def _arena_worker(rank, world, port, out_dir):
+    """Sharded optimiser step (reduce-scatter -> Adam on the owned 1/world slice -> parameter allgather) against the
+    replicated one (allreduce -> Adam on everything) on a capacity-segmented arena, across an append and a prune (the
+    ownership slices move: the moments are gathered first); the segmented exchange modes against NCCL."""
+    import torch.distributed as dist
+    from wildgs_slam_blackwell_b200.arena import GaussianArena
+    from wildgs_slam_blackwell_b200.peer import owned_pieces
+    from wildgs_slam_blackwell_b200.window import GradBucket
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    ok = {}
+    try:
+        lrs = {"xyz": 1e-3, "f_dc": 2e-3, "opacity": 5e-2, "scaling": 1e-3, "rotation": 1e-3}
+        for mode in ("p2p", "nvls"):
+            def leaves(P):
+                g = torch.Generator(device=dev).manual_seed(3)
+                r = lambda *s: torch.randn(*s, device=dev, generator=g)
+                return {"xyz": r(P, 3), "f_dc": r(P, 1, 3), "opacity": r(P, 1), "scaling": r(P, 3), "rotation": r(P, 4)}
+            arenas = [GaussianArena(leaves(20_001), group=dist.group.WORLD, peer_mode=mode) for _ in range(2)]   # [replicated, sharded]
+            buckets = [GradBucket(a.params, dist.group.WORLD, mode, side_floats=64, stat_floats=2, capacity=a.capacity) for a in arenas]
+            step = 0
+
+            def fill(a, b):
+                for i, k in enumerate(a.names):       # each rank contributes its own gradient
+                    b.views[k].copy_(torch.cos(a.params[k].detach() * (1.5 + i) + 0.3 * step + rank))
+                b.side.fill_(float(rank + 1))
+
+            def both_steps():
+                nonlocal step
+                step += 1
+                fill(arenas[0], buckets[0])
+                want = {k: buckets[0].views[k].clone() for k in arenas[0].names}
+                for t in want.values():
+                    dist.all_reduce(t)
+                buckets[0].all_reduce()
+                torch.cuda.synchronize()
+                good = all(torch.allclose(buckets[0].views[k], want[k], rtol=1e-6, atol=1e-6) for k in want)
+                good = good and bool((buckets[0].side == sum(range(1, world + 1))).all())
+                arenas[0].adam_step(buckets[0], lrs)
+                fill(arenas[1], buckets[1])
+                buckets[1].reduce_scatter()
+                torch.cuda.synchronize()
+                for off, n in owned_pieces(arenas[1].segments(), rank, world):        # my slice holds the sum
+                    k = next(name for name in arenas[1].names if arenas[1].offsets[name] <= off < arenas[1].offsets[name] + arenas[1].capacity * arenas[1].widths[name])
+                    lo = off - arenas[1].offsets[k]
+                    n_used = min(n, arenas[1].P * arenas[1].widths[k] - lo)
+                    good = good and torch.allclose(buckets[1]._all[off:off + n_used], want[k].reshape(-1)[lo:lo + n_used], rtol=1e-6, atol=1e-6)
+                good = good and bool((buckets[1].side == sum(range(1, world + 1))).all())
+                arenas[1].sharded_adam_step(buckets[1], lrs)
+                torch.cuda.synchronize()
+                return good and all(torch.equal(arenas[0].params[k].detach(), arenas[1].params[k].detach()) for k in arenas[0].names)
+
+            res = [both_steps(), both_steps()]
+            new = {k: p.detach()[:5_003] * 0.5 for k, p in arenas[0].params.items()}   # append: within the capacity class
+            for a, b in zip(arenas, buckets):
+                a.append(new)
+                b.retarget(a.params)
+            res += [both_steps(), both_steps()]
+            remove = torch.arange(arenas[0].P, device=dev) % 5 == 0                  # prune
+            for a, b in zip(arenas, buckets):
+                a.prune(remove)
+                b.retarget(a.params)
+            res += [both_steps()]
+            for a in arenas:
+                a._sync_moments()
+            torch.cuda.synchronize()
+            res.append(all(torch.equal(arenas[0].moments(k)[j], arenas[1].moments(k)[j]) for k in arenas[0].names for j in (0, 1)))
+            big = {k: p.detach().repeat(2, *([1] * (p.dim() - 1))) for k, p in arenas[0].params.items()}   # new capacity class
+            grew = [a.append(big) for a in arenas]
+            buckets = [GradBucket(a.params, dist.group.WORLD, mode, side_floats=64, stat_floats=2, capacity=a.capacity) for a in arenas]
+            res += [all(grew), both_steps()]
+            ok[mode] = res
+            del arenas, buckets
+        torch.save(ok, os.path.join(out_dir, f"arena{rank}.pt"))
+    finally:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one NVLink domain")
+def test_sharded_adam_matches_replicated_two_gpus(tmp_path):
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    world = 2
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=_arena_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(600)
+        assert p.exitcode == 0
+    for r in range(world):
+        ok = torch.load(tmp_path / f"arena{r}.pt")
+        for mode, res in ok.items():
+            assert len(res) == 8 and all(res), (mode, res)

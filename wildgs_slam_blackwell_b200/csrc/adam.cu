@@ -69,7 +69,11 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const __grid_constan
 // after the update: advance the device-side step counters of the capturable tensors
 __global__ void adam_advance_kernel(const __grid_constant__ AdamParams p) {
     const int e = threadIdx.x;
-    if (e < p.count && p.t[e].step_dev) *p.t[e].step_dev += 1.f;
+    if (e < p.count && p.t[e].step_dev) {
+        bool first = true;   // descriptors may share one counter (segments of one arena): advance it once
+        for (int j = 0; j < e; j++) first = first && p.t[j].step_dev != p.t[e].step_dev;
+        if (first) *p.t[e].step_dev += 1.f;
+    }
 }
 
 }  // namespace wgs

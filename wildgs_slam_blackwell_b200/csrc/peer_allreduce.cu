@@ -17,14 +17,33 @@ constexpr int PEER_MAX_WORLD = 16;
 constexpr int PEER_BLOCKS = 144;  // ~one CTA per SM: the kernel runs alone, what matters is bytes in flight on NVLink
 constexpr int PEER_THREADS = 512;
 
+constexpr int PEER_MAX_SEGMENTS = 12;
+
 struct PeerParams {
-    float* buf[PEER_MAX_WORLD];        // this rank's mapping of every rank's bucket
+    float* buf[PEER_MAX_WORLD];        // this rank's mapping of every rank's buffer
     uint32_t* flags[PEER_MAX_WORLD];   // ... and of every rank's flag array [PEER_BLOCKS][PEER_MAX_WORLD]
-    float* mc;                         // multicast mapping of the bucket (null: P2P path)
+    float* mc;                         // multicast mapping of the buffer (null: P2P path)
     int rank, world;
-    size_t n4;                         // float4 elements
+    int mode;                          // 0 allreduce, 1 reduce-scatter (sum of my slice -> my copy), 2 allgather (my slice -> all)
+    int nseg;
+    size_t seg_off4[PEER_MAX_SEGMENTS];   // the exchanged data: `nseg` pieces of the buffer (offset / length in float4),
+    size_t seg_end4[PEER_MAX_SEGMENTS];   // laid end to end as one virtual array; seg_end4 = running end in that array
+    size_t n4;                         // float4 elements of the virtual array
     uint32_t* epochs;                  // [PEER_BLOCKS] in THIS rank's flag area: barrier generation of each block
 };
+
+// virtual float4 index -> float4 offset inside the buffer
+__device__ __forceinline__ size_t seg_addr(const PeerParams& p, size_t i) {
+    size_t begin = 0;
+#pragma unroll
+    for (int s = 0; s < PEER_MAX_SEGMENTS - 1; s++) {
+        if (s + 1 < p.nseg && i >= p.seg_end4[s]) begin = p.seg_end4[s];
+    }
+    int k = 0;
+#pragma unroll
+    for (int s = 0; s < PEER_MAX_SEGMENTS - 1; s++) k += (s + 1 < p.nseg && i >= p.seg_end4[s]) ? 1 : 0;
+    return p.seg_off4[k] + (i - begin);
+}
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -69,32 +88,52 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const __gr
     const size_t per = (p.n4 + p.world - 1) / p.world;
     const size_t begin = min(p.n4, per * p.rank), end = min(p.n4, begin + per);
     const size_t stride = (size_t)gridDim.x * PEER_THREADS;
+    const bool reduce = p.mode != 2, spread = p.mode != 1;
+    float4* const mine = reinterpret_cast<float4*>(p.buf[p.rank]);
     constexpr int U = 4;  // independent float4 per thread and trip: keeps U (x world) 16-B requests in flight
     for (size_t i0 = begin + (size_t)blockIdx.x * PEER_THREADS + threadIdx.x; i0 < end; i0 += U * stride) {
         float4 s[U];
+        size_t a[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) a[u] = i0 + u * stride < end ? seg_addr(p, i0 + u * stride) : 0;
         if (NVLS) {
 #pragma unroll
             for (int u = 0; u < U; u++)
-                if (i0 + u * stride < end) s[u] = multimem_ld_reduce(p.mc + 4 * (i0 + u * stride));
+                if (i0 + u * stride < end) s[u] = reduce ? multimem_ld_reduce(p.mc + 4 * a[u]) : __ldcg(mine + a[u]);
 #pragma unroll
             for (int u = 0; u < U; u++)
-                if (i0 + u * stride < end) multimem_st(p.mc + 4 * (i0 + u * stride), s[u]);
+                if (i0 + u * stride < end) {
+                    if (spread) multimem_st(p.mc + 4 * a[u], s[u]);
+                    else __stcg(mine + a[u], s[u]);
+                }
         } else {
 #pragma unroll
             for (int u = 0; u < U; u++) s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int r = 0; r < p.world; r++) {   // fixed order: identical bits on every run
-                float4 v[U];
+            if (reduce) {
+                for (int r = 0; r < p.world; r++) {   // fixed order: identical bits on every run
+                    float4 v[U];
+#pragma unroll
+                    for (int u = 0; u < U; u++)
+                        v[u] = i0 + u * stride < end ? __ldcg(reinterpret_cast<const float4*>(p.buf[r]) + a[u])
+                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int u = 0; u < U; u++) { s[u].x += v[u].x; s[u].y += v[u].y; s[u].z += v[u].z; s[u].w += v[u].w; }
+                }
+            } else {
 #pragma unroll
                 for (int u = 0; u < U; u++)
-                    v[u] = i0 + u * stride < end ? __ldcg(reinterpret_cast<const float4*>(p.buf[r]) + i0 + u * stride)
-                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                for (int u = 0; u < U; u++) { s[u].x += v[u].x; s[u].y += v[u].y; s[u].z += v[u].z; s[u].w += v[u].w; }
+                    if (i0 + u * stride < end) s[u] = __ldcg(mine + a[u]);
             }
-            for (int r = 0; r < p.world; r++)
+            if (spread) {
+                for (int r = 0; r < p.world; r++)
+#pragma unroll
+                    for (int u = 0; u < U; u++)
+                        if (i0 + u * stride < end) __stcg(reinterpret_cast<float4*>(p.buf[r]) + a[u], s[u]);
+            } else {
 #pragma unroll
                 for (int u = 0; u < U; u++)
-                    if (i0 + u * stride < end) __stcg(reinterpret_cast<float4*>(p.buf[r]) + i0 + u * stride, s[u]);
+                    if (i0 + u * stride < end) __stcg(mine + a[u], s[u]);
+            }
         }
     }
     block_barrier(p, epoch + 1u);
@@ -110,12 +149,13 @@ size_t wgs_peer_flags_bytes(void) {
     return (size_t)wgs::PEER_BLOCKS * (wgs::PEER_MAX_WORLD + 1) * sizeof(uint32_t);  // flags + per-block generation
 }
 
-int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
-                       int32_t world, uint64_t n_floats, void* cuda_stream) {
+int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
+                      int32_t world, const uint64_t* seg_offsets, const uint64_t* seg_lengths, int32_t n_segments,
+                      int32_t mode, void* cuda_stream) {
     using namespace wgs;
     if (!buffer_ptrs || !flag_ptrs || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world ||
-        (n_floats & 3u)) {
-        wgs_set_error_message("wgs_peer_allreduce: bad world/rank or n_floats not a multiple of 4");
+        !seg_offsets || !seg_lengths || n_segments < 1 || n_segments > PEER_MAX_SEGMENTS || mode < 0 || mode > 2) {
+        wgs_set_error_message("wgs_peer_exchange: bad world/rank/segment table/mode");
         return WGS_ERR_INVALID_ARGUMENT;
     }
     PeerParams p;
@@ -123,11 +163,25 @@ int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, u
         p.buf[r] = r < world ? (float*)buffer_ptrs[r] : nullptr;
         p.flags[r] = r < world ? (uint32_t*)flag_ptrs[r] : nullptr;
         if (r < world && (!p.buf[r] || !p.flags[r] || (buffer_ptrs[r] & 15u))) {
-            wgs_set_error_message("wgs_peer_allreduce: null or misaligned peer pointer");
+            wgs_set_error_message("wgs_peer_exchange: null or misaligned peer pointer");
             return WGS_ERR_INVALID_ARGUMENT;
         }
     }
-    p.mc = (float*)multicast_ptr; p.rank = rank; p.world = world; p.n4 = n_floats / 4;
+    size_t run = 0;
+    for (int k = 0; k < PEER_MAX_SEGMENTS; k++) {
+        if (k < n_segments) {
+            if ((seg_offsets[k] & 3u) || (seg_lengths[k] & 3u)) {
+                wgs_set_error_message("wgs_peer_exchange: segment offsets and lengths must be multiples of 4 floats");
+                return WGS_ERR_INVALID_ARGUMENT;
+            }
+            p.seg_off4[k] = seg_offsets[k] / 4;
+            run += seg_lengths[k] / 4;
+        } else {
+            p.seg_off4[k] = 0;
+        }
+        p.seg_end4[k] = run;
+    }
+    p.mc = (float*)multicast_ptr; p.rank = rank; p.world = world; p.n4 = run; p.mode = mode; p.nseg = n_segments;
     p.epochs = p.flags[rank] + PEER_BLOCKS * PEER_MAX_WORLD;
     cudaStream_t s = (cudaStream_t)cuda_stream;
     if (p.mc) peer_allreduce_kernel<true><<<PEER_BLOCKS, PEER_THREADS, 0, s>>>(p);
@@ -138,5 +192,11 @@ int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, u
         return WGS_ERR_CUDA;
     }
     return WGS_OK;
+}
+
+int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
+                       int32_t world, uint64_t n_floats, void* cuda_stream) {
+    const uint64_t off = 0;
+    return wgs_peer_exchange(buffer_ptrs, flag_ptrs, multicast_ptr, rank, world, &off, &n_floats, 1, 0, cuda_stream);
 }
 }

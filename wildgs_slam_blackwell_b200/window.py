@@ -111,60 +111,135 @@ def assign_balanced(costs: Sequence[float], world: int, tile_rows: int) -> List[
 
 
 class GradBucket:
-    """One flat fp32 buffer holding the gradients of all replicated leaves back to back, plus
-    per-leaf views into it.  Installing the views as `.grad` makes autograd accumulate straight into
-    the buffer, so the allreduce needs no packing copy."""
+    """One fp32 buffer holding the gradients of all replicated leaves, plus per-leaf views into it.  Installing the
+    views as `.grad` makes autograd accumulate straight into the buffer, so the exchange needs no packing copy.
+
+    capacity=None: the leaves sit back to back (one flat range).  capacity=C (rows, >= P): every leaf owns a SEGMENT
+    sized for C rows and uses its first P -- a model that grows by densification or shrinks by pruning re-targets the
+    views (`retarget`) without re-allocating, so a bucket in symmetric peer memory is rendezvoused once per capacity
+    class, not once per densification; only the used rows are exchanged (segment list of the peer kernel)."""
 
     def __init__(self, params: Dict[str, torch.Tensor], peer_group=None, peer_mode: str = "auto", side_floats: int = 0,
-                 stat_floats: int = 0):
+                 stat_floats: int = 0, capacity: Optional[int] = None):
         """stat_floats: floats between the gradients and the side block (`self.stats`), summed by the same allreduce --
-        the window's densification statistics.
+        the window's densification statistics (2 per Gaussian; with a capacity: 2 segments of `capacity` floats).
         side_floats: extra floats behind the gradients (`self.side`) that ride in the same allreduce -- the window's
         per-view losses / costs / pose gradients, so that a step is ONE collective.
         peer_group: a process group whose ranks share one NVLink domain -> the buffer is allocated in
         symmetric peer memory (peer.PeerBucket) and all_reduce() runs the library's own kernel instead of
         ncclAllReduce.  peer_mode: 'nvls' | 'p2p' | 'auto' (multicast from 4 ranks up)."""
         self.names = list(params)
-        self.params = params
-        n = sum(p.numel() for p in params.values())
         first = next(iter(params.values()))
+        P = first.shape[0]
+        self.widths = {k: (p.numel() // P if P else int(torch.tensor(p.shape[1:]).prod())) for k, p in params.items()}
+        self.tails = {k: tuple(p.shape[1:]) for k, p in params.items()}
+        for k, p in params.items():
+            if p.dtype != torch.float32:
+                raise TypeError(f"GradBucket: leaf {k} must be float32")
+        self.capacity = None if capacity is None else max((int(capacity) + 3) // 4 * 4, (P + 3) // 4 * 4)
+        self._with_stats = stat_floats > 0
+        rows = P if self.capacity is None else self.capacity
+        self.offsets, off = {}, 0
+        for k in self.names:
+            self.offsets[k] = off
+            off += rows * self.widths[k]
+        self._grad_floats = off
+        self._stat_off = off
+        stat_total = (2 * rows if self.capacity is not None else stat_floats) if self._with_stats else 0
+        self._side_off = off + stat_total
+        total = self._side_off + side_floats
         self.peer = None
         if peer_group is not None and first.is_cuda:
             from .peer import PeerBucket
             world = dist.get_world_size(peer_group)
             mc = peer_mode == "nvls" or (peer_mode == "auto" and world >= 4)
-            self.peer = PeerBucket(n + side_floats + stat_floats, first.device, peer_group, use_multicast=mc)
+            self.peer = PeerBucket(total, first.device, peer_group, use_multicast=mc)
             self._all = self.peer.flat
         else:
-            self._all = torch.zeros(n + side_floats + stat_floats, dtype=torch.float32, device=first.device)
-        self.flat, self.stats, self.side = self._all[:n], self._all[n:n + stat_floats], self._all[n + stat_floats:]
+            self._all = torch.zeros(total, dtype=torch.float32, device=first.device)
+        self.side = self._all[self._side_off:]
         self.views: Dict[str, torch.Tensor] = {}
-        off = 0
-        for k, p in params.items():
-            if p.dtype != torch.float32:
-                raise TypeError(f"GradBucket: leaf {k} must be float32")
-            self.views[k] = self.flat[off:off + p.numel()].view(p.shape)
-            off += p.numel()
+        self.retarget(params)
+
+    def retarget(self, params: Dict[str, torch.Tensor]):
+        """Point the views at the first P rows of every segment (P = rows of `params`; same leaves, P <= capacity)."""
+        P = next(iter(params.values())).shape[0]
+        if list(params) != self.names or any(tuple(params[k].shape[1:]) != self.tails[k] for k in params) or \
+                (self.capacity is not None and P > self.capacity) or (self.capacity is None and self.views and P != self.P):
+            raise ValueError("GradBucket.retarget: other leaves, or more rows than the bucket's capacity")
+        self.params, self.P = params, P
+        for k in self.names:
+            o = self.offsets[k]
+            self.views[k] = self._all[o:o + P * self.widths[k]].view((P,) + self.tails[k])
+        if self.capacity is None:
+            self.flat = self._all[:self._grad_floats]
+            self.stats = self._all[self._stat_off:self._side_off]
+            self.stat_views = (self.stats[:P], self.stats[P:2 * P]) if self._with_stats else None
+            self._segments = None
+        else:
+            self.flat = self._all[:self._grad_floats]      # (includes the unused rows of every segment)
+            r4 = lambda n: (n + 3) // 4 * 4
+            self._segments = [(self.offsets[k], r4(P * self.widths[k])) for k in self.names]
+            if self._with_stats:
+                c = self.capacity
+                self.stat_views = (self._all[self._stat_off:self._stat_off + P], self._all[self._stat_off + c:self._stat_off + c + P])
+                self._segments += [(self._stat_off, r4(P)), (self._stat_off + c, r4(P))]
+            else:
+                self.stat_views = None
+            self.stats = self._all[self._stat_off:self._side_off]
+            if self.side.numel():
+                self._segments.append((self._side_off, r4(self.side.numel())))
+
+    @property
+    def device(self):
+        return self._all.device
 
     def matches(self, params: Dict[str, torch.Tensor]) -> bool:
-        return list(params) == self.names and all(params[k].shape == self.views[k].shape and
-                                                  params[k].device == self.flat.device for k in params)
+        """True if `params` can use this bucket as it is laid out (same leaves; the same P, or P within the capacity)."""
+        if list(params) != self.names or any(tuple(params[k].shape[1:]) != self.tails[k] or params[k].device != self._all.device
+                                             for k in params):
+            return False
+        P = next(iter(params.values())).shape[0]
+        return P == self.P if self.capacity is None else P <= self.capacity
+
+    def zero_grads(self):
+        if self.capacity is None:
+            self.flat.zero_()
+        else:
+            for v in self.views.values():
+                v.zero_()
+
+    def zero_stats(self):
+        if self.stat_views is not None:
+            for v in self.stat_views:
+                v.zero_()
 
     def install(self, zero=True):
         """Point every leaf's .grad at its slice (optionally zeroing the buffer first)."""
         if zero:
-            self.flat.zero_()
+            self.zero_grads()
         for k, p in self.params.items():
             p.grad = self.views[k]
 
     @property
     def nbytes(self) -> int:
-        return self.flat.numel() * 4
+        return sum(v.numel() for v in self.views.values()) * 4
+
+    def reduce_scatter(self):
+        """First half of a sharded optimiser step (arena.GaussianArena.sharded_adam_step): the slice of the leaf
+        gradients this rank owns receives the sum over the ranks; the small statistics / side segments are all-reduced
+        (every rank reads them).  Needs a capacity-segmented bucket in peer memory."""
+        if self.peer is None or self._segments is None:
+            raise RuntimeError("GradBucket.reduce_scatter needs peer memory and a capacity (segmented) layout")
+        n = len(self.names)
+        self.peer.reduce_scatter(self._segments[:n])
+        if len(self._segments) > n:
+            self.peer.all_reduce(self._segments[n:])
 
     def all_reduce(self, group=None, async_op=False):
         """Sum the bucket over the ranks: the peer-memory kernel when allocated there, else NCCL/gloo."""
         if self.peer is not None:
-            self.peer.all_reduce()
+            self.peer.all_reduce(self._segments)
             return None
         return dist.all_reduce(self._all, group=group, async_op=async_op)
 
@@ -193,12 +268,16 @@ class WindowTrainer:
         if 8 * n_views <= b.side.numel():
             b.side.zero_()
             return b.side[:8 * n_views].view(n_views, 8), True
-        return torch.zeros(n_views, 8, dtype=torch.float32, device=b.flat.device), False
+        return torch.zeros(n_views, 8, dtype=torch.float32, device=b.device), False
 
     def _finish(self, side, fused, cost_fn, assignment):
         b = self.bucket
-        if self._exchange:
+        if self._exchange and self.exchange == "reduce_scatter":
+            b.reduce_scatter()
+            work = None
+        elif self._exchange:
             work = b.all_reduce(self.group, async_op=True)
+        if self._exchange:
             if not fused:
                 dist.all_reduce(side, group=self.group)
             if work is not None:
@@ -210,13 +289,14 @@ class WindowTrainer:
 
     def __init__(self, params: Dict[str, torch.Tensor], group: Optional[dist.ProcessGroup] = None,
                  sink_names: Optional[Dict[str, str]] = None, peer: bool = False, peer_mode: str = "auto",
-                 densify_stats: bool = False, streams: int = 1, emulate: Optional[tuple] = None):
+                 densify_stats: bool = False, streams: int = 1, emulate: Optional[tuple] = None,
+                 capacity: Optional[int] = None, exchange: str = "allreduce"):
         """`sink_names` (optional): leaf name -> rasterizer gradient name ('means3D', 'sh', 'opacity',
         'scales', 'rotations', ...).  When given, the rasterizer's backward kernel writes / accumulates
         straight into the bucket (rasterizer.grad_sink) instead of autograd allocating per-view
         gradient tensors and adding them; requires that the leaves are passed to the rasterizer
-        unmodified (no activation in between)."""
-        """streams=2 (needs sink_names): a rank's work units run on two CUDA streams, all of them accumulating
+        unmodified (no activation in between).
+        streams=2 (needs sink_names): a rank's work units run on two CUDA streams, all of them accumulating
         into the bucket with reduction atomics -- the small kernels of one unit (scan, sort, per-Gaussian stages) and
         the tail waves of its compositing kernels overlap the other unit's work; inside a CUDA graph the two branches
         are scheduled by the device.  The bucket sum is then order-dependent in the last bit.
@@ -232,24 +312,31 @@ class WindowTrainer:
             if self.distributed:
                 raise RuntimeError("emulate=(rank, world) is for a single, non-distributed process")
             self.rank, self.world = int(emulate[0]), int(emulate[1])
+        self.exchange = exchange      # 'allreduce' | 'reduce_scatter' (leaf gradients only summed on their owner rank)
         self.streams = int(streams) if sink_names is not None else 1
         self._side_stream = None
         # peer=True: bucket in NVLink peer memory, summed by wgs_peer_allreduce (single node, CUDA only)
         self._peer_group = (group if group is not None else dist.group.WORLD) if (peer and self.world > 1) else None
         self._peer_mode = peer_mode
         self._stats = bool(densify_stats)
-        self.bucket = self._make_bucket(params)
+        self.bucket = self._make_bucket(params, capacity)
         self.costs: List[float] = []
 
-    def _make_bucket(self, params):
+    def _make_bucket(self, params, capacity=None):
         P = next(iter(params.values())).shape[0]
-        b = GradBucket(params, self._peer_group, self._peer_mode, self.SIDE_FLOATS, 2 * P if self._stats else 0)
+        b = GradBucket(params, self._peer_group, self._peer_mode, self.SIDE_FLOATS, 2 * P if self._stats else 0,
+                       capacity=capacity)
+        self._bind_stats(b, P)
+        return b
+
+    def _bind_stats(self, b, P):
         if self._stats:
             # window sums of ||dL_dmeans2D[:, :2]|| and of the visibility counts ride in the bucket; the
             # screen-space radius needs a MAX: kept per rank, reduced on demand (reduce_max_radii)
-            self.grad_accum, self.denom = b.stats[:P].view(P, 1), b.stats[P:].view(P, 1)
-            self.max_radii = torch.zeros(P, dtype=torch.float32, device=b.flat.device)
-        return b
+            self.grad_accum, self.denom = b.stat_views[0].view(P, 1), b.stat_views[1].view(P, 1)
+            old = getattr(self, "max_radii", None)
+            if old is None or old.shape[0] != P:
+                self.max_radii = torch.zeros(P, dtype=torch.float32, device=b.device)
 
     def _stats_ctx(self):
         if not self._stats:
@@ -269,12 +356,15 @@ class WindowTrainer:
             for p in self.bucket.params.values():
                 dist.broadcast(p.data, src=src, group=self.group)
 
-    def rebind(self, params: Dict[str, torch.Tensor]):
-        """Call after densify/prune changed the number of Gaussians."""
-        if not self.bucket.matches(params):
-            self.bucket = self._make_bucket(params)
+    def rebind(self, params: Dict[str, torch.Tensor], capacity: Optional[int] = None):
+        """Call after densify/prune changed the number of Gaussians.  A bucket with capacity headroom is re-targeted in
+        place while the new row count fits (no allocation, no peer rendezvous); otherwise a new one is made, with
+        `capacity` rows of headroom when given."""
+        if self.bucket.matches(params):
+            self.bucket.retarget(params)
+            self._bind_stats(self.bucket, next(iter(params.values())).shape[0])
         else:
-            self.bucket.params = params
+            self.bucket = self._make_bucket(params, capacity)
 
     def plan(self, n_views: int, tile_rows: Optional[int] = None, plan: Optional[str] = None) -> List[List[tuple]]:
         """Work units (view, row_begin, row_end) per rank; a whole view is (view, 0, tile_rows) -- or (view, 0, 0) when
@@ -315,12 +405,12 @@ class WindowTrainer:
             for p in b.params.values():
                 p.grad = None
             if two:
-                b.flat.zero_()                       # every unit adds atomically
+                b.zero_grads()                       # every unit adds atomically
         else:
             b.install()
         side, fused = self._side(n_views)  # loss, cost, pose grad (6)
         if self._stats:
-            b.stats.zero_()
+            b.zero_stats()
 
         def run(unit, first):
             v, r0, r1 = unit
@@ -347,7 +437,7 @@ class WindowTrainer:
                 i = 0 if load[0] <= load[1] else 1
                 lanes[i].append(u)
                 load[i] += w(u)
-            dev = b.flat.device
+            dev = b.device
             if self._side_stream is None:
                 self._side_stream = torch.cuda.Stream(dev)
             main = torch.cuda.current_stream(dev)
