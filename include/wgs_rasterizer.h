@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define WGS_ABI_VERSION 10
+#define WGS_ABI_VERSION 11
 
 /* status codes (negative = error) */
 #define WGS_OK 0
@@ -206,6 +206,16 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* args, void* cuda_stream
 int wgs_set_async(WgsContext* ctx, int enable);
 int wgs_last_num_rendered(WgsContext* ctx, int64_t* num_rendered, int64_t* capacity);
 int wgs_overflow_status(WgsContext* ctx, int64_t* overflowed_forwards, int64_t* max_num_rendered, int clear);
+
+/* Chained launches (programmatic dependent launch; no reference counterpart).  The kernels of a forward and of a
+ * backward are launched with cudaLaunchAttributeProgrammaticStreamSerialization: each starts with
+ * griddepcontrol.wait (all data of the preceding kernel visible) and lets the next grid take the SM slots its own last
+ * wave frees, which removes the drain / launch / ramp-up gap between the 5 + 2 kernels of a frame (config 2: 435 ->
+ * 427 us).  The CTAs of the waiting grid hold their registers and shared memory, so when a SECOND stream has work that
+ * could use those slots (window.WindowTrainer with two streams per rank) the switch should be off: measured 5.41 ms
+ * per window step without, 6.00 ms with.  Process-wide; affects launches (and graph captures) made after the call;
+ * returns the previous setting.  Default: on, or the environment's WGS_PDL=0/1. */
+int wgs_set_chained_launch(int enable);
 
 /* Debug counting pass for the roofline report (no reference counterpart): replays the
  * compositing of the forward that `args` describes and returns, in two device u64 words,

@@ -50,7 +50,7 @@ def main():
             "value_at_final_size": recs[-1]["steps_per_s"], "rows_final": recs[-1]["rows"],
             "stages": [{k: r[k] for k in ("step", "rows", "capacity", "ms_per_window_step", "steps_per_s", "densify_ms")} for r in stages],
             "all_steps_ms": [r["ms_per_window_step"] for r in recs], "rows": [r["rows"] for r in recs],
-            "densify_ms": [r["densify_ms"] for r in recs],
+            "densify_ms": [r["densify_ms"] for r in recs], "loss_sums": [r["loss_sum"] for r in recs],
             "capacity_classes_entered": wl.arena.allocations, "bucket_allocations": wl.bucket_allocations,
             "growth_steps": len(recs),
             "config": {"optimizer": "sharded Adam (reduce-scatter, 1/world slice per rank, parameter allgather)" if wl.sharded

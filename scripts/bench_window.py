@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--eager", action="store_true", help="do not capture the rank's step in a CUDA graph")
     ap.add_argument("--emulate", type=int, default=0,
                     help="N: run, one after the other, what each rank of an N-rank job would compute (no exchange)")
+    ap.add_argument("--emulate-rank", type=int, default=-1, help="with --emulate: only this rank (for a profiler run)")
     ap.add_argument("--parity", action="store_true", help="also run the multi-GPU gradient parity check")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -52,7 +53,7 @@ def main():
         from wildgs_slam_blackwell_b200 import scenes
         scene = scenes.make_scene(a.workload)
         per_rank = []
-        for r in range(a.emulate):
+        for r in (range(a.emulate) if a.emulate_rank < 0 else [a.emulate_rank]):
             wl = WindowWorkload(a.workload, dev, peer="off", plan=a.plan, streams=a.streams, use_graph=not a.eager,
                                 sink=not a.no_sink, emulate=(r, a.emulate), scene=scene)
             ms, out = wl.time(a.steps, a.warmup)

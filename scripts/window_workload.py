@@ -5,7 +5,11 @@ One step = every keyframe of the window rendered + back-propagated against the r
 strips sharded over the ranks by WindowTrainer, the backward kernels accumulating straight into the flat gradient
 bucket) + ONE exchange of the bucket (the library's NVLink peer kernel, or NCCL).  STRONG scaling: the window is fixed.
 Per-view semantics follow the reference's mapping loop (src/mapper.py:1083-1093,1170: one keyframe per iteration),
-summed over `window_size` keyframes (configs/wildgs_slam.yaml:34)."""
+summed over `window_size` keyframes (configs/wildgs_slam.yaml:34).  The loss is get_loss_mapping's L1 form
+(slam_utils.py:116-143: alpha mean|rgb - gt| + (1 - alpha) mean|depth - gt_depth| on the valid pixels, alpha = 0.5 as in
+configs/wildgs_slam.yaml:21) through the fused loss kernel; a tile-row strip evaluates it on its rows only (pixel mask),
+so that the strips of a view add up to the view's loss.  loss="fixed": fixed cotangents instead (sum of color * dc +
+depth * dd in torch ops), the form bench.py's headline frame uses."""
 import os
 import sys
 
@@ -16,8 +20,11 @@ if ROOT not in sys.path:
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
+import numpy as np  # noqa: E402
+
 import diff_gaussian_rasterization as dgr  # noqa: E402
-from wildgs_slam_blackwell_b200 import graph, scenes  # noqa: E402
+from wildgs_slam_blackwell_b200 import graph, rasterizer, scenes  # noqa: E402
+from wildgs_slam_blackwell_b200.loss import _PhotometricLoss  # noqa: E402
 from wildgs_slam_blackwell_b200.window import WindowTrainer  # noqa: E402
 
 LEAVES = ("means3D", "sh", "opacities", "scales", "rotations")
@@ -26,7 +33,7 @@ SINK_NAMES = {"means3D": "means3D", "sh": "sh", "opacities": "opacity", "scales"
 
 class WindowWorkload:
     def __init__(self, name, dev, peer="auto", plan="balanced", streams=2, use_graph=True, sink=True, emulate=None,
-                 scene=None):
+                 scene=None, loss="mapping"):
         """peer: 'off' (NCCL) | 'auto' | 'nvls' | 'p2p'; plan: WindowTrainer.plan(); emulate=(rank, world): one process
         runs that rank's share without the exchange; scene: (gaussians, cameras, cotangents) to use instead of `name`."""
         self.name, self.dev = name, dev
@@ -38,13 +45,14 @@ class WindowWorkload:
         t = lambda x: torch.from_numpy(x).to(dev)
         self.params = {k: t(g[k]).requires_grad_(True) for k in LEAVES}
         self.peer = peer if self.world > 1 else "off"
-        self.plan, self.use_graph, self.emulate = plan, use_graph, emulate
+        self.plan, self.use_graph, self.emulate, self.loss = plan, use_graph, emulate, loss
         if use_graph and self.world > 1 and self.peer == "off":
             raise SystemExit("a captured window step needs the peer exchange (an NCCL allreduce is not captured here)")
         self.trainer = WindowTrainer(self.params, sink_names=SINK_NAMES if sink else None, peer=self.peer != "off",
                                      peer_mode=self.peer if self.peer != "off" else "auto", streams=streams, emulate=emulate)
         self.means2D = torch.zeros(self.P, 3, device=dev, requires_grad=True)
         self.views = []
+        rng = np.random.default_rng(20260)
         for cam, cot in zip(cams, cots):
             s = dgr.GaussianRasterizationSettings(
                 image_height=self.H, image_width=self.W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
@@ -52,6 +60,8 @@ class WindowWorkload:
                 projmatrix=t(cam["projmatrix"]), projmatrix_raw=t(cam["projmatrix_raw"]), sh_degree=self.deg,
                 campos=t(cam["campos"]), prefiltered=False, debug=False)
             self.views.append(dict(rast=dgr.GaussianRasterizer(s), dc=t(cot[0]), dd=t(cot[1]),
+                                   gt_color=t(rng.uniform(0.0, 1.0, (3, self.H, self.W)).astype(np.float32)),
+                                   gt_depth=t(rng.uniform(0.5, 6.0, (1, self.H, self.W)).astype(np.float32)), strips={},
                                    theta=torch.zeros(3, device=dev, requires_grad=True),
                                    rho=torch.zeros(3, device=dev, requires_grad=True)))
         self.tile_rows = (self.H + 15) // 16
@@ -65,8 +75,25 @@ class WindowWorkload:
         color, radii, depth, opacity, n_touched = vw["rast"](
             p["means3D"], self.means2D, p["opacities"], shs=p["sh"], scales=p["scales"], rotations=p["rotations"],
             theta=vw["theta"], rho=vw["rho"])
-        loss = (color * vw["dc"]).sum() + (depth * vw["dd"]).sum()
+        if self.loss == "fixed":
+            loss = (color * vw["dc"]).sum() + (depth * vw["dd"]).sum()
+        else:
+            kw = dict(gt_color=vw["gt_color"], gt_depth=vw["gt_depth"], rgb_boundary_threshold=0.01, color_weight=0.5,
+                      depth_weight=0.5)
+            strip = rasterizer.tile_rows.current()
+            if strip is not None:
+                kw.update(self._strip_targets(vw, strip))
+            loss = _PhotometricLoss.apply(color, depth, None, None, kw)
         return loss, (lambda: torch.cat([vw["rho"].grad.reshape(-1), vw["theta"].grad.reshape(-1)]))
+
+    def _strip_targets(self, vw, strip):
+        """pixel mask of the strip's rows (colour term) and the target depth with the other rows invalid (depth term)"""
+        r0, r1 = strip.begin, strip.end
+        if (r0, r1) not in vw["strips"]:
+            m = torch.zeros(1, self.H, self.W, device=self.dev)
+            m[:, 16 * r0:16 * r1] = 1.0
+            vw["strips"][(r0, r1)] = dict(pixel_mask=m, gt_depth=vw["gt_depth"] * m)
+        return vw["strips"][(r0, r1)]
 
     def eager_step(self, plan=None):
         return self.trainer.step(self.n_views, self.render_loss, tile_rows=self.tile_rows,

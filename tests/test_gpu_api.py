@@ -223,7 +223,7 @@ def test_integration_md_stub_drives_the_library():
     from wildgs_slam_blackwell_b200 import _lib
     os.environ["WGS_LIB"] = _lib.LIB_PATH
     ns = {}
-    exec(blocks["# --- wgs-abi-structs (ABI v10; field order of include/wgs_rasterizer.h) ---"], ns)
+    exec([b for k, b in blocks.items() if k.startswith("# --- wgs-abi-structs")][0], ns)
     exec([b for k, b in blocks.items() if k.startswith("# --- wgs-abi-calls")][0], ns)
     g, cams, cots = scenes.make_scene(20000, 200, 136, 1, seed=31)
     cam, cot = cams[0], cots[0]

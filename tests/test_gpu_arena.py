@@ -109,11 +109,13 @@ def test_arena_matches_the_torch_cat_boolean_index_procedure():
             ref.step(step_no)
         torch.cuda.synchronize()
         for k in arena.names:
-            torch.testing.assert_close(arena.params[k].detach(), ref.p[k].detach(), rtol=2e-6, atol=1e-7, msg=f"{k} at stage {s}")
+            torch.testing.assert_close(arena.params[k].detach(), ref.p[k].detach(), rtol=2e-6, atol=2e-7, msg=f"{k} at stage {s}")
             m, v = arena.moments(k)
             st = ref.opt.state[ref.p[k]]
-            torch.testing.assert_close(m, st["exp_avg"], rtol=2e-6, atol=1e-9)
-            torch.testing.assert_close(v, st["exp_avg_sq"], rtol=2e-6, atol=1e-12)
+            # torch's Adam forms m with lerp (m + (g - m)(1 - b1)), the kernel with b1 m + (1 - b1) g: a few ulp OF THE
+            # TERMS apart (|g| ~ 1 here), which is a large relative error where they cancel -> absolute tolerance
+            torch.testing.assert_close(m, st["exp_avg"], rtol=1e-5, atol=2e-6)
+            torch.testing.assert_close(v, st["exp_avg_sq"], rtol=1e-5, atol=1e-8)
         torch.testing.assert_close(arena.xyz_gradient_accum.reshape(-1), ref.stats["xyz_gradient_accum"])
     assert arena.allocations == 3 and ptr_changes == 2 and arena.capacity == 65536      # 16384 -> 32768 -> 65536
 
@@ -126,7 +128,11 @@ def test_config5_workload_small():
     recs = wl.run(reps=2)
     assert [r["rows"] for r in recs] == wl.sched and recs[-1]["rows"] == 40_000
     assert all(np.isfinite(r["loss_sum"]) and r["ms_per_window_step"] > 0 for r in recs)
-    assert recs[-1]["loss_sum"] < recs[0]["loss_sum"]                  # Adam on the arena does reduce the loss
+    first = float(wl.step().sum())                                     # at a fixed row count Adam on the arena reduces the loss
+    for _ in range(30):
+        last = float(wl.step().sum())
+    wl.check()
+    assert last < first
     assert wl.arena.allocations == 3 and wl.bucket_allocations == 3    # 16384, 32768, 65536: no allocation per densification
     p = wl.arena.params
     assert all(bool(torch.isfinite(t).all()) for t in p.values())

@@ -4,8 +4,9 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libwgs_rasterizer.so")
-ABI_VERSION = 10
+# WGS_RASTERIZER_LIB: load another build of the same ABI (kernel A/B runs: scripts/build_variant.py)
+LIB_PATH = os.environ.get("WGS_RASTERIZER_LIB") or os.path.join(_HERE, "libwgs_rasterizer.so")
+ABI_VERSION = 11
 
 WGS_OK = 0
 WGS_ERR_INVALID_ARGUMENT = -1
@@ -65,7 +66,7 @@ class BackwardArgs(_SizedStructure):
 EXPORTS = ("wgs_abi_version", "wgs_last_error", "wgs_context_create", "wgs_context_destroy",
            "wgs_workspace_sizes", "wgs_forward", "wgs_backward", "wgs_mark_visible", "wgs_export_binning",
            "wgs_export_geometry", "wgs_stage_timing", "wgs_stage_times", "wgs_camera_matrices", "wgs_set_async",
-           "wgs_last_num_rendered", "wgs_overflow_status", "wgs_count_pairs", "wgs_peer_flags_bytes",
+           "wgs_last_num_rendered", "wgs_set_chained_launch", "wgs_overflow_status", "wgs_count_pairs", "wgs_peer_flags_bytes",
            "wgs_peer_allreduce", "wgs_peer_exchange")
 NUM_STAGES = 8
 STAGE_NAMES = ("preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd", "render_bwd", "preprocess_bwd",
@@ -103,6 +104,7 @@ def load():
     lib.wgs_peer_exchange.argtypes = [C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_uint64, C.c_int32, C.c_int32,
                                       C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int32, C.c_int32, C.c_void_p]
     lib.wgs_set_async.argtypes = [C.c_void_p, C.c_int]
+    lib.wgs_set_chained_launch.argtypes = [C.c_int]
     lib.wgs_last_num_rendered.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.wgs_overflow_status.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_int]
     lib.wgs_count_pairs.argtypes = [C.POINTER(ForwardArgs), _fp, C.c_void_p]

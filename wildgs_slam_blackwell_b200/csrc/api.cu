@@ -2,6 +2,8 @@
 // carving and stage sequencing.  Replaces RasterizeGaussiansCUDA / RasterizeGaussiansBackwardCUDA
 // (rasterize_points.cu:35-211) and CudaRasterizer::Rasterizer::{forward,backward,markVisible}
 // (rasterizer_impl.cu:141-455).
+#include <atomic>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -26,6 +28,22 @@ struct WgsContext {
     bool fwd_timed = false, bwd_timed = false;
     cudaEvent_t ev_stage[9] = {};
 };
+
+namespace wgs {
+// -1: not yet read from the environment (WGS_PDL=0 turns the chained launches off for the process)
+static std::atomic<int> g_chained{-1};
+bool pdl_enabled() {
+    int v = g_chained.load(std::memory_order_relaxed);
+    if (v < 0) {
+        const char* e = getenv("WGS_PDL");
+        v = (e && e[0] == '0') ? 0 : 1;
+        int expected = -1;
+        g_chained.compare_exchange_strong(expected, v);
+        v = g_chained.load(std::memory_order_relaxed);
+    }
+    return v != 0;
+}
+}  // namespace wgs
 
 namespace {
 thread_local char g_err[512] = "";
@@ -325,6 +343,12 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     MARK(ctx, 8, s);
     ctx->bwd_timed = ctx->timing && !capturing;
     return WGS_OK;
+}
+
+int wgs_set_chained_launch(int enable) {
+    const int before = wgs::pdl_enabled() ? 1 : 0;
+    wgs::g_chained.store(enable ? 1 : 0, std::memory_order_relaxed);
+    return before;
 }
 
 int wgs_set_async(WgsContext* ctx, int enable) {

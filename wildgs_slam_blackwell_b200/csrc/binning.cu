@@ -42,6 +42,8 @@ __device__ __forceinline__ void publish_total(const BinParams& p, uint32_t total
 // K = number of privatised histogram copies (compile-time so that all K loads are in flight at once)
 template <int K>
 __global__ void __launch_bounds__(1024) tile_scan_kernel(const __grid_constant__ BinParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     __shared__ uint32_t warp_sums[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint32_t carry = 0;
@@ -103,6 +105,8 @@ constexpr int ORDER_CLASSES = 256;
 template <int K>
 __global__ void __cluster_dims__(SCAN_CLUSTER, 1, 1) __launch_bounds__(1024)
     tile_scan_cluster_kernel(const __grid_constant__ BinParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t s_total;
     __shared__ uint32_t cls_hist[ORDER_CLASSES];  // tiles of this CTA per class
@@ -195,6 +199,8 @@ __global__ void __cluster_dims__(SCAN_CLUSTER, 1, 1) __launch_bounds__(1024)
 
 // duplicateWithKeys (rasterizer_impl.cu:70-111), tile digit already consumed
 __global__ void __launch_bounds__(256) scatter_kernel(const __grid_constant__ BinParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     const int idx = blockIdx.x * 256 + threadIdx.x;
     const int lane = threadIdx.x & 31;
     uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
@@ -284,6 +290,8 @@ constexpr int BUCKET_LIMIT = 32;
 constexpr int EPT = SMALL_MAX / SMALL_THREADS;  // entries per thread
 
 __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __grid_constant__ BinParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     __shared__ unsigned long long out[SMALL_MAX];
     __shared__ uint32_t hist[NB];
     __shared__ uint32_t wsum[SMALL_THREADS / 32];
@@ -386,6 +394,8 @@ __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __
 }
 
 __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __grid_constant__ BinParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     extern __shared__ unsigned long long lkeys[];
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int n_large = (int)p.tile.misc[MISC_N_LARGE];
@@ -445,32 +455,32 @@ __global__ void export_geometry_kernel(int P, GeomView g, const int* radii, floa
 void launch_tile_scan(const BinParams& p, cudaStream_t s) {
     if (p.tiles <= SCAN_CLUSTER * 1024) {
         switch (p.copies) {
-            case 32: tile_scan_cluster_kernel<32><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
-            case 16: tile_scan_cluster_kernel<16><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
-            case 8: tile_scan_cluster_kernel<8><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
-            case 4: tile_scan_cluster_kernel<4><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
-            case 2: tile_scan_cluster_kernel<2><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
-            default: tile_scan_cluster_kernel<1><<<SCAN_CLUSTER, 1024, 0, s>>>(p); break;
+            case 32: launch_chained(tile_scan_cluster_kernel<32>, SCAN_CLUSTER, 1024, 0, s, p); break;
+            case 16: launch_chained(tile_scan_cluster_kernel<16>, SCAN_CLUSTER, 1024, 0, s, p); break;
+            case 8: launch_chained(tile_scan_cluster_kernel<8>, SCAN_CLUSTER, 1024, 0, s, p); break;
+            case 4: launch_chained(tile_scan_cluster_kernel<4>, SCAN_CLUSTER, 1024, 0, s, p); break;
+            case 2: launch_chained(tile_scan_cluster_kernel<2>, SCAN_CLUSTER, 1024, 0, s, p); break;
+            default: launch_chained(tile_scan_cluster_kernel<1>, SCAN_CLUSTER, 1024, 0, s, p); break;
         }
         return;
     }
     switch (p.copies) {
-        case 32: tile_scan_kernel<32><<<1, 1024, 0, s>>>(p); break;
-        case 16: tile_scan_kernel<16><<<1, 1024, 0, s>>>(p); break;
-        case 8: tile_scan_kernel<8><<<1, 1024, 0, s>>>(p); break;
-        case 4: tile_scan_kernel<4><<<1, 1024, 0, s>>>(p); break;
-        case 2: tile_scan_kernel<2><<<1, 1024, 0, s>>>(p); break;
-        default: tile_scan_kernel<1><<<1, 1024, 0, s>>>(p); break;
+        case 32: launch_chained(tile_scan_kernel<32>, 1, 1024, 0, s, p); break;
+        case 16: launch_chained(tile_scan_kernel<16>, 1, 1024, 0, s, p); break;
+        case 8: launch_chained(tile_scan_kernel<8>, 1, 1024, 0, s, p); break;
+        case 4: launch_chained(tile_scan_kernel<4>, 1, 1024, 0, s, p); break;
+        case 2: launch_chained(tile_scan_kernel<2>, 1, 1024, 0, s, p); break;
+        default: launch_chained(tile_scan_kernel<1>, 1, 1024, 0, s, p); break;
     }
 }
 
 void launch_scatter(const BinParams& p, cudaStream_t s) {
-    if (p.P > 0) scatter_kernel<<<(p.P + 255) / 256, 256, 0, s>>>(p);
+    if (p.P > 0) launch_chained(scatter_kernel, (p.P + 255) / 256, 256, 0, s, p);
 }
 
 void launch_tile_sorts(const BinParams& p, int num_sms, cudaStream_t s) {
-    tile_sort_small_kernel<<<p.tiles, SMALL_THREADS, 0, s>>>(p);
-    tile_sort_large_kernel<<<num_sms, LARGE_THREADS, LARGE_MAX * 8, s>>>(p);
+    launch_chained(tile_sort_small_kernel, p.tiles, SMALL_THREADS, 0, s, p);
+    launch_chained(tile_sort_large_kernel, num_sms, LARGE_THREADS, LARGE_MAX * 8, s, p);
 }
 
 void launch_export_binning(const BinParams& p, const ImageView& image, int W, int H, unsigned long long* keys,

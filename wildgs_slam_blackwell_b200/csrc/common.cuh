@@ -37,6 +37,38 @@
 
 namespace wgs {
 
+// ---- programmatic dependent launch (PDL) -------------------------------------------------------------------------
+// The kernels of one forward / backward follow each other on one stream and each needs the previous one's output, so
+// between two of them the GPU drains, the next grid is launched and its CTAs ramp up: 2-4 us per boundary, a tenth of
+// a 0.43 ms frame.  With PDL the next grid is launched while the previous one is still running: a kernel of the chain
+//   * starts with pdl_wait() -- griddepcontrol.wait: returns once the preceding kernel has completed and its writes
+//     are visible -- as its FIRST statement, before any early return (a grid whose CTAs all left without waiting would
+//     "complete" before its predecessor, and the kernel after it would no longer be ordered behind that one),
+//   * then calls pdl_trigger() -- griddepcontrol.launch_dependents: once every CTA of this grid has executed it (i.e.
+//     the last wave is resident), the next kernel's CTAs may take the SM slots that free up and sit in their wait.
+// Nothing is read or written before the wait, so the ordering of the data is that of a plain stream.  Launched without
+// the attribute (WGS_PDL=0, or a stream of a library that does not know PDL) both instructions are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // api.cu: environment WGS_PDL (default on)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chained(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                  Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 enum MiscSlot : int {
     MISC_NUM_RENDERED = 0,   // R: total (Gaussian,tile) instances of this forward
     MISC_OVERFLOW = 1,       // set if R > capacity

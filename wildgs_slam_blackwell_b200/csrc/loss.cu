@@ -41,6 +41,8 @@ __device__ __forceinline__ void st4(float* p, size_t i, size_t N, float4 v) {
 }
 
 __global__ void __launch_bounds__(LOSS_THREADS) photometric_loss_kernel(const __grid_constant__ LossParams p) {
+    pdl_wait();     // first statement: see common.cuh (the loss sits between render_fwd and render_bwd)
+    pdl_trigger();
     const WgsLossArgs& a = p.a;
     const size_t N = p.N;
     const size_t i0 = ((size_t)blockIdx.x * LOSS_THREADS + threadIdx.x) * LOSS_PIX_PER_THREAD;
@@ -215,7 +217,7 @@ int wgs_photometric_loss(const WgsLossArgs* a, void* cuda_stream) {
     p.blocks = loss_blocks(p.N);
     p.ticket = (unsigned int*)a->workspace;
     p.partials = (double*)((char*)a->workspace + 256);
-    photometric_loss_kernel<<<p.blocks, LOSS_THREADS, 0, (cudaStream_t)cuda_stream>>>(p);
+    wgs::launch_chained(photometric_loss_kernel, p.blocks, LOSS_THREADS, 0, (cudaStream_t)cuda_stream, p);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         wgs_set_error_message(cudaGetErrorString(e));

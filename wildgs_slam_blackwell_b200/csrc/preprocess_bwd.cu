@@ -61,14 +61,24 @@ __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const 
 // row access to global memory (192-B stride) moved 1.9 GB for 1.2 GB of algorithmic traffic at config 4.
 template <bool STAGED>
 __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     extern __shared__ float sh_stage[];
-    const int gidx = blockIdx.x * WGS_PRE_BWD_THREADS + threadIdx.x;
     const int accm = p.accumulate;
+    __shared__ float s_part[WGS_PRE_BWD_THREADS / 32][6];   // pose partials of the block's warps, summed over its chunks
+    if ((threadIdx.x & 31) < 6) s_part[threadIdx.x >> 5][threadIdx.x & 31] = 0.f;   // (each warp only touches its own row)
+    // A block walks chunks of WGS_PRE_BWD_THREADS Gaussians, chunk = blockIdx.x, + gridDim.x, ... (the grid is sized to
+    // the SMs, launch_preprocess_bwd): the block-level epilogue -- pose partials, fence, the ticket atomic, ~3 us of
+    // latency during which the block only holds its registers -- is paid once per block instead of once per 256
+    // Gaussians (3 907 times at 1 M: it was what kept a quarter-image strip at 80 us of the whole view's 96).
+    const int nchunks = (p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS;
+    for (int chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+    const int gidx = chunk * WGS_PRE_BWD_THREADS + threadIdx.x;
     float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     // staged SH rows of this warp: packed (P,M,3) rows, or the (P,M-1,3) rest rows in raw-parameter mode
     const int sh_rw = STAGED ? (p.sh_rest ? 3 * (p.M - 1) : 3 * p.M) : 1;
     const int sh_rs = sh_row_stride(sh_rw);
-    const int wrow0 = blockIdx.x * WGS_PRE_BWD_THREADS + (threadIdx.x & ~31);  // first Gaussian of the warp
+    const int wrow0 = chunk * WGS_PRE_BWD_THREADS + (threadIdx.x & ~31);  // first Gaussian of the warp
     float* const wstage = sh_stage + (threadIdx.x & ~31) * sh_rs;
     unsigned vmask = 0;
     // Which Gaussian this thread works on.  STAGED: its own (the SH rows of a warp must stay one contiguous span);
@@ -135,7 +145,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
         work = (int)threadIdx.x < total;
         live = work;
         if (work) {
-            idx = blockIdx.x * WGS_PRE_BWD_THREADS + (int)s_list[threadIdx.x];
+            idx = chunk * WGS_PRE_BWD_THREADS + (int)s_list[threadIdx.x];
             // (radii / rect of the adopted Gaussian: both answered "visible")
             rad = __ldg(p.radii + idx);
             rect = __ldg(p.geom.rect + idx);
@@ -453,20 +463,23 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
         float* dst = p.sh_rest ? p.dL_dsh_rest : p.dL_dsh;
         if (dst && wrow0 < p.P)
             sh_stage_store(wstage, dst + (size_t)wrow0 * sh_rw, vmask, (uint32_t)min(32, p.P - wrow0), sh_rw, sh_rs, accm);
+        __syncwarp();   // the warp's stage is refilled by its next chunk
     }
-    // ---- pose gradient: warp -> block -> grid, deterministic ----
-    __shared__ float s_part[WGS_PRE_BWD_THREADS / 32][6];
-    __shared__ bool s_last;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // pose gradient of the chunk: lanes -> the warp's running partial (kept in shared memory, not in six registers
+    // that would stay live across the next chunk)
 #pragma unroll
     for (int i = 0; i < 6; i++) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) tau[i] += __shfl_xor_sync(0xffffffffu, tau[i], o);
     }
-    if (lane == 0) {
+    if ((threadIdx.x & 31) == 0) {
 #pragma unroll
-        for (int i = 0; i < 6; i++) s_part[warp][i] = tau[i];
+        for (int i = 0; i < 6; i++) s_part[threadIdx.x >> 5][i] += tau[i];
     }
+    }   // chunk loop
+    // ---- pose gradient: warp (over its chunks) -> block -> grid, deterministic for a given grid ----
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __syncthreads();
     if (threadIdx.x < 6) {
         float s = 0.f;
@@ -501,11 +514,20 @@ static_assert(WGS_PRE_BWD_THREADS >= 6 * 32, "the last block sums the six pose c
 
 void launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
     if (p.P <= 0) return;
-    const int blocks = (p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS;
+    // every resident slot gets one block (768 / WGS_PRE_BWD_THREADS per SM, __launch_bounds__), twice over so that the
+    // hardware scheduler can even out blocks whose chunks hold few visible Gaussians
+    static int slots = 0;
+    if (!slots) {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        slots = sms * (768 / WGS_PRE_BWD_THREADS) * 2;
+    }
+    const int blocks = min((p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS, slots);
     if (p.sh && p.M > 1 && p.M <= SH_STAGE_MAX_M)
-        preprocess_bwd_kernel<true><<<blocks, WGS_PRE_BWD_THREADS, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M, WGS_PRE_BWD_THREADS), s>>>(p);
+        launch_chained(preprocess_bwd_kernel<true>, blocks, WGS_PRE_BWD_THREADS, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M, WGS_PRE_BWD_THREADS), s, p);
     else
-        preprocess_bwd_kernel<false><<<blocks, WGS_PRE_BWD_THREADS, 0, s>>>(p);
+        launch_chained(preprocess_bwd_kernel<false>, blocks, WGS_PRE_BWD_THREADS, 0, s, p);
 }
 
 }  // namespace wgs

@@ -117,6 +117,8 @@ __device__ __forceinline__ float3 sh_to_rgb(const float* __restrict__ sh, const 
 // thread reads its row from there; per-thread row reads (192-B stride at M = 16) reached only 2.9 TB/s at config 4.
 template <bool STAGED>
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const __grid_constant__ PreFwdParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     extern __shared__ float sh_stage[];
     const int idx = blockIdx.x * 256 + threadIdx.x;
     const int lane = threadIdx.x & 31;
@@ -273,9 +275,9 @@ int configure_preprocess_fwd() {
 void launch_preprocess_fwd(const PreFwdParams& p, cudaStream_t s) {
     if (p.P <= 0) return;
     if (p.sh && !p.colors_precomp && p.M > 1 && p.M <= SH_STAGE_MAX_M)
-        preprocess_fwd_kernel<true><<<(p.P + 255) / 256, 256, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M, 256), s>>>(p);
+        launch_chained(preprocess_fwd_kernel<true>, (p.P + 255) / 256, 256, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M, 256), s, p);
     else
-        preprocess_fwd_kernel<false><<<(p.P + 255) / 256, 256, 0, s>>>(p);
+        launch_chained(preprocess_fwd_kernel<false>, (p.P + 255) / 256, 256, 0, s, p);
 }
 void launch_mark_visible(int P, const float* means3D, const float* V, uint8_t* present, cudaStream_t s) {
     if (P > 0) mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, V, present);

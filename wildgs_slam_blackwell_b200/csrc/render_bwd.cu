@@ -53,8 +53,11 @@ struct __align__(16) WarpRed {
 struct __align__(16) BwdSmem {
     BwdStage st[2];
     WarpRed red[8];
+    float4 list[8][32];  // per warp: the survivors of the current chunk {gaussian id (bits), mean2D - warp origin, slot (bits)}
     uint32_t hi;
 };
+// four CTAs per SM (the register budget at 64 registers x 256 threads): 228 KB of shared memory, 1 KB reserved per CTA
+static_assert(sizeof(BwdSmem) + 1024 <= 233472 / 4, "BwdSmem no longer fits four CTAs per SM");
 
 __device__ __forceinline__ float rcp_approx(float x) {
     float r;
@@ -152,6 +155,8 @@ __device__ __forceinline__ void flush_pending(const WarpRed& wr, unsigned lm_add
 }
 
 __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constant__ RenderBwdParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
     if (p.tile.misc[MISC_OVERFLOW]) return;
@@ -195,6 +200,7 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
     float* __restrict__ acc = (float*)p.grad.acc;
 
     WarpRed& wr = sm.red[warp];
+    float4* __restrict__ wl = sm.list[warp];
     // ---- constant B fragments of this warp (b0: k = t, b1: k = t + 4 of k-step s; column n = q) ----
     unsigned bw[4][2], bc[4][2];
     {
@@ -228,7 +234,7 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
     unsigned wcol, wcst;  // shared addresses of this lane's column in the w plane / of cst[0] (32-bit registers)
     asm volatile("mov.u32 %0, %1;" : "=r"(wcol) : "r"((unsigned)__cvta_generic_to_shared(&wr.w[0][lane])));
     asm volatile("mov.u32 %0, %1;" : "=r"(wcst) : "r"((unsigned)__cvta_generic_to_shared(&wr.cst[0])));
-    int pending = 0;
+    unsigned ca = wcol, cs = wcst;  // where the next pending row goes
 
     // round r holds list entries k = hi - (r+1)*BB + slot, slot in [0, BB)
     const int slot = tid & (BB - 1);
@@ -257,67 +263,72 @@ __global__ void __launch_bounds__(256, 4) render_bwd_kernel(const __grid_constan
             const int mine = c0 + lane;
             const int kmine = base + mine;
             bool hit = false;
+            float ex = 0.f, ey = 0.f;
             if (kmine >= 0 && kmine < warp_last) {
                 const float4 a = s.rec0[mine];
                 const float4 b = s.rec1[mine];
                 hit = reaches_rect(a.x, a.y, a.z, a.w, b.x, b.w, rx0, ry0, rx1, ry1);
+                ex = a.x - rx0;
+                ey = a.y - ry0;
             }
-            unsigned m = __ballot_sync(0xffffffffu, hit);
-            while (m) {
-                const int bit = 31 - __clz(m);
-                m &= ~(1u << bit);
-                const int j = c0 + bit;
-                const int k = base + j;
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (m == 0) continue;
+            // compact the survivors, last list entry first (back to front): the walk below reads slots 0..n-1 at
+            // warp-uniform addresses instead of decoding the bit mask once per entry
+            if (hit) wl[__popc(m & (0xfffffffeu << lane))] = make_float4(__uint_as_float(s.id[mine]), ex, ey, __int_as_float(mine));
+            __syncwarp();
+            const int n = __popc(m);
+#pragma unroll 2
+            for (int q = 0; q < n; q++) {
+                const float4 e = wl[q];
+                const int j = __float_as_int(e.w);
                 const float4 a = s.rec0[j];
                 const float4 b = s.rec1[j];
+                const float dx = a.x - pixx, dy = a.y - pixy;
+                // same expression as the forward so that skip decisions agree
+                const float power = FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
+                const float G = ex2_approx(power * 1.4426950408889634f);
+                const float alpha = fminf(b.y * G, 0.99f);
+                // backward.cu:685-706: behind this pixel's last contributor, power > 0, alpha < 1/255 -> no contribution
+                const bool active = (base + j < last_contributor) & !(power > 0.f) & !(alpha < 1.0f / 255.0f);
                 float w = 0.f, c = 0.f;
-                bool active = false;
-                if (k < last_contributor) {
-                    const float dx = a.x - pixx, dy = a.y - pixy;
-                    // same expression as the forward so that skip decisions agree
-                    const float power = FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
-                    if (!(power > 0.f)) {
-                        const float G = ex2_approx(power * 1.4426950408889634f);
-                        const float alpha = fminf(b.y * G, 0.99f);
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            active = true;
-                            const float4 col = s.col[j];
-                            const float inv = rcp_approx(1.f - alpha);
-                            T *= inv;
-                            const float x = fmaf(col.x, dpx, fmaf(col.y, dpy, fmaf(col.z, dpz, b.z * dpd)));
-                            A = fmaf(last_alpha, last_x - A, A);
-                            last_x = x;
-                            last_alpha = alpha;
-                            const float dLa = fmaf(-tfbg, inv, (x - A) * T);  // dL/dalpha
-                            c = alpha * T;
-                            w = G * dLa;
-                        }
-                    }
+                if (active) {
+                    const float4 col = s.col[j];
+                    const float inv = rcp_approx(1.f - alpha);
+                    T *= inv;
+                    const float x = fmaf(col.x, dpx, fmaf(col.y, dpy, fmaf(col.z, dpz, b.z * dpd)));
+                    A = fmaf(last_alpha, last_x - A, A);
+                    last_x = x;
+                    last_alpha = alpha;
+                    const float dLa = fmaf(-tfbg, inv, (x - A) * T);  // dL/dalpha
+                    c = alpha * T;
+                    w = G * dLa;
                 }
                 if (__any_sync(0xffffffffu, active)) {
-                    const unsigned ca = wcol + pending * (VP * 4);
+                    // row `pending` of the w / c planes and of cst (every lane stores the same cst record: one
+                    // address, no lane predicate to keep)
                     asm volatile("st.shared.f32 [%0], %1;\n\tst.shared.f32 [%0+%3], %2;\n" ::"r"(ca), "f"(w), "f"(c),
                                  "n"(MG * VP * 4) : "memory");
-                    {
-                        const float gid = __uint_as_float(s.id[j]), ex = a.x - rx0, ey = a.y - ry0;
-                        if (lane == 0)
-                            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %3};\n" ::"r"(wcst + pending * 16), "f"(gid),
-                                         "f"(ex), "f"(ey) : "memory");
-                    }
-                    if (++pending == MG) {
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %3};\n" ::"r"(cs), "f"(e.x), "f"(e.y), "f"(e.z)
+                                 : "memory");
+                    ca += VP * 4;
+                    cs += 16;
+                    if (cs == wcst + MG * 16) {
                         flush_pending(wr, lm_addr, MG, lane, bw, bc, acc);
-                        pending = 0;
+                        ca = wcol;
+                        cs = wcst;
                     }
                 }
             }
+            __syncwarp();  // the list is rewritten by the next chunk
         }
     }
-    if (pending) flush_pending(wr, lm_addr, pending, lane, bw, bc, acc);
+    if (cs != wcst) flush_pending(wr, lm_addr, (int)(cs - wcst) >> 4, lane, bw, bc, acc);
     cp_async_wait<0>();
 }
 
 void launch_render_bwd(const RenderBwdParams& p, cudaStream_t s) {
-    render_bwd_kernel<<<p.gx * p.gy, 256, sizeof(BwdSmem), s>>>(p);
+    launch_chained(render_bwd_kernel, p.gx * p.gy, 256, sizeof(BwdSmem), s, p);
 }
 
 int configure_render_bwd() {

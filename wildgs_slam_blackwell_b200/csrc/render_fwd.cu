@@ -13,50 +13,60 @@
 
 namespace wgs {
 
-// Walk the survivors (bit mask m) of one 32-entry chunk front to back for this lane's pixel.
-// The arithmetic is the reference's rn-sequence (forward.cu:336-380).
+// The survivors of one 32-entry chunk, compacted by the warp that culled them: each hit lane already holds its
+// Gaussian's two records in registers and writes them to slot popc(hits below it); the walk then reads slots
+// 0..n-1 with warp-uniform addresses (LDS broadcast, immediate offsets once unrolled) instead of decoding a bit mask
+// per entry.  b.w (ln(255 opacity), only needed by the cull) is replaced by the entry's index in the stage.
+struct __align__(16) WarpList {
+    float4 a[32];
+    float4 b[32];
+};
+
+// Walk the n compacted survivors front to back for this lane's pixel.  The arithmetic is the reference's
+// rn-sequence (forward.cu:336-380).  A pixel that is done (the reference's `done` flag: its transmittance test
+// failed once, or it lies outside the image) carries T with the sign bit set -- T > 0 while it is live -- so the loop
+// has no separate flag and no divergent early-outs: the three conditions become one predicate around the blend.
 template <bool TOUCH>
-__device__ __forceinline__ void walk_survivors(const FwdStage& s, unsigned m, int c0, int round_base, float pixx,
+__device__ __forceinline__ void walk_survivors(const FwdStage& s, const WarpList& wl, int n, int lc_base, float pixx,
                                                float pixy, float& T, float& C0, float& C1, float& C2, float& D,
-                                               uint32_t& last_contributor, bool& done, int lane,
-                                               int* __restrict__ n_touched) {
-    while (m) {
-        const int j = c0 + __ffs(m) - 1;
-        m &= m - 1;
-        const float4 a = s.rec0[j];
-        const float4 b = s.rec1[j];
+                                               uint32_t& last_contributor, int lane, int* __restrict__ n_touched) {
+#pragma unroll 2
+    for (int k = 0; k < n; k++) {
+        const float4 a = wl.a[k];
+        const float4 b = wl.b[k];
+        const float dx = SUB(a.x, pixx), dy = SUB(a.y, pixy);
+        const float power = FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
+        const float alpha = fminf(MUL(b.y, expf(power)), 0.99f);
+        const float test_T = MUL(T, SUB(1.f, alpha));
+        // forward.cu:345-372: skip if power > 0, skip if alpha < 1/255, stop if T (1 - alpha) < 1e-4.  A done pixel
+        // has T < 0, so its test_T is <= 0: it "stops" again (idempotent) and never blends.
+        const bool valid = !(power > 0.f) & !(alpha < 1.0f / 255.0f);
+        const bool stop = test_T < 0.0001f;
+        if (valid & stop) T = -fabsf(T);
         bool touched = false;
-        if (!done) {
-            const float dx = SUB(a.x, pixx), dy = SUB(a.y, pixy);
-            const float power = FMA(FMA(dx, MUL(dx, a.z), MUL(dy, MUL(dy, b.x))), -0.5f, -MUL(dy, MUL(dx, a.w)));
-            if (!(power > 0.f)) {
-                const float alpha = fminf(MUL(b.y, expf(power)), 0.99f);
-                if (!(alpha < 1.0f / 255.0f)) {
-                    const float test_T = MUL(T, SUB(1.f, alpha));
-                    if (test_T < 0.0001f) {
-                        done = true;
-                    } else {
-                        const float4 col = s.col[j];
-                        C0 = FMA(T, MUL(alpha, col.x), C0);
-                        C1 = FMA(T, MUL(alpha, col.y), C1);
-                        C2 = FMA(T, MUL(alpha, col.z), C2);
-                        D = FMA(T, MUL(alpha, b.z), D);
-                        if (TOUCH) touched = test_T > 0.5f;
-                        T = test_T;
-                        last_contributor = (uint32_t)(round_base + j + 1);
-                    }
-                }
-            }
+        if (valid & !stop) {
+            const int j = __float_as_int(b.w);
+            const float4 col = s.col[j];
+            C0 = FMA(T, MUL(alpha, col.x), C0);
+            C1 = FMA(T, MUL(alpha, col.y), C1);
+            C2 = FMA(T, MUL(alpha, col.z), C2);
+            D = FMA(T, MUL(alpha, b.z), D);
+            if (TOUCH) touched = test_T > 0.5f;
+            T = test_T;
+            last_contributor = (uint32_t)(lc_base + j);
         }
         if (TOUCH) {
             const unsigned tm = __ballot_sync(0xffffffffu, touched);
-            if (tm && lane == 0) atomicAdd(n_touched + s.id[j], __popc(tm));
+            if (tm && lane == 0) atomicAdd(n_touched + s.id[__float_as_int(b.w)], __popc(tm));
         }
     }
 }
 
 __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__ RenderFwdParams p) {
+    pdl_wait();     // first statement: see common.cuh
+    pdl_trigger();
     __shared__ FwdStage st[2];
+    __shared__ WarpList lists[8];
     // R exceeded the instance capacity (only reachable in no-wait / graph mode, where no host is there to grow the
     // buffer and retry): every tile composites an EMPTY list, i.e. background colour, zero depth / opacity and
     // n_contrib = 0, so a missed overflow check never hands uninitialised memory to a loss or an optimiser (the
@@ -82,9 +92,10 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
     const int rounds = (total + BATCH - 1) / BATCH;
     const unsigned long long* __restrict__ list = p.bucket + range.x;
 
-    float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
+    float T = inside ? 1.f : -1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
     uint32_t last_contributor = 0;
-    bool done = !inside;
+    WarpList& wl = lists[warp];
+    const unsigned lt_mask = (1u << lane) - 1u;
 
     // prologue: ids of batch 0 -> issue gathers; prefetch ids of batch 1
     uint32_t id_next = 0;
@@ -103,7 +114,7 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
         const int count = min(BATCH, total - r * BATCH);
         cp_async_wait<0>();
         // all threads done with buffer buf^1 (read in round r-1) and batch r visible
-        if (__syncthreads_and(done)) break;
+        if (__syncthreads_and(T < 0.f)) break;
         if (r + 1 < rounds) {
             const int k = (r + 1) * BATCH + tid;
             if (k < total) {
@@ -116,30 +127,41 @@ __global__ void __launch_bounds__(256) render_fwd_kernel(const __grid_constant__
             if (k + BATCH < total) id_next = (uint32_t)list[k + BATCH];
         }
         cp_async_commit();
-        if (!warp_in_image || __all_sync(0xffffffffu, done)) continue;
+        if (!warp_in_image || __all_sync(0xffffffffu, T < 0.f)) continue;
 
         const FwdStage& s = st[buf];
         for (int c0 = 0; c0 < count; c0 += 32) {
             const int mine = c0 + lane;
             bool hit = false;
+            float4 a, b;
             if (mine < count) {
-                const float4 a = s.rec0[mine];
-                const float4 b = s.rec1[mine];
+                a = s.rec0[mine];
+                b = s.rec1[mine];
                 hit = reaches_rect(a.x, a.y, a.z, a.w, b.x, b.w, rx0, ry0, rx1, ry1);
             }
-            unsigned m = __ballot_sync(0xffffffffu, hit);
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (m == 0) continue;
+            if (hit) {
+                const int slot = __popc(m & lt_mask);
+                b.w = __int_as_float(mine);
+                wl.a[slot] = a;
+                wl.b[slot] = b;
+            }
+            __syncwarp();
             // T only decreases: once no pixel of the warp has T > 0.5, n_touched cannot change any more
             // (forward.cu:369-371 needs test_T > 0.5), and the cheaper loop without its vote is used.
-            if (__any_sync(0xffffffffu, !done && T > 0.5f))
-                walk_survivors<true>(s, m, c0, r * BATCH, pixx, pixy, T, C0, C1, C2, D, last_contributor, done, lane,
-                                     p.n_touched);
+            if (__any_sync(0xffffffffu, T > 0.5f))
+                walk_survivors<true>(s, wl, __popc(m), r * BATCH + 1, pixx, pixy, T, C0, C1, C2, D, last_contributor,
+                                     lane, p.n_touched);
             else
-                walk_survivors<false>(s, m, c0, r * BATCH, pixx, pixy, T, C0, C1, C2, D, last_contributor, done, lane,
-                                      p.n_touched);
-            if (__all_sync(0xffffffffu, done)) break;
+                walk_survivors<false>(s, wl, __popc(m), r * BATCH + 1, pixx, pixy, T, C0, C1, C2, D, last_contributor,
+                                      lane, p.n_touched);
+            __syncwarp();      // the list is rewritten by the next chunk
+            if (__all_sync(0xffffffffu, T < 0.f)) break;
         }
     }
     cp_async_wait<0>();
+    T = fabsf(T);
     if (inside) {
         const size_t N = (size_t)p.W * p.H;
         const size_t pix = (size_t)pyi * p.W + pxi;
@@ -198,7 +220,7 @@ void launch_count_pairs(const RenderFwdParams& p, unsigned long long* counts, cu
 }
 
 void launch_render_fwd(const RenderFwdParams& p, cudaStream_t s) {
-    render_fwd_kernel<<<p.gx * p.gy, 256, 0, s>>>(p);
+    launch_chained(render_fwd_kernel, p.gx * p.gy, 256, 0, s, p);
 }
 
 }  // namespace wgs

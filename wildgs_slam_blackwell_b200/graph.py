@@ -90,6 +90,25 @@ class async_forward:
         return False
 
 
+class chained_launch:
+    """Context manager around wgs_set_chained_launch: the programmatic dependent launch of the forward / backward
+    kernels (on by default) is switched for the launches and graph captures made inside.  It pays on one stream (no gap
+    between the kernels of a frame); with a second stream that could use the SM slots the waiting grid holds it costs
+    more than it saves, so window.WindowTrainer turns it off around its two-stream section.  Process-wide setting;
+    the previous one is restored on exit."""
+
+    def __init__(self, enabled):
+        self.enabled = bool(enabled)
+
+    def __enter__(self):
+        self._before = _lib.load().wgs_set_chained_launch(int(self.enabled))
+        return self
+
+    def __exit__(self, *exc):
+        _lib.load().wgs_set_chained_launch(self._before)
+        return False
+
+
 class CapturedIteration:
     """Capture `step()` -- a whole iteration over tensors with fixed storage, backward included -- into a
     CUDA graph.  `step` must set the .grad of its leaves to None before its backward (so the captured

@@ -94,8 +94,9 @@ def _f32(t, device, shape=None):
 def photometric_loss(color, gt_color, *, depth=None, gt_depth=None, opacity=None, pixel_mask=None,
                      uncertainty=None, exposure_a=None, exposure_b=None, rgb_boundary_threshold=0.01,
                      depth_min=0.01, color_weight=1.0, depth_weight=0.0, depth_max=0.0, depth_weighted=False,
-                     depth_margin=1.0, uncertainty_rate=None, weight_mean=None):
-    """One launch: returns (loss (1,), dL_dcolor (3,H,W), dL_ddepth (1,H,W), dL_dexposure (2,) or None).
+                     depth_margin=1.0, uncertainty_rate=None, weight_mean=None, _packed=False):
+    """One launch: returns (loss (1,), dL_dcolor (3,H,W), dL_ddepth (1,H,W), dL_dexposure (2,) or None)
+    (+ the (4HW,) buffer both cotangents are views of, with _packed).
     See include/wgs_loss.h for the exact expression.  uncertainty_rate given: `uncertainty` is the patch-resolution
     network output, up-sampled inside; weight_mean: a (1,) float tensor that receives mean(w)."""
     if color.dim() != 3 or color.shape[0] != 3:
@@ -145,6 +146,8 @@ def photometric_loss(color, gt_color, *, depth=None, gt_depth=None, opacity=None
         rc = _lib_loss().wgs_photometric_loss(C.byref(a), C.c_void_p(torch.cuda.current_stream(device).cuda_stream))
     if rc != _lib.WGS_OK:
         raise RuntimeError(f"wgs_photometric_loss failed ({rc}): {_lib.last_error()}")
+    if _packed:
+        return loss, dL_dcolor, dL_ddepth, (dexp if ea is not None else None), out[:4 * H * W]
     return loss, dL_dcolor, dL_ddepth, (dexp if ea is not None else None)
 
 
@@ -153,29 +156,32 @@ class _PhotometricLoss(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, color, depth, exposure_a, exposure_b, kw):
-        loss, dc, dd, de = photometric_loss(color, kw["gt_color"], depth=depth, gt_depth=kw.get("gt_depth"),
-                                            opacity=kw.get("opacity"), pixel_mask=kw.get("pixel_mask"),
-                                            uncertainty=kw.get("uncertainty"), exposure_a=exposure_a,
-                                            exposure_b=exposure_b,
-                                            rgb_boundary_threshold=kw["rgb_boundary_threshold"],
-                                            color_weight=kw["color_weight"], depth_weight=kw["depth_weight"],
-                                            depth_max=kw.get("depth_max", 0.0),
-                                            depth_weighted=kw.get("depth_weighted", False),
-                                            uncertainty_rate=kw.get("uncertainty_rate"),
-                                            weight_mean=kw.get("weight_mean"))
+        loss, dc, dd, de, packed = photometric_loss(color, kw["gt_color"], depth=depth, gt_depth=kw.get("gt_depth"),
+                                                    opacity=kw.get("opacity"), pixel_mask=kw.get("pixel_mask"),
+                                                    uncertainty=kw.get("uncertainty"), exposure_a=exposure_a,
+                                                    exposure_b=exposure_b,
+                                                    rgb_boundary_threshold=kw["rgb_boundary_threshold"],
+                                                    color_weight=kw["color_weight"], depth_weight=kw["depth_weight"],
+                                                    depth_max=kw.get("depth_max", 0.0),
+                                                    depth_weighted=kw.get("depth_weighted", False),
+                                                    uncertainty_rate=kw.get("uncertainty_rate"),
+                                                    weight_mean=kw.get("weight_mean"), _packed=True)
         ctx.has_depth = depth is not None and kw["depth_weight"] != 0.0
         ctx.has_exp = de is not None
-        ctx.save_for_backward(dc, dd, de if de is not None else dc.new_empty(0))
+        ctx.shape = tuple(dc.shape)
+        ctx.save_for_backward(packed, de if de is not None else dc.new_empty(0))
         return loss.reshape(())
 
     @staticmethod
     def backward(ctx, g):
-        dc, dd, de = ctx.saved_tensors
+        packed, de = ctx.saved_tensors
+        _, H, W = ctx.shape
         ga = gb = None
         if ctx.has_exp:
             ge = de * g
             ga, gb = ge[0:1], ge[1:2]
-        return dc * g, (dd * g if ctx.has_depth else None), ga, gb, None
+        gp = packed * g                      # both cotangents in one launch (they share the kernel's output buffer)
+        return gp[:3 * H * W].view(3, H, W), (gp[3 * H * W:].view(1, H, W) if ctx.has_depth else None), ga, gb, None
 
 
 def _gt_image(viewpoint, device):

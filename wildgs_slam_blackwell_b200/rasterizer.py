@@ -117,6 +117,8 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
         campos = _f32c(s.campos, device)
         M = int(sh.shape[1]) if (sh is not None and sh.numel() != 0) else 0
         sh_rest = _f32c(sh_rest, device)
+        if sh_rest is not None and sh_rest.numel() == 0:
+            sh_rest = None                  # degree 0: DC coefficients only
         if sh_rest is not None and M:
             if sh.shape[1] != 1:
                 raise RuntimeError("with sh_rest, sh must be the (P,1,3) DC coefficients")

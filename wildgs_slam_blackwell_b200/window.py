@@ -442,11 +442,15 @@ class WindowTrainer:
                 self._side_stream = torch.cuda.Stream(dev)
             main = torch.cuda.current_stream(dev)
             self._side_stream.wait_stream(main)
-            with torch.cuda.stream(self._side_stream):
-                for u in lanes[1]:
+            from . import graph
+            # chained (programmatic dependent) launches off: the waiting grid of one stream would sit on the SM slots
+            # the other stream's kernels are meant to fill
+            with graph.chained_launch(False):
+                with torch.cuda.stream(self._side_stream):
+                    for u in lanes[1]:
+                        run(u, False)
+                for u in lanes[0]:
                     run(u, False)
-            for u in lanes[0]:
-                run(u, False)
             main.wait_stream(self._side_stream)
         else:
             for n_done, u in enumerate(mine):
