@@ -18,6 +18,7 @@ def main():
     name, repl = sys.argv[1], dict(a.split("=") for a in sys.argv[2:])
     B.build(quiet=True)
     out_dir = os.path.join(ROOT, "scripts", "variants")
+    os.makedirs(out_dir, exist_ok=True)
     objs = []
     for src in B.SOURCES:
         if src in repl:

@@ -68,84 +68,103 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
     __shared__ float s_part[WGS_PRE_BWD_THREADS / 32][6];   // pose partials of the block's warps, summed over its chunks
     if ((threadIdx.x & 31) < 6) s_part[threadIdx.x >> 5][threadIdx.x & 31] = 0.f;   // (each warp only touches its own row)
     // A block walks chunks of WGS_PRE_BWD_THREADS Gaussians, chunk = blockIdx.x, + gridDim.x, ... (the grid is sized to
-    // the SMs, launch_preprocess_bwd): the block-level epilogue -- pose partials, fence, the ticket atomic, ~3 us of
-    // latency during which the block only holds its registers -- is paid once per block instead of once per 256
-    // Gaussians (3 907 times at 1 M: it was what kept a quarter-image strip at 80 us of the whole view's 96).
+    // the SMs, launch_preprocess_bwd), so the block-level epilogue (pose partials, fence, ticket atomic) is paid once per
+    // block.  STAGED: a thread works on its own Gaussian of the chunk (the SH rows of a warp must stay one contiguous
+    // span); dead threads of the last chunk shadow its last Gaussian and write nothing.  Otherwise the block QUEUES the
+    // visible Gaussians (radii > 0 and a non-empty rectangle inside the rendered strip) of as many chunks as it takes
+    // to fill WGS_PRE_BWD_THREADS slots and only then runs the expensive part, on full warps: a 3-row strip of a mapping
+    // window keeps 1/7 of the Gaussians, and with per-chunk compaction one or two warps of a block worked while the
+    // others sat in the next barrier (ncu: 16 % issue utilisation, 24 of 34 warp-cycles in the barrier).  Invisible
+    // Gaussians have nothing to add to an accumulating backward; an overwriting one zero-fills their outputs here.
     const int nchunks = (p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS;
-    for (int chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
-    const int gidx = chunk * WGS_PRE_BWD_THREADS + threadIdx.x;
+    __shared__ int s_queue[2 * WGS_PRE_BWD_THREADS];
+    __shared__ int s_wcount[WGS_PRE_BWD_THREADS / 32];
+    int chunk = blockIdx.x, qn = 0;   // qn: queued Gaussians (the same value in every thread)
+    for (;;) {
     float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     // staged SH rows of this warp: packed (P,M,3) rows, or the (P,M-1,3) rest rows in raw-parameter mode
     const int sh_rw = STAGED ? (p.sh_rest ? 3 * (p.M - 1) : 3 * p.M) : 1;
     const int sh_rs = sh_row_stride(sh_rw);
-    const int wrow0 = chunk * WGS_PRE_BWD_THREADS + (threadIdx.x & ~31);  // first Gaussian of the warp
+    int wrow0 = 0;  // STAGED: first Gaussian of the warp
     float* const wstage = sh_stage + (threadIdx.x & ~31) * sh_rs;
     unsigned vmask = 0;
-    // Which Gaussian this thread works on.  STAGED: its own (the SH rows of a warp must stay one contiguous span);
-    // dead threads of the last block shadow its last Gaussian and write nothing.  Otherwise the block first COMPACTS
-    // its visible Gaussians (radii > 0 and a non-empty rectangle inside the rendered strip) onto its leading threads:
-    // the expensive part then runs on full warps and whole warps retire early -- a quarter-image strip of a mapping
-    // window keeps ~1/4 of the Gaussians, a whole view ~3/4.  Invisible Gaussians have nothing to add to an
-    // accumulating backward; an overwriting one zero-fills their outputs here.
-    bool live = gidx < p.P, work = true;
-    int idx = live ? gidx : p.P - 1;
-    int rad = 0;
+    bool live, work;
+    int idx, rad = 0;
     uint2 rect = make_uint2(0u, 0u);
     if (STAGED) {
+        if (chunk >= nchunks) break;
+        const int gidx = chunk * WGS_PRE_BWD_THREADS + threadIdx.x;
+        wrow0 = chunk * WGS_PRE_BWD_THREADS + (threadIdx.x & ~31);
+        chunk += gridDim.x;
+        live = gidx < p.P;
+        work = true;
+        idx = live ? gidx : p.P - 1;
         rad = __ldg(p.radii + idx);
         rect = __ldg(p.geom.rect + idx);
     } else {
-        __shared__ uint16_t s_list[WGS_PRE_BWD_THREADS];
-        __shared__ int s_wcount[WGS_PRE_BWD_THREADS / 32];
         const int lane_ = threadIdx.x & 31, warp_ = threadIdx.x >> 5;
-        bool vis1 = false;
-        if (live) {
-            rad = __ldg(p.radii + gidx);
-            rect = __ldg(p.geom.rect + gidx);
-            vis1 = rad > 0 && rect.x != rect.y;
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, vis1);
-        if (lane_ == 0) s_wcount[warp_] = __popc(bal);
-        if (live && !vis1 && accm == 0) {
-            const size_t i = (size_t)gidx;
-            if (p.dL_dmeans3D) { p.dL_dmeans3D[3 * i] = 0.f; p.dL_dmeans3D[3 * i + 1] = 0.f; p.dL_dmeans3D[3 * i + 2] = 0.f; }
-            if (p.dL_dmeans2D) { p.dL_dmeans2D[3 * i] = 0.f; p.dL_dmeans2D[3 * i + 1] = 0.f; p.dL_dmeans2D[3 * i + 2] = 0.f; }
-            if (p.dL_dopacity) p.dL_dopacity[i] = 0.f;
-            if (p.dL_dcolors) { p.dL_dcolors[3 * i] = 0.f; p.dL_dcolors[3 * i + 1] = 0.f; p.dL_dcolors[3 * i + 2] = 0.f; }
-            if (p.dL_dcov3D) {
-#pragma unroll
-                for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * i + k] = 0.f;
+        while (qn < WGS_PRE_BWD_THREADS && chunk < nchunks) {
+            const int gidx = chunk * WGS_PRE_BWD_THREADS + threadIdx.x;
+            chunk += gridDim.x;
+            live = gidx < p.P;
+            bool vis1 = false;
+            if (live) {
+                const int r_ = __ldg(p.radii + gidx);
+                const uint2 q_ = __ldg(p.geom.rect + gidx);
+                vis1 = r_ > 0 && q_.x != q_.y;
             }
-            if (p.dL_dscales) { p.dL_dscales[3 * i] = 0.f; p.dL_dscales[3 * i + 1] = 0.f; p.dL_dscales[3 * i + 2] = 0.f; }
-            if (p.dL_drotations) {
+            const unsigned bal = __ballot_sync(0xffffffffu, vis1);
+            if (lane_ == 0) s_wcount[warp_] = __popc(bal);
+            if (live && !vis1 && accm == 0) {
+                const size_t i = (size_t)gidx;
+                if (p.dL_dmeans3D) { p.dL_dmeans3D[3 * i] = 0.f; p.dL_dmeans3D[3 * i + 1] = 0.f; p.dL_dmeans3D[3 * i + 2] = 0.f; }
+                if (p.dL_dmeans2D) { p.dL_dmeans2D[3 * i] = 0.f; p.dL_dmeans2D[3 * i + 1] = 0.f; p.dL_dmeans2D[3 * i + 2] = 0.f; }
+                if (p.dL_dopacity) p.dL_dopacity[i] = 0.f;
+                if (p.dL_dcolors) { p.dL_dcolors[3 * i] = 0.f; p.dL_dcolors[3 * i + 1] = 0.f; p.dL_dcolors[3 * i + 2] = 0.f; }
+                if (p.dL_dcov3D) {
 #pragma unroll
-                for (int k = 0; k < 4; k++) p.dL_drotations[4 * i + k] = 0.f;
-            }
-            if (p.sh && p.dL_dsh) {
-                if (p.sh_rest) {
-                    float* __restrict__ d0 = p.dL_dsh + i * 3;
-                    d0[0] = d0[1] = d0[2] = 0.f;
-                    if (p.dL_dsh_rest)
-                        for (int k = 0; k < 3 * (p.M - 1); k++) p.dL_dsh_rest[i * (p.M - 1) * 3 + k] = 0.f;
-                } else {
-                    for (int k = 0; k < 3 * p.M; k++) p.dL_dsh[i * p.M * 3 + k] = 0.f;
+                    for (int k = 0; k < 6; k++) p.dL_dcov3D[6 * i + k] = 0.f;
+                }
+                if (p.dL_dscales) { p.dL_dscales[3 * i] = 0.f; p.dL_dscales[3 * i + 1] = 0.f; p.dL_dscales[3 * i + 2] = 0.f; }
+                if (p.dL_drotations) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) p.dL_drotations[4 * i + k] = 0.f;
+                }
+                if (p.sh && p.dL_dsh) {
+                    if (p.sh_rest) {
+                        float* __restrict__ d0 = p.dL_dsh + i * 3;
+                        d0[0] = d0[1] = d0[2] = 0.f;
+                        if (p.dL_dsh_rest)
+                            for (int k = 0; k < 3 * (p.M - 1); k++) p.dL_dsh_rest[i * (p.M - 1) * 3 + k] = 0.f;
+                    } else {
+                        for (int k = 0; k < 3 * p.M; k++) p.dL_dsh[i * p.M * 3 + k] = 0.f;
+                    }
                 }
             }
-        }
-        __syncthreads();
-        int before = 0, total = 0;
+            __syncthreads();
+            int before = 0, total = 0;
 #pragma unroll
-        for (int w = 0; w < WGS_PRE_BWD_THREADS / 32; w++) {
-            const int c = s_wcount[w];
-            before += w < warp_ ? c : 0;
-            total += c;
+            for (int w = 0; w < WGS_PRE_BWD_THREADS / 32; w++) {
+                const int c = s_wcount[w];
+                before += w < warp_ ? c : 0;
+                total += c;
+            }
+            if (vis1) s_queue[qn + before + __popc(bal & ((1u << lane_) - 1u))] = gidx;
+            qn += total;
+            __syncthreads();
         }
-        if (vis1) s_list[before + __popc(bal & ((1u << lane_) - 1u))] = (uint16_t)threadIdx.x;
-        __syncthreads();
-        work = (int)threadIdx.x < total;
+        if (qn == 0) break;
+        const int take = min(qn, WGS_PRE_BWD_THREADS);
+        work = (int)threadIdx.x < take;
         live = work;
+        idx = work ? s_queue[threadIdx.x] : p.P - 1;
+        // the queue's tail moves to its head
+        const int rest = qn - take;
+        const int moved = (int)threadIdx.x < rest ? s_queue[take + threadIdx.x] : 0;
+        __syncthreads();
+        if ((int)threadIdx.x < rest) s_queue[threadIdx.x] = moved;
+        qn = rest;
         if (work) {
-            idx = chunk * WGS_PRE_BWD_THREADS + (int)s_list[threadIdx.x];
             // (radii / rect of the adopted Gaussian: both answered "visible")
             rad = __ldg(p.radii + idx);
             rect = __ldg(p.geom.rect + idx);
@@ -476,7 +495,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
 #pragma unroll
         for (int i = 0; i < 6; i++) s_part[threadIdx.x >> 5][i] += tau[i];
     }
-    }   // chunk loop
+    }   // fill / process loop
     // ---- pose gradient: warp (over its chunks) -> block -> grid, deterministic for a given grid ----
     __shared__ bool s_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
