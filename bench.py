@@ -124,7 +124,15 @@ class _Set:
     inputs are views into ONE flat device buffer so that a step's H2D traffic is a single copy."""
 
     def __init__(self, wl, mod, dev):
-        self.flat = torch.empty_like(wl.host_flat, device=dev)
+        self.mem = None
+        if wl.peer is not None:
+            # multi-GPU: the buffer lives in NVLink peer memory, so that each rank uploads 1/world of the replicated
+            # Gaussian set and the library's allgather kernel completes it (Workload.prefetch / _compute_e2e)
+            from wildgs_slam_blackwell_b200.peer import PeerMemory
+            self.mem = PeerMemory(wl.host_flat.numel(), dev, use_multicast=wl.peer.multicast)
+            self.flat = self.mem.flat
+        else:
+            self.flat = torch.empty_like(wl.host_flat, device=dev)
         self.flat.copy_(wl.host_flat)
         self.d = {k: self.flat[o:o + n].view(shape) for k, (o, n, shape) in wl.layout.items()}
         self.leaves = [self.d[k].requires_grad_(True) for k in ("means3D", "sh", "opacities", "scales", "rotations")]
@@ -165,6 +173,22 @@ class Workload:
         for k, a in arrays.items():
             o, n, _ = self.layout[k]
             self.host_flat[o:o + n] = torch.from_numpy(np.ascontiguousarray(a, np.float32).reshape(-1))
+        self.n_gauss_floats = self.layout["viewmatrix"][0]     # the replicated Gaussian set: the head of the buffer
+        self.bucket_floats = sum(self.layout[k][1] for k in ("means3D", "sh", "opacities", "scales", "rotations"))
+        # multi-GPU: the backward kernel writes the Gaussian gradients straight into one flat bucket
+        # (rasterizer.grad_sink) ... which lives in NVLink peer memory and is summed by the library's own kernel
+        # (peer.PeerBucket, csrc/peer_allreduce.cu) unless WGS_ALLREDUCE=nccl
+        self.peer = None
+        mode = os.environ.get("WGS_ALLREDUCE", "auto")
+        if hasattr(mod, "grad_sink") and dist.is_initialized() and dist.get_world_size() > 1 and mode != "nccl":
+            from wildgs_slam_blackwell_b200.peer import PeerBucket, owned_pieces
+            w = dist.get_world_size()
+            self.peer = PeerBucket(self.bucket_floats, dev, use_multicast=(mode == "nvls" or (mode == "auto" and w >= 4)))
+            self.bucket = self.peer.flat
+            # e2e: this rank's share of the replicated Gaussian set (the split the allgather kernel uses)
+            self.upload_pieces = owned_pieces([(0, self.n_gauss_floats)], dist.get_rank(), w)
+        else:
+            self.bucket = torch.zeros(self.bucket_floats, dtype=torch.float32, device=dev)
         # two input sets: the e2e loop copies step i+1's inputs (copy stream) while step i computes
         self.sets = [_Set(self, mod, dev), _Set(self, mod, dev)]
         self.copy_stream = torch.cuda.Stream(device=dev)
@@ -177,21 +201,9 @@ class Workload:
         self.dc, self.dd = torch.from_numpy(dc).to(dev), torch.from_numpy(dd).to(dev)
         self.out_host = torch.zeros(7, dtype=torch.float32).pin_memory()
         self.h2d_bytes = self.host_flat.numel() * 4
+        if self.peer is not None:
+            self.h2d_bytes = 4 * (sum(n for _, n in self.upload_pieces) + self.host_flat.numel() - self.n_gauss_floats)
         self.d2h_bytes = 7 * 4
-        self.bucket_floats = sum(t.numel() for t in self.leaves)
-        # multi-GPU: the backward kernel writes the Gaussian gradients straight into one flat bucket
-        # (rasterizer.grad_sink) that NCCL then sums in place -- no packing copy
-        # ... which lives in NVLink peer memory and is summed by the library's own kernel (peer.PeerBucket,
-        # csrc/peer_allreduce.cu) unless WGS_ALLREDUCE=nccl
-        self.peer = None
-        mode = os.environ.get("WGS_ALLREDUCE", "auto")
-        if hasattr(mod, "grad_sink") and dist.is_initialized() and dist.get_world_size() > 1 and mode != "nccl":
-            from wildgs_slam_blackwell_b200.peer import PeerBucket
-            w = dist.get_world_size()
-            self.peer = PeerBucket(self.bucket_floats, dev, use_multicast=(mode == "nvls" or (mode == "auto" and w >= 4)))
-            self.bucket = self.peer.flat
-        else:
-            self.bucket = torch.zeros(self.bucket_floats, dtype=torch.float32, device=dev)
         self.sink = None
         self.fused_loss = None
         self.use_graph, self.graphs = hasattr(mod, "grad_sink"), {}
@@ -239,10 +251,20 @@ class Workload:
         st = self.sets[i % 2]
         with torch.cuda.stream(self.copy_stream), torch.no_grad():
             self.copy_stream.wait_event(st.compute_done)      # the step that last used this set has finished
-            st.flat.copy_(self.host_flat, non_blocking=True)
+            if self.peer is None:
+                st.flat.copy_(self.host_flat, non_blocking=True)
+            else:
+                # this rank's 1/world of the replicated Gaussian set + its own camera and targets; the other ranks'
+                # shares arrive over NVLink (allgather kernel at the head of the step)
+                for o, n in self.upload_pieces:
+                    st.flat[o:o + n].copy_(self.host_flat[o:o + n], non_blocking=True)
+                g = self.n_gauss_floats
+                st.flat[g:].copy_(self.host_flat[g:], non_blocking=True)
             st.copy_done.record(self.copy_stream)
 
     def _compute_e2e(self, st, world):
+        if self.peer is not None:
+            self.peer.all_gather(target=st.mem, segments=[(0, self.n_gauss_floats)])
         self._zero_grads(st.leaves)
         color, radii, depth, opacity, n_touched = self._forward(st)
         if self.fused_loss is not None:
@@ -584,8 +606,11 @@ def main():
             e2e_ms, _ = timed_loop(lambda: wl.step_e2e(world), a.steps, a.warmup, flush, world)
         e2e = {"value": round(frames / (e2e_ms * 1e-3), 3), "unit": "frames/s", "h2d_bytes_per_step": wl.h2d_bytes,
                "d2h_bytes_per_step": wl.d2h_bytes, "ms_per_step": round(e2e_ms / a.steps, 4),
-               "pipelining": "inputs of step i+1 copied (one packed H2D copy) on a second stream during step i "
-                              "(double-buffered)" + ("; the step's device work replayed from a CUDA graph (graph.CapturedIteration), "
+               "pipelining": ("inputs of step i+1 copied (one packed H2D copy) on a second stream during step i "
+                              "(double-buffered)" if wl.peer is None else
+                              "inputs of step i+1 copied on a second stream during step i (double-buffered): each rank uploads "
+                              "1/world of the replicated Gaussian set + its own camera and targets, the library's allgather "
+                              "kernel completes the set over NVLink at the head of the step") + ("; the step's device work replayed from a CUDA graph (graph.CapturedIteration), "
                                                      "instance-capacity overflow checked after the loop"
                                                      if a.impl == "ours" else ""),
                "loss": "mean|color - target| + mean|depth - target|: " +

@@ -219,12 +219,17 @@ __global__ void __launch_bounds__(256) scatter_kernel(const __grid_constant__ Bi
     if (n && !wide) {
         // four cursor atomics in flight before their dependent stores (the kernel is bound by the
         // round trip of the returning atomics, not by their number)
+        // (the tile index advances row-major through the rectangle: no division per instance)
+        uint32_t t = y0 * p.gx + x0, x = 0;
         for (uint32_t i = 0; i < n; i += 4) {
             uint32_t slot[4];
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const uint32_t q = i + j;
-                if (q < n) slot[j] = atomicAdd(cursor + (y0 + q / w) * p.gx + x0 + q % w, 1u);
+                if (i + j < n) {
+                    slot[j] = atomicAdd(cursor + t, 1u);
+                    t++;
+                    if (++x == w) { x = 0; t += p.gx - w; }
+                }
             }
 #pragma unroll
             for (int j = 0; j < 4; j++)
