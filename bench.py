@@ -187,6 +187,7 @@ class Workload:
             self.bucket = self.peer.flat
             # e2e: this rank's share of the replicated Gaussian set (the split the allgather kernel uses)
             self.upload_pieces = owned_pieces([(0, self.n_gauss_floats)], dist.get_rank(), w)
+            self.upload_sync = PeerBucket(4, dev, use_multicast=self.peer.multicast)   # flags of the upload allgather
         else:
             self.bucket = torch.zeros(self.bucket_floats, dtype=torch.float32, device=dev)
         # two input sets: the e2e loop copies step i+1's inputs (copy stream) while step i computes
@@ -255,16 +256,16 @@ class Workload:
                 st.flat.copy_(self.host_flat, non_blocking=True)
             else:
                 # this rank's 1/world of the replicated Gaussian set + its own camera and targets; the other ranks'
-                # shares arrive over NVLink (allgather kernel at the head of the step)
+                # shares arrive over NVLink (allgather kernel behind the copies)
                 for o, n in self.upload_pieces:
                     st.flat[o:o + n].copy_(self.host_flat[o:o + n], non_blocking=True)
                 g = self.n_gauss_floats
                 st.flat[g:].copy_(self.host_flat[g:], non_blocking=True)
+                # (on the copy stream, with its own flag area: it overlaps the compute of the step before)
+                self.upload_sync.all_gather(target=st.mem, segments=[(0, g)])
             st.copy_done.record(self.copy_stream)
 
     def _compute_e2e(self, st, world):
-        if self.peer is not None:
-            self.peer.all_gather(target=st.mem, segments=[(0, self.n_gauss_floats)])
         self._zero_grads(st.leaves)
         color, radii, depth, opacity, n_touched = self._forward(st)
         if self.fused_loss is not None:
@@ -610,7 +611,7 @@ def main():
                               "(double-buffered)" if wl.peer is None else
                               "inputs of step i+1 copied on a second stream during step i (double-buffered): each rank uploads "
                               "1/world of the replicated Gaussian set + its own camera and targets, the library's allgather "
-                              "kernel completes the set over NVLink at the head of the step") + ("; the step's device work replayed from a CUDA graph (graph.CapturedIteration), "
+                              "kernel completes the set over NVLink on the copy stream") + ("; the step's device work replayed from a CUDA graph (graph.CapturedIteration), "
                                                      "instance-capacity overflow checked after the loop"
                                                      if a.impl == "ours" else ""),
                "loss": "mean|color - target| + mean|depth - target|: " +

@@ -17,7 +17,7 @@ PATTERNS = [("HMMA", r"^HMMA"), ("LDSM", r"^LDSM"), ("LDGSTS", r"^LDGSTS"), ("RE
             ("ATOMG/ATOM", r"^ATOM"), ("ATOMS", r"^ATOMS"), ("multimem (LDGMC / ST..MMEM)", r"^(LDGMC|STGMC|REDGMC|.*MMEM|.*\.MC\b)"),
             ("MAPA", r"^MAPA"), ("UCGABAR (cluster barrier)", r"^UCGABAR"), ("MUFU", r"^MUFU"), ("SHFL", r"^SHFL"), ("VOTE", r"^VOTE"),
             ("REDUX", r"^REDUX"), ("BAR", r"^BAR"), ("FFMA", r"^FFMA"), ("LDG", r"^LDG"), ("STG", r"^STG"),
-            ("LDS", r"^LDS(?!M)"), ("STS", r"^STS"), ("ACQBULK/UBLKCP (TMA)", r"^(UBLKCP|UTMA|SYNCS)")]
+            ("LDS", r"^LDS(?!M)"), ("STS", r"^STS"), ("ACQBULK / PREEXIT (griddepcontrol)", r"^(ACQBULK|PREEXIT)"), ("UBLKCP/UTMA (TMA)", r"^(UBLKCP|UTMA)")]
 
 
 def main():
