@@ -262,6 +262,9 @@ class Workload:
                 g = self.n_gauss_floats
                 st.flat[g:].copy_(self.host_flat[g:], non_blocking=True)
                 # (on the copy stream, with its own flag area: it overlaps the compute of the step before)
+                # a one-block rendezvous first: the wait for the slowest rank's copies is not spent by the whole
+                # allgather grid on SM slots the running step's kernels need)
+                self.upload_sync.rendezvous()
                 self.upload_sync.all_gather(target=st.mem, segments=[(0, g)])
             st.copy_done.record(self.copy_stream)
 
@@ -498,7 +501,7 @@ def window_entry(a, dev, world, rank, flush):
     sys.path.insert(0, os.path.join(ROOT, "scripts"))
     from window_workload import WindowWorkload
     wl = WindowWorkload("config3", dev, peer=os.environ.get("WGS_ALLREDUCE", "auto").replace("nccl", "off"),
-                        plan="balanced", streams=2, use_graph=os.environ.get("WGS_ALLREDUCE", "auto") != "nccl")
+                        plan="auto", streams=2, use_graph=os.environ.get("WGS_ALLREDUCE", "auto") != "nccl")
     ms, out = wl.time(a.window_steps, max(a.warmup, 3), flush)
     par = wl.parity() if world > 1 else None
     entry = {"metric": "mapping-window iterations/sec (config 3)", "value": round(1e3 / ms, 3), "unit": "window steps/s",

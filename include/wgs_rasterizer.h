@@ -278,6 +278,9 @@ int wgs_peer_allreduce(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, u
  *                           the first half of a sharded optimiser step -- Adam then runs on 1/world of the model per rank
  *   mode 2  allgather       this rank's copy of its slice is written into every rank's copy (on another buffer of the same
  *                           layout, the updated parameters return to all ranks)
+ *   mode 3  rendezvous      nothing moves: ONE block runs the two peer barriers.  In front of an exchange whose peers may
+ *                           arrive late (behind their own H2D copies, say) it does the waiting with one block, not with
+ *                           the whole exchange grid spinning on SM slots a concurrent stream's kernels could use
  * Every call is bracketed by the block-level peer barriers of wgs_peer_allreduce; flag_ptrs may belong to a different
  * allocation than buffer_ptrs (one flag area serves all buffers exchanged in stream order). */
 int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,

@@ -33,7 +33,7 @@ def main():
     ap.add_argument("--no-sink", action="store_true", help="let autograd allocate/add per-view gradients")
     ap.add_argument("--peer", default="auto", choices=["off", "auto", "nvls", "p2p"],
                     help="bucket in NVLink peer memory, summed by wgs_peer_allreduce instead of NCCL")
-    ap.add_argument("--plan", default="balanced", choices=["views", "strips", "balanced"])
+    ap.add_argument("--plan", default="auto", choices=["views", "strips", "balanced", "auto"])
     ap.add_argument("--streams", type=int, default=2, help="CUDA streams a rank spreads its work units over")
     ap.add_argument("--eager", action="store_true", help="do not capture the rank's step in a CUDA graph")
     ap.add_argument("--emulate", type=int, default=0,

@@ -115,9 +115,24 @@ class WindowWorkload:
         return graph.check_overflow(self.dev)
 
     # ---- timing: W warm-up steps, K timed steps, L2 flushed between steps, max over ranks ----
+    def choose_plan(self, flush, candidates=("balanced", "strips"), steps=3):
+        """plan="auto": time a few steps of each candidate plan (max over ranks, so every rank picks the same one) and
+        keep the faster -- whole views + strips of the remainder against contiguous strips of everything; which one wins
+        depends on how the window divides by the world size."""
+        self.plan_trials = {}
+        if self.world == 1 and self.emulate is None:
+            self.plan = candidates[0]            # one rank: every plan is "all views, whole"
+            return
+        for c in candidates:
+            self.plan, self._it = c, None
+            self.plan_trials[c] = round(self.time(steps, 2, flush)[0], 4)
+        self.plan, self._it = min(self.plan_trials, key=self.plan_trials.get), None
+
     def time(self, steps, warmup, flush=None):
         if flush is None:
             flush = torch.zeros((512 << 20) // 4, device=self.dev)
+        if self.plan == "auto":
+            self.choose_plan(flush)
         for _ in range(max(warmup, 1)):
             out = self.step()
             flush.add_(1)
@@ -144,7 +159,7 @@ class WindowWorkload:
         return float(total.item()) / steps, out
 
     # ---- allreduced bucket == sum over views of single-GPU per-view gradients, whatever the assignment ----
-    def parity(self, plans=("views", "balanced")):
+    def parity(self, plans=("views", "balanced", "strips")):
         """Every rank renders ALL views whole through plain autograd (no sink, no strips, no exchange) and sums the
         per-view gradients; then one eager window step per plan, and the bucket every rank ends up with is compared
         with that sum.  Tolerance of the parity suite: |err| <= 1e-3 |ref| + 1e-4 max|ref| per tensor."""
@@ -192,7 +207,7 @@ class WindowWorkload:
     def describe(self, out):
         b = self.trainer.bucket
         return {"workload": f"{self.name}: {self.P} Gaussians, {self.n_views} keyframes {self.W}x{self.H}, SH degree {self.deg}",
-                "plan": self.plan, "assignment": out["assignment"], "bucket_bytes": out["bucket_bytes"],
+                "plan": self.plan, "plan_trials_ms": getattr(self, "plan_trials", None), "assignment": out["assignment"], "bucket_bytes": out["bucket_bytes"],
                 "streams_per_rank": self.trainer.streams, "cuda_graph": self.use_graph,
                 "exchange": ("none (one rank)" if self.world == 1 else "NCCL allreduce" if self.peer == "off" else
                              "peer-memory allreduce kernel (" + ("NVLS multimem" if b.peer.multicast else "P2P two-shot") + ")"),

@@ -31,6 +31,9 @@ def _worker(rank, world, port, out_dir):
                     b.flat.copy_(x)
                     ref = x.clone()
                     dist.all_reduce(ref)
+                    if it == 1:
+                        b.rendezvous()            # one-block peer barrier (mode 3): moves nothing, keeps the generations in step
+                        assert torch.equal(b.flat, x)
                     b.all_reduce()
                     torch.cuda.synchronize()
                     same = b.flat.clone()

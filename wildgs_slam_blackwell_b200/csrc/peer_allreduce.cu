@@ -154,7 +154,7 @@ int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, ui
                       int32_t mode, void* cuda_stream) {
     using namespace wgs;
     if (!buffer_ptrs || !flag_ptrs || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world ||
-        !seg_offsets || !seg_lengths || n_segments < 1 || n_segments > PEER_MAX_SEGMENTS || mode < 0 || mode > 2) {
+        !seg_offsets || !seg_lengths || n_segments < 1 || n_segments > PEER_MAX_SEGMENTS || mode < 0 || mode > 3) {
         wgs_set_error_message("wgs_peer_exchange: bad world/rank/segment table/mode");
         return WGS_ERR_INVALID_ARGUMENT;
     }
@@ -184,8 +184,13 @@ int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, ui
     p.mc = (float*)multicast_ptr; p.rank = rank; p.world = world; p.n4 = run; p.mode = mode; p.nseg = n_segments;
     p.epochs = p.flags[rank] + PEER_BLOCKS * PEER_MAX_WORLD;
     cudaStream_t s = (cudaStream_t)cuda_stream;
-    if (p.mc) peer_allreduce_kernel<true><<<PEER_BLOCKS, PEER_THREADS, 0, s>>>(p);
-    else peer_allreduce_kernel<false><<<PEER_BLOCKS, PEER_THREADS, 0, s>>>(p);
+    // mode 3, rendezvous: ONE block runs the two flag barriers and moves nothing.  Put in front of an exchange whose
+    // peers may arrive late (e.g. behind their own H2D copies), it does the waiting with one block instead of with the
+    // whole exchange grid spinning on SM slots that a concurrent stream's kernels could use.
+    const int grid = mode == 3 ? 1 : PEER_BLOCKS;
+    if (mode == 3) { p.n4 = 0; p.mode = 0; }
+    if (p.mc) peer_allreduce_kernel<true><<<grid, PEER_THREADS, 0, s>>>(p);
+    else peer_allreduce_kernel<false><<<grid, PEER_THREADS, 0, s>>>(p);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         wgs_set_error_message(cudaGetErrorString(e));

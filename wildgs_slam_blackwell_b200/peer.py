@@ -18,7 +18,7 @@ import torch.distributed as dist
 
 from . import _lib
 
-ALLREDUCE, REDUCE_SCATTER, ALLGATHER = 0, 1, 2
+ALLREDUCE, REDUCE_SCATTER, ALLGATHER, RENDEZVOUS = 0, 1, 2, 3
 
 
 class PeerMemory:
@@ -95,6 +95,10 @@ class PeerBucket(PeerMemory):
     def reduce_scatter(self, segments=None):
         """The slice of the (segmented) data this rank owns -- owned_pieces() -- receives the sum over the group."""
         self._exchange(REDUCE_SCATTER, segments)
+
+    def rendezvous(self):
+        """One-block peer barrier on the current stream (no data): see wgs_peer_exchange mode 3."""
+        self._exchange(RENDEZVOUS, [(0, 4)])
 
     def all_gather(self, target=None, segments=None):
         """Every rank's owned slice of `target` (another PeerMemory with the same segment layout; default: this bucket)
