@@ -291,3 +291,32 @@ def test_emulated_rank_runs_that_ranks_units_without_exchange():
             assert len(out["assignment"]) == 2
         for k in total:
             torch.testing.assert_close(total[k], ref_params[k].grad, rtol=1e-5, atol=1e-6)
+
+
+def test_owned_pieces_partition_the_segments_like_the_kernel():
+    """peer.owned_pieces: the host-side mirror of the exchange kernel's split (float4 granularity, ceil(n4 / world)
+    per rank over the segments laid end to end) -- the pieces of all ranks tile the segments exactly once."""
+    from wildgs_slam_blackwell_b200.peer import owned_pieces
+    for segments, world in (([(0, 4000)], 8), ([(0, 12), (64, 4), (128, 36)], 3), ([(256, 1000), (4096, 8)], 2),
+                            ([(0, 4)], 8), ([(0, 300_000 * 3), (1_048_576 * 3, 300_000 * 4)], 8)):
+        covered = []
+        for r in range(world):
+            pieces = owned_pieces(segments, r, world)
+            assert all(o % 4 == 0 and n % 4 == 0 and n > 0 for o, n in pieces)
+            covered += pieces
+        cells = sorted(x for o, n in covered for x in range(o, o + n, 4))
+        expect = sorted(x for o, n in segments for x in range(o, o + n, 4))
+        assert cells == expect                                   # every float4 exactly once
+        n4 = sum(n // 4 for _, n in segments)
+        per = -(-n4 // world)
+        sizes = [sum(n for _, n in owned_pieces(segments, r, world)) // 4 for r in range(world)]
+        assert sizes == [max(0, min(per, n4 - per * r)) for r in range(world)]
+
+
+def test_capacity_classes_are_powers_of_two_with_a_floor():
+    from wildgs_slam_blackwell_b200.arena import capacity_class
+    assert capacity_class(1) == capacity_class(16384) == 16384
+    assert capacity_class(16385) == 32768 and capacity_class(100_000) == 131072 and capacity_class(2_000_000) == 2097152
+    # BASELINE config 5's schedule enters five classes
+    sched = [int(round(100_000 * 20 ** (s / 39))) for s in range(40)]
+    assert len({capacity_class(p) for p in sched}) == 5
