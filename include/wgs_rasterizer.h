@@ -287,6 +287,12 @@ int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, ui
                       int32_t world, const uint64_t* seg_offsets, const uint64_t* seg_lengths, int32_t n_segments,
                       int32_t mode, void* cuda_stream);
 
+/* Launch shape of the exchange kernel: `blocks` CTAs of 512 threads, `unroll` float4 per thread and trip (bytes in flight
+ * on NVLink = blocks x 512 x unroll x 16).  Process-wide; EVERY rank must use the same setting for a given flag area (block
+ * b of one rank meets block b of the others).  Default 144 x 4; environment WGS_PEER_BLOCKS / WGS_PEER_UNROLL are read
+ * by the Python layer. */
+int wgs_peer_configure(int32_t blocks, int32_t unroll);
+
 int wgs_stage_timing(WgsContext* ctx, int enable);
 int wgs_stage_times(WgsContext* ctx, float* ms_out /* WGS_NUM_STAGES floats, host */);
 

@@ -67,7 +67,7 @@ EXPORTS = ("wgs_abi_version", "wgs_last_error", "wgs_context_create", "wgs_conte
            "wgs_workspace_sizes", "wgs_forward", "wgs_backward", "wgs_mark_visible", "wgs_export_binning",
            "wgs_export_geometry", "wgs_stage_timing", "wgs_stage_times", "wgs_camera_matrices", "wgs_set_async",
            "wgs_last_num_rendered", "wgs_set_chained_launch", "wgs_overflow_status", "wgs_count_pairs", "wgs_peer_flags_bytes",
-           "wgs_peer_allreduce", "wgs_peer_exchange")
+           "wgs_peer_allreduce", "wgs_peer_exchange", "wgs_peer_configure")
 NUM_STAGES = 8
 STAGE_NAMES = ("preprocess_fwd", "tile_scan", "scatter", "tile_sort", "render_fwd", "render_bwd", "preprocess_bwd",
                "reserved")
@@ -103,6 +103,7 @@ def load():
                                        C.c_uint64, C.c_void_p]
     lib.wgs_peer_exchange.argtypes = [C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_uint64, C.c_int32, C.c_int32,
                                       C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_int32, C.c_int32, C.c_void_p]
+    lib.wgs_peer_configure.argtypes = [C.c_int32, C.c_int32]
     lib.wgs_set_async.argtypes = [C.c_void_p, C.c_int]
     lib.wgs_set_chained_launch.argtypes = [C.c_int]
     lib.wgs_last_num_rendered.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]

@@ -317,6 +317,7 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
 
     PreBwdParams pb;
     pb.P = a->P; pb.D = a->sh_degree; pb.M = a->M; pb.W = a->width; pb.H = a->height; pb.accumulate = a->accumulate;
+    pb.strip = (row0 != 0 || row1 != gy) ? 1 : 0;
     pb.tanfovx = a->tanfovx; pb.tanfovy = a->tanfovy;
     pb.focal_y = a->height / (2.0f * a->tanfovy);
     pb.focal_x = a->width / (2.0f * a->tanfovx);

@@ -56,6 +56,7 @@ struct RenderBwdParams {
 struct PreBwdParams {
     int P, D, M, W, H, accumulate;
     int act;
+    int strip;                 // the backward of a tile-row strip (few visible Gaussians): the queued kernel variant
     const float* sh_rest;
     float* dL_dsh_rest;
     float *stat_grad_accum, *stat_denom, *stat_max_radii;   // fused densification statistics (may be null)

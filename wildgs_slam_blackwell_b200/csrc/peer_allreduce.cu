@@ -14,14 +14,16 @@
 namespace wgs {
 
 constexpr int PEER_MAX_WORLD = 16;
-constexpr int PEER_BLOCKS = 144;  // ~one CTA per SM: the kernel runs alone, what matters is bytes in flight on NVLink
+constexpr int PEER_MAX_BLOCKS = 592;  // flag area: one barrier slot set per block
 constexpr int PEER_THREADS = 512;
+// launch shape (wgs_peer_configure): blocks x 512 threads x U float4 per thread and trip = bytes in flight on NVLink
+static int g_peer_blocks = 144, g_peer_unroll = 4;
 
 constexpr int PEER_MAX_SEGMENTS = 12;
 
 struct PeerParams {
     float* buf[PEER_MAX_WORLD];        // this rank's mapping of every rank's buffer
-    uint32_t* flags[PEER_MAX_WORLD];   // ... and of every rank's flag array [PEER_BLOCKS][PEER_MAX_WORLD]
+    uint32_t* flags[PEER_MAX_WORLD];   // ... and of every rank's flag array [PEER_MAX_BLOCKS][PEER_MAX_WORLD]
     float* mc;                         // multicast mapping of the buffer (null: P2P path)
     int rank, world;
     int mode;                          // 0 allreduce, 1 reduce-scatter (sum of my slice -> my copy), 2 allgather (my slice -> all)
@@ -29,7 +31,7 @@ struct PeerParams {
     size_t seg_off4[PEER_MAX_SEGMENTS];   // the exchanged data: `nseg` pieces of the buffer (offset / length in float4),
     size_t seg_end4[PEER_MAX_SEGMENTS];   // laid end to end as one virtual array; seg_end4 = running end in that array
     size_t n4;                         // float4 elements of the virtual array
-    uint32_t* epochs;                  // [PEER_BLOCKS] in THIS rank's flag area: barrier generation of each block
+    uint32_t* epochs;                  // [PEER_MAX_BLOCKS] in THIS rank's flag area: barrier generation of each block
 };
 
 // virtual float4 index -> float4 offset inside the buffer
@@ -76,7 +78,7 @@ __device__ __forceinline__ void multimem_st(float* mc, float4 v) {
                  "f"(v.z), "f"(v.w) : "memory");
 }
 
-template <bool NVLS>
+template <bool NVLS, int U>   // U independent float4 per thread and trip: keeps U (x world) 16-B requests in flight
 __global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const __grid_constant__ PeerParams p) {
     // The barrier generation lives on the device (one counter per block, advanced by 2 per launch), so the
     // launch has no per-call host argument and can be replayed from a CUDA graph; all ranks launch equally often.
@@ -90,7 +92,6 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_allreduce_kernel(const __gr
     const size_t stride = (size_t)gridDim.x * PEER_THREADS;
     const bool reduce = p.mode != 2, spread = p.mode != 1;
     float4* const mine = reinterpret_cast<float4*>(p.buf[p.rank]);
-    constexpr int U = 4;  // independent float4 per thread and trip: keeps U (x world) 16-B requests in flight
     for (size_t i0 = begin + (size_t)blockIdx.x * PEER_THREADS + threadIdx.x; i0 < end; i0 += U * stride) {
         float4 s[U];
         size_t a[U];
@@ -146,7 +147,7 @@ extern "C" {
 void wgs_set_error_message(const char* msg);
 
 size_t wgs_peer_flags_bytes(void) {
-    return (size_t)wgs::PEER_BLOCKS * (wgs::PEER_MAX_WORLD + 1) * sizeof(uint32_t);  // flags + per-block generation
+    return (size_t)wgs::PEER_MAX_BLOCKS * (wgs::PEER_MAX_WORLD + 1) * sizeof(uint32_t);  // flags + per-block generation
 }
 
 int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, uint64_t multicast_ptr, int32_t rank,
@@ -182,20 +183,40 @@ int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, ui
         p.seg_end4[k] = run;
     }
     p.mc = (float*)multicast_ptr; p.rank = rank; p.world = world; p.n4 = run; p.mode = mode; p.nseg = n_segments;
-    p.epochs = p.flags[rank] + PEER_BLOCKS * PEER_MAX_WORLD;
+    p.epochs = p.flags[rank] + PEER_MAX_BLOCKS * PEER_MAX_WORLD;
     cudaStream_t s = (cudaStream_t)cuda_stream;
     // mode 3, rendezvous: ONE block runs the two flag barriers and moves nothing.  Put in front of an exchange whose
     // peers may arrive late (e.g. behind their own H2D copies), it does the waiting with one block instead of with the
     // whole exchange grid spinning on SM slots that a concurrent stream's kernels could use.
-    const int grid = mode == 3 ? 1 : PEER_BLOCKS;
+    const int grid = mode == 3 ? 1 : g_peer_blocks;
     if (mode == 3) { p.n4 = 0; p.mode = 0; }
-    if (p.mc) peer_allreduce_kernel<true><<<grid, PEER_THREADS, 0, s>>>(p);
-    else peer_allreduce_kernel<false><<<grid, PEER_THREADS, 0, s>>>(p);
+#define WGS_PEER_LAUNCH(U_)                                                                      \
+    do {                                                                                         \
+        if (p.mc) peer_allreduce_kernel<true, U_><<<grid, PEER_THREADS, 0, s>>>(p);              \
+        else peer_allreduce_kernel<false, U_><<<grid, PEER_THREADS, 0, s>>>(p);                  \
+    } while (0)
+    switch (g_peer_unroll) {
+        case 1: WGS_PEER_LAUNCH(1); break;
+        case 2: WGS_PEER_LAUNCH(2); break;
+        case 8: WGS_PEER_LAUNCH(8); break;
+        default: WGS_PEER_LAUNCH(4); break;
+    }
+#undef WGS_PEER_LAUNCH
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         wgs_set_error_message(cudaGetErrorString(e));
         return WGS_ERR_CUDA;
     }
+    return WGS_OK;
+}
+
+int wgs_peer_configure(int32_t blocks, int32_t unroll) {
+    if (blocks < 1 || blocks > wgs::PEER_MAX_BLOCKS || (unroll != 1 && unroll != 2 && unroll != 4 && unroll != 8)) {
+        wgs_set_error_message("wgs_peer_configure: blocks in [1, 592], unroll in {1, 2, 4, 8}");
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    wgs::g_peer_blocks = blocks;
+    wgs::g_peer_unroll = unroll;
     return WGS_OK;
 }
 

@@ -59,7 +59,8 @@ __device__ __forceinline__ void cov3d_natural(const float* s3, float mod, const 
 // through shared memory (sh_stage.cuh): coalesced cp.async in (rows of culled Gaussians skipped), each thread reads
 // its coefficients and leaves its dL_dsh there in place, coalesced write-back (zeros for culled rows).  Per-thread
 // row access to global memory (192-B stride) moved 1.9 GB for 1.2 GB of algorithmic traffic at config 4.
-template <bool STAGED>
+// QUEUED (tile-row strips, where few Gaussians are visible): see below; otherwise every thread takes its own Gaussian.
+template <bool STAGED, bool QUEUED>
 __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS) preprocess_bwd_kernel(const __grid_constant__ PreBwdParams p) {
     pdl_wait();     // first statement: see common.cuh
     pdl_trigger();
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
     // others sat in the next barrier (ncu: 16 % issue utilisation, 24 of 34 warp-cycles in the barrier).  Invisible
     // Gaussians have nothing to add to an accumulating backward; an overwriting one zero-fills their outputs here.
     const int nchunks = (p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS;
-    __shared__ int s_queue[2 * WGS_PRE_BWD_THREADS];
+    __shared__ int s_queue[QUEUED ? 2 * WGS_PRE_BWD_THREADS : 1];
     __shared__ int s_wcount[WGS_PRE_BWD_THREADS / 32];
     int chunk = blockIdx.x, qn = 0;   // qn: queued Gaussians (the same value in every thread)
     for (;;) {
@@ -91,7 +92,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
     bool live, work;
     int idx, rad = 0;
     uint2 rect = make_uint2(0u, 0u);
-    if (STAGED) {
+    if (STAGED || !QUEUED) {
         if (chunk >= nchunks) break;
         const int gidx = chunk * WGS_PRE_BWD_THREADS + threadIdx.x;
         wrow0 = chunk * WGS_PRE_BWD_THREADS + (threadIdx.x & ~31);
@@ -525,7 +526,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
 }
 
 int configure_preprocess_bwd() {
-    return (int)cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    return (int)cudaFuncSetAttribute(preprocess_bwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sh_stage_bytes(SH_STAGE_MAX_M, WGS_PRE_BWD_THREADS));
 }
 
@@ -544,9 +545,11 @@ void launch_preprocess_bwd(const PreBwdParams& p, cudaStream_t s) {
     }
     const int blocks = min((p.P + WGS_PRE_BWD_THREADS - 1) / WGS_PRE_BWD_THREADS, slots);
     if (p.sh && p.M > 1 && p.M <= SH_STAGE_MAX_M)
-        launch_chained(preprocess_bwd_kernel<true>, blocks, WGS_PRE_BWD_THREADS, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M, WGS_PRE_BWD_THREADS), s, p);
+        launch_chained(preprocess_bwd_kernel<true, false>, blocks, WGS_PRE_BWD_THREADS, sh_stage_bytes(p.sh_rest ? p.M - 1 : p.M, WGS_PRE_BWD_THREADS), s, p);
+    else if (p.strip)   // a strip keeps a fraction of the Gaussians: queue the visible ones (whole views: 32 vs 28 us at config 2)
+        launch_chained(preprocess_bwd_kernel<false, true>, blocks, WGS_PRE_BWD_THREADS, 0, s, p);
     else
-        launch_chained(preprocess_bwd_kernel<false>, blocks, WGS_PRE_BWD_THREADS, 0, s, p);
+        launch_chained(preprocess_bwd_kernel<false, false>, blocks, WGS_PRE_BWD_THREADS, 0, s, p);
 }
 
 }  // namespace wgs

@@ -49,6 +49,18 @@ class PeerMemory:
         return self.n * 4
 
 
+def configure(blocks=None, unroll=None):
+    """Launch shape of the exchange kernel (wgs_peer_configure); every rank must call it with the same values.  Defaults:
+    environment WGS_PEER_BLOCKS / WGS_PEER_UNROLL, else the library's 144 x 4."""
+    import os
+    b = int(blocks if blocks is not None else os.environ.get("WGS_PEER_BLOCKS", 0) or 0)
+    u = int(unroll if unroll is not None else os.environ.get("WGS_PEER_UNROLL", 0) or 0)
+    if b or u:
+        rc = _lib.load().wgs_peer_configure(b or 144, u or 4)
+        if rc != _lib.WGS_OK:
+            raise RuntimeError(f"wgs_peer_configure failed ({rc}): {_lib.last_error()}")
+
+
 def owned_pieces(segments, rank, world):
     """The part of the virtual array (the `segments` = [(offset, length)] in floats laid end to end) rank `rank` owns in a
     reduce-scatter / allgather: a list of (offset, length) pieces of the buffer.  Mirrors the kernel's split (float4
@@ -67,8 +79,13 @@ def owned_pieces(segments, rank, world):
 
 
 class PeerBucket(PeerMemory):
+    _configured = False
+
     def __init__(self, n_floats, device, group=None, use_multicast=True):
         flag_floats = int(_lib.load().wgs_peer_flags_bytes()) // 4
+        if not PeerBucket._configured:
+            PeerBucket._configured = True
+            configure()                                        # environment overrides, once per process
         super().__init__(n_floats, device, group, use_multicast, extra_floats=flag_floats)
         self._flags = (C.c_uint64 * self.world)(*[p + 4 * self._extra_off for p in self._buf_ptrs])
 
