@@ -289,8 +289,9 @@ int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, ui
 
 /* Launch shape of the exchange kernel: `blocks` CTAs of 512 threads, `unroll` float4 per thread and trip (bytes in flight
  * on NVLink = blocks x 512 x unroll x 16).  Process-wide; EVERY rank must use the same setting for a given flag area (block
- * b of one rank meets block b of the others).  Default 144 x 4; environment WGS_PEER_BLOCKS / WGS_PEER_UNROLL are read
- * by the Python layer. */
+ * b of one rank meets block b of the others).  0 selects the measured default: 48 x 2 on the NVSwitch-multimem path (the
+ * switch is the bound: 59 / 146 / 290 us for 16.8 / 56 / 128 MB at 8 GPUs, 775 GB/s bus bandwidth; NCCL 100 / 244 / 390),
+ * 144 x 4 on the peer load/store path.  Environment WGS_PEER_BLOCKS / WGS_PEER_UNROLL are read by the Python layer. */
 int wgs_peer_configure(int32_t blocks, int32_t unroll);
 
 int wgs_stage_timing(WgsContext* ctx, int enable);

@@ -12,11 +12,13 @@ rank = int(os.environ["RANK"]); local = int(os.environ["LOCAL_RANK"]); world = i
 torch.cuda.set_device(local); dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 res = {}
+SWEEP_BLOCKS = [int(x) for x in os.environ.get("SWEEP_BLOCKS", "72,144,296,592").split(",")]
+SWEEP_UNROLL = [int(x) for x in os.environ.get("SWEEP_UNROLL", "2,4,8").split(",")]
 for n in (4_200_000, 14_000_000, 32_000_000):
     b = PeerBucket(n, dev, use_multicast=True)
     b.flat.normal_()
-    for blocks in (72, 144, 296, 592):
-        for unroll in (2, 4, 8):
+    for blocks in SWEEP_BLOCKS:
+        for unroll in SWEEP_UNROLL:
             dist.barrier(); torch.cuda.synchronize()
             peer.configure(blocks, unroll)
             ts = []

@@ -16,8 +16,11 @@ namespace wgs {
 constexpr int PEER_MAX_WORLD = 16;
 constexpr int PEER_MAX_BLOCKS = 592;  // flag area: one barrier slot set per block
 constexpr int PEER_THREADS = 512;
-// launch shape (wgs_peer_configure): blocks x 512 threads x U float4 per thread and trip = bytes in flight on NVLink
-static int g_peer_blocks = 144, g_peer_unroll = 4;
+// launch shape (wgs_peer_configure): blocks x 512 threads x U float4 per thread and trip = bytes in flight on NVLink.
+// 0 = the measured defaults: the NVLS path is bound by the switch and runs fastest with little in flight (8 x B200,
+// profiles/r02o_tune_peer_n8*.json: 48 x 2 -> 59 / 146 / 290 us for 16.8 / 56 / 128 MB, 144 x 4 -> 68 / 170 / 318,
+// 592 x 8 -> 102 / 203 / 411; NCCL 100 / 244 / 390); the P2P path keeps every peer's loads in flight with 144 x 4.
+static int g_peer_blocks = 0, g_peer_unroll = 0;
 
 constexpr int PEER_MAX_SEGMENTS = 12;
 
@@ -188,14 +191,16 @@ int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, ui
     // mode 3, rendezvous: ONE block runs the two flag barriers and moves nothing.  Put in front of an exchange whose
     // peers may arrive late (e.g. behind their own H2D copies), it does the waiting with one block instead of with the
     // whole exchange grid spinning on SM slots that a concurrent stream's kernels could use.
-    const int grid = mode == 3 ? 1 : g_peer_blocks;
+    const int blocks = g_peer_blocks ? g_peer_blocks : (p.mc ? 48 : 144);
+    const int unroll = g_peer_unroll ? g_peer_unroll : (p.mc ? 2 : 4);
+    const int grid = mode == 3 ? 1 : blocks;
     if (mode == 3) { p.n4 = 0; p.mode = 0; }
 #define WGS_PEER_LAUNCH(U_)                                                                      \
     do {                                                                                         \
         if (p.mc) peer_allreduce_kernel<true, U_><<<grid, PEER_THREADS, 0, s>>>(p);              \
         else peer_allreduce_kernel<false, U_><<<grid, PEER_THREADS, 0, s>>>(p);                  \
     } while (0)
-    switch (g_peer_unroll) {
+    switch (unroll) {
         case 1: WGS_PEER_LAUNCH(1); break;
         case 2: WGS_PEER_LAUNCH(2); break;
         case 8: WGS_PEER_LAUNCH(8); break;
@@ -211,8 +216,8 @@ int wgs_peer_exchange(const uint64_t* buffer_ptrs, const uint64_t* flag_ptrs, ui
 }
 
 int wgs_peer_configure(int32_t blocks, int32_t unroll) {
-    if (blocks < 1 || blocks > wgs::PEER_MAX_BLOCKS || (unroll != 1 && unroll != 2 && unroll != 4 && unroll != 8)) {
-        wgs_set_error_message("wgs_peer_configure: blocks in [1, 592], unroll in {1, 2, 4, 8}");
+    if (blocks < 0 || blocks > wgs::PEER_MAX_BLOCKS || (unroll != 0 && unroll != 1 && unroll != 2 && unroll != 4 && unroll != 8)) {
+        wgs_set_error_message("wgs_peer_configure: blocks in [0, 592], unroll in {0, 1, 2, 4, 8} (0 = default)");
         return WGS_ERR_INVALID_ARGUMENT;
     }
     wgs::g_peer_blocks = blocks;

@@ -51,12 +51,12 @@ class PeerMemory:
 
 def configure(blocks=None, unroll=None):
     """Launch shape of the exchange kernel (wgs_peer_configure); every rank must call it with the same values.  Defaults:
-    environment WGS_PEER_BLOCKS / WGS_PEER_UNROLL, else the library's 144 x 4."""
+    environment WGS_PEER_BLOCKS / WGS_PEER_UNROLL, else (0) the library's measured defaults per path."""
     import os
     b = int(blocks if blocks is not None else os.environ.get("WGS_PEER_BLOCKS", 0) or 0)
     u = int(unroll if unroll is not None else os.environ.get("WGS_PEER_UNROLL", 0) or 0)
     if b or u:
-        rc = _lib.load().wgs_peer_configure(b or 144, u or 4)
+        rc = _lib.load().wgs_peer_configure(b, u)
         if rc != _lib.WGS_OK:
             raise RuntimeError(f"wgs_peer_configure failed ({rc}): {_lib.last_error()}")
 
