@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--streams", type=int, default=2)
     ap.add_argument("--eager", action="store_true")
     ap.add_argument("--small", action="store_true", help="10 k -> 200 k over 12 steps (smoke)")
+    ap.add_argument("--fixed-rows", type=int, default=0, help="one stage at this row count instead of the schedule")
+    ap.add_argument("--emulate", type=int, default=0, help="with --fixed-rows: per-rank compute of an N-rank step (rank 0), no exchange")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -40,6 +42,10 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     kw = dict(p0=10_000, p1=200_000, steps=12, prune_every=4) if a.small else {}
+    if a.fixed_rows:
+        kw = dict(sched=[a.fixed_rows])
+        if a.emulate:
+            kw["emulate"] = (0, a.emulate)
     wl = Config5Workload(dev, peer=a.peer, streams=a.streams, sharded=a.sharded, use_graph=not a.eager, **kw)
     recs = wl.run(reps=a.reps)
     if rank == 0:

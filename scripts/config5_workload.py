@@ -49,11 +49,13 @@ def schedule(p0=100_000, p1=2_000_000, steps=40):
 
 class Config5Workload:
     def __init__(self, dev, p0=100_000, p1=2_000_000, steps=40, n_views=16, W=640, H=480, peer="auto", plan="balanced",
-                 streams=2, sharded=False, prune_every=10, prune_frac=0.05, use_graph=True, seed=1005):
+                 streams=2, sharded=False, prune_every=10, prune_frac=0.05, use_graph=True, seed=1005, emulate=None,
+                 sched=None):
         self.dev, self.W, self.H, self.n_views = dev, W, H, n_views
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
-        self.sched = schedule(p0, p1, steps)
+        self.sched = list(sched) if sched is not None else schedule(p0, p1, steps)
+        p0 = self.sched[0]
         self.prune_every, self.prune_frac, self.use_graph = prune_every, prune_frac, use_graph
         self.peer = peer if self.world > 1 else "off"
         self.sharded = sharded and self.world > 1
@@ -71,7 +73,7 @@ class Config5Workload:
                                    capturable=True)
         self.trainer = WindowTrainer(self.arena.params, sink_names=SINK_NAMES, peer=self.peer != "off",
                                      peer_mode=self.peer if self.peer != "off" else "auto", densify_stats=True,
-                                     streams=streams, capacity=self.arena.capacity,
+                                     streams=streams, capacity=self.arena.capacity, emulate=emulate,
                                      exchange="reduce_scatter" if self.sharded else "allreduce")
         self.bucket_allocations = 1
         rng = np.random.default_rng(seed + 500)

@@ -398,26 +398,115 @@ __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __
     for (int i = tid; i < n; i += SMALL_THREADS) seg[i] = out[i];
 }
 
+// Tile segments longer than SMALL_MAX: persistent CTAs (one per SM, 224 KB of shared memory) take them from the list
+// the scan kernel wrote.  Up to LARGE_MAX entries the same bucket sort as above runs with NBL buckets over the keys as
+// they lie in global memory (L2-resident: the scatter kernel has just written them) -- min/max pass, histogram pass,
+// scan, scatter pass into shared memory through per-bucket cursors, insertion sort inside the buckets (expected
+// occupancy <= 3), write-back.  A 2 M-Gaussian scene at 640x480 has ~600 such tiles per view: the bitonic network this
+// replaces took 0.5 ms of a 1.3 ms view there (profiles/r02r_c5_rank0_launches.csv).  A bucket above
+// LARGE_BUCKET_LIMIT (pathological depth distribution) or a segment above LARGE_MAX falls back to the network.
+constexpr int NBL = 8192;
+constexpr int LARGE_BUCKET_LIMIT = 64;
+constexpr size_t LARGE_SMEM = (size_t)LARGE_MAX * 8 + (size_t)NBL * 4;
+
 __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __grid_constant__ BinParams p) {
     pdl_wait();     // first statement: see common.cuh
     pdl_trigger();
     extern __shared__ unsigned long long lkeys[];
+    uint32_t* const lhist = reinterpret_cast<uint32_t*>(lkeys + LARGE_MAX);
+    __shared__ uint32_t wsum[LARGE_THREADS / 32];
+    __shared__ uint32_t s_min, s_max, s_maxcnt;
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int n_large = (int)p.tile.misc[MISC_N_LARGE];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int q = blockIdx.x; q < n_large; q += gridDim.x) {
         const uint2 r = p.tile.ranges[p.tile.large_list[q]];
         const int n = (int)(r.y - r.x);
         unsigned long long* seg = p.bucket + r.x;
-        if (n <= LARGE_MAX) {
-            for (int i = threadIdx.x; i < n; i += LARGE_THREADS) lkeys[i] = seg[i];
+        if (n > LARGE_MAX) {
             __syncthreads();
-            bitonic_sort(lkeys, n, threadIdx.x, LARGE_THREADS);
-            for (int i = threadIdx.x; i < n; i += LARGE_THREADS) seg[i] = lkeys[i];
-            __syncthreads();
-        } else {
-            __syncthreads();
-            bitonic_sort(seg, n, threadIdx.x, LARGE_THREADS);  // in global memory (L2-resident)
+            bitonic_sort(seg, n, tid, LARGE_THREADS);  // in global memory (L2-resident)
+            continue;
         }
+        // pass 1: depth range of the segment
+        uint32_t lo = 0xffffffffu, hi = 0u;
+        for (int i = tid; i < n; i += LARGE_THREADS) {
+            const uint32_t d = (uint32_t)(__ldcg(seg + i) >> 32);
+            lo = min(lo, d);
+            hi = max(hi, d);
+        }
+        for (int i = tid; i < NBL; i += LARGE_THREADS) lhist[i] = 0;
+        if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; }
+        __syncthreads();
+        lo = __reduce_min_sync(0xffffffffu, lo);
+        hi = __reduce_max_sync(0xffffffffu, hi);
+        if (lane == 0) { atomicMin(&s_min, lo); atomicMax(&s_max, hi); }
+        __syncthreads();
+        const uint32_t kmin = s_min;
+        const float scale = (float)NBL / ((float)(s_max - kmin) + 1.0f);
+        // pass 2: histogram (monotone non-decreasing bucket map, as in the small kernel)
+        for (int i = tid; i < n; i += LARGE_THREADS) {
+            const uint32_t d = (uint32_t)(__ldcg(seg + i) >> 32);
+            atomicAdd(&lhist[min((uint32_t)((float)(d - kmin) * scale), (uint32_t)(NBL - 1))], 1u);
+        }
+        __syncthreads();
+        // exclusive scan in place (NBL / LARGE_THREADS consecutive buckets per thread) + largest bucket
+        {
+            constexpr int BPT = NBL / LARGE_THREADS;
+            uint32_t c[BPT], v = 0, mx = 0;
+#pragma unroll
+            for (int k = 0; k < BPT; k++) { c[k] = lhist[BPT * tid + k]; v += c[k]; mx = max(mx, c[k]); }
+            const uint32_t mine = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += u;
+            }
+            if (lane == 31) wsum[warp] = v;
+            mx = __reduce_max_sync(0xffffffffu, mx);
+            if (lane == 0) atomicMax(&s_maxcnt, mx);
+            __syncthreads();
+            if (warp == 0) {
+                uint32_t w = wsum[lane];
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t u = __shfl_up_sync(0xffffffffu, w, o);
+                    if (lane >= o) w += u;
+                }
+                wsum[lane] = w;
+            }
+            __syncthreads();
+            uint32_t excl = (warp ? wsum[warp - 1] : 0u) + v - mine;
+#pragma unroll
+            for (int k = 0; k < BPT; k++) { lhist[BPT * tid + k] = excl; excl += c[k]; }
+        }
+        __syncthreads();
+        if (s_maxcnt > (uint32_t)LARGE_BUCKET_LIMIT) {
+            for (int i = tid; i < n; i += LARGE_THREADS) lkeys[i] = seg[i];
+            __syncthreads();
+            bitonic_sort(lkeys, n, tid, LARGE_THREADS);
+        } else {
+            // pass 3: scatter through the cursors (lhist[b] ends at the END of bucket b)
+            for (int i = tid; i < n; i += LARGE_THREADS) {
+                const unsigned long long key = __ldcg(seg + i);
+                const uint32_t d = (uint32_t)(key >> 32);
+                const uint32_t bkt = min((uint32_t)((float)(d - kmin) * scale), (uint32_t)(NBL - 1));
+                lkeys[atomicAdd(&lhist[bkt], 1u)] = key;
+            }
+            __syncthreads();
+            for (int bkt = tid; bkt < NBL; bkt += LARGE_THREADS) {
+                const int s0 = bkt ? (int)lhist[bkt - 1] : 0, e0 = (int)lhist[bkt];
+                for (int i = s0 + 1; i < e0; i++) {  // insertion sort of lkeys[s0, e0): full 64-bit compare
+                    const unsigned long long k = lkeys[i];
+                    int j = i - 1;
+                    while (j >= s0 && lkeys[j] > k) { lkeys[j + 1] = lkeys[j]; j--; }
+                    lkeys[j + 1] = k;
+                }
+            }
+            __syncthreads();
+        }
+        for (int i = tid; i < n; i += LARGE_THREADS) seg[i] = lkeys[i];
+        __syncthreads();
     }
 }
 
@@ -485,7 +574,7 @@ void launch_scatter(const BinParams& p, cudaStream_t s) {
 
 void launch_tile_sorts(const BinParams& p, int num_sms, cudaStream_t s) {
     launch_chained(tile_sort_small_kernel, p.tiles, SMALL_THREADS, 0, s, p);
-    launch_chained(tile_sort_large_kernel, num_sms, LARGE_THREADS, LARGE_MAX * 8, s, p);
+    launch_chained(tile_sort_large_kernel, num_sms, LARGE_THREADS, LARGE_SMEM, s, p);
 }
 
 void launch_export_binning(const BinParams& p, const ImageView& image, int W, int H, unsigned long long* keys,
@@ -506,7 +595,7 @@ void launch_export_geometry(int P, const GeomView& g, const int* radii, float* d
 
 int configure_binning() {
     return (int)cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     LARGE_MAX * 8);
+                                     (int)LARGE_SMEM);
 }
 
 }  // namespace wgs
