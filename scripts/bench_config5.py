@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--streams", type=int, default=2)
     ap.add_argument("--eager", action="store_true")
     ap.add_argument("--small", action="store_true", help="10 k -> 200 k over 12 steps (smoke)")
+    ap.add_argument("--profile-last", action="store_true", help="cudaProfilerStart before the timed steps of the last stage")
+    ap.add_argument("--stop-at", type=int, default=0, help="cut the schedule after this many growth steps")
     ap.add_argument("--fixed-rows", type=int, default=0, help="one stage at this row count instead of the schedule")
     ap.add_argument("--emulate", type=int, default=0, help="with --fixed-rows: per-rank compute of an N-rank step (rank 0), no exchange")
     a = ap.parse_args()
@@ -46,8 +48,11 @@ def main():
         kw = dict(sched=[a.fixed_rows])
         if a.emulate:
             kw["emulate"] = (0, a.emulate)
+    if a.stop_at:
+        from config5_workload import schedule
+        kw["sched"] = schedule()[:a.stop_at]
     wl = Config5Workload(dev, peer=a.peer, streams=a.streams, sharded=a.sharded, use_graph=not a.eager, **kw)
-    recs = wl.run(reps=a.reps)
+    recs = wl.run(reps=a.reps, profile_last=a.profile_last)
     if rank == 0:
         stages = [recs[i] for i in sorted({0, len(recs) // 4, len(recs) // 2, 3 * len(recs) // 4, len(recs) - 1})]
         print(json.dumps({

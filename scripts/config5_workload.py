@@ -162,7 +162,7 @@ class Config5Workload:
         self._means2D = torch.zeros(a.P, 3, device=self.dev, requires_grad=True)
 
     # ---- the whole schedule ----
-    def run(self, reps=3, log=None):
+    def run(self, reps=3, log=None, profile_last=False):
         """Returns one record per growth step: rows, ms per window step (max over ranks, median of `reps` timed replays
         after one untimed), ms of the densify/prune that led to it."""
         flush = torch.zeros((512 << 20) // 4, device=self.dev)
@@ -173,6 +173,9 @@ class Config5Workload:
             self.grow_to(rows, prune=(s > 0 and s % self.prune_every == 0))
             e1.record()
             self.step()                                 # untimed (capture happens here)
+            if profile_last and s == len(self.sched) - 1:
+                torch.cuda.synchronize()
+                torch.cuda.profiler.start()             # ncu --profile-from-start off: only the last stage's steps
             times = []
             for _ in range(reps):
                 flush.add_(1)

@@ -75,6 +75,33 @@ def test_very_long_tile_lists_use_the_large_sort():
     np.testing.assert_array_equal(ours["st_ranges"].view(np.uint32), o["st_ranges"])
 
 
+@pytest.mark.parametrize("P, W, H, sigma", [(6000, 96, 64, 4e-3), (40000, 48, 32, 2e-2), (6000, 96, 64, 2e-4), (40000, 48, 32, 2e-4)])
+def test_clustered_depths_sort_like_the_reference(P, W, H, sigma):
+    """Two narrow depth clusters per tile (a foreground sheet in front of a far one, plus exact clones: what densification
+    produces and what a fronto-parallel surface looks like) put hundreds of entries into a few buckets of the per-tile
+    bucket sort -- the per-bucket warp sort (17..256 entries) and the whole-segment fallback (> 256) must give the
+    reference's order (stable on equal depths = ascending id); small tiles (<= 4096 entries) and long ones."""
+    g, cams, _ = scenes.make_scene(P, W, H, 0, seed=41)
+    g = {k: (v.copy() if hasattr(v, "copy") else v) for k, v in g.items()}
+    cam = cams[0]
+    # (sigma 4e-3 / 2e-2: ~60 entries per bucket -> the warp sort; 2e-4: everything in one or two buckets -> the fallback)
+    # move every Gaussian onto one of two planes of constant view-space depth (+ a tiny spread), keep its pixel position
+    V = cam["viewmatrix"].reshape(4, 4)                       # row-vector convention: p_view = [p, 1] @ V
+    pv = np.concatenate([g["means3D"], np.ones((P, 1), np.float32)], 1) @ V
+    rng = np.random.default_rng(41)
+    z_new = np.where(rng.random(P) < 0.5, 2.0, 9.0).astype(np.float32) + rng.normal(0, sigma, P).astype(np.float32)
+    pv[:, :3] *= (z_new / np.maximum(pv[:, 2], 1e-3))[:, None]
+    g["means3D"] = (pv @ np.linalg.inv(V))[:, :3].astype(np.float32)
+    g["means3D"][P // 2:P // 2 + P // 8] = g["means3D"][:P // 8]           # exact clones: equal depth keys
+    o = cpu_oracle.forward_backward(g, cam, None, export=True)
+    lens = o["st_ranges"][:, 1] - o["st_ranges"][:, 0]
+    assert (lens.max() > 4096) == (P == 40000)
+    ours = util.run_ours(g, cam, None)
+    np.testing.assert_array_equal(ours["st_ranges"].view(np.uint32), o["st_ranges"])
+    np.testing.assert_array_equal(ours["st_point_list_keys"].view(np.uint64), o["st_point_list_keys"])
+    np.testing.assert_array_equal(ours["st_point_list"].view(np.uint32), o["st_point_list"])
+
+
 def test_mark_visible_matches_oracle():
     g, cams, _ = scenes.make_scene(5000, 64, 64, 0, seed=5)
     s = util.settings_from_cam(cams[0], 0)

@@ -281,6 +281,35 @@ __device__ __forceinline__ void bitonic_sort(unsigned long long* a, int n, int t
     }
 }
 
+// One warp sorts a[0, c), c <= 32 * MAXPL, keys distinct (the Gaussian id sits in the low word): every lane counts,
+// for its entries, the keys that are smaller (broadcast reads of a[j]) and then stores each entry at its rank.  For the
+// buckets that a cluster of near-equal depths fills (a foreground object in front of a far wall puts two narrow depth
+// clusters into a tile's linear bucket map; densification clones start at identical positions): c^2 / 32 steps on a
+// warp instead of c^2 / 2 on one thread or a whole-segment comparison network.
+template <int MAXPL>
+__device__ __forceinline__ void warp_rank_sort(unsigned long long* a, int c, int lane) {
+    unsigned long long key[MAXPL];
+    int rank[MAXPL];
+#pragma unroll
+    for (int e = 0; e < MAXPL; e++) {
+        const int i = lane + 32 * e;
+        key[e] = i < c ? a[i] : ~0ull;
+        rank[e] = 0;
+    }
+    for (int j = 0; j < c; j++) {
+        const unsigned long long kj = a[j];
+#pragma unroll
+        for (int e = 0; e < MAXPL; e++) rank[e] += kj < key[e] ? 1 : 0;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int e = 0; e < MAXPL; e++)
+        if (lane + 32 * e < c) a[rank[e]] = key[e];
+    __syncwarp();
+}
+constexpr int LIGHT_BUCKET = 16;   // up to here: insertion sort by the bucket's thread
+constexpr int HEAVY_BUCKET = 256;  // up to here: warp_rank_sort<8>; above: comparison network over the whole segment
+
 // One CTA sorts one tile segment of up to SMALL_MAX entries.  Depth keys inside a tile are spread
 // over a range, so instead of a comparison network the segment is bucketed: a monotone linear map
 // of the depth bits between the tile's min and max onto NB buckets (shared-memory histogram whose
@@ -288,19 +317,19 @@ __device__ __forceinline__ void bitonic_sort(unsigned long long* a, int n, int t
 // histogram, a scatter into shared memory, and an insertion sort inside every bucket that
 // received more than one entry (full 64-bit compare, so equal depths end up in ascending-id
 // order exactly like the reference's stable radix sort).  Expected bucket occupancy is < 1 for
-// the typical tile and <= 4 at SMALL_MAX; a pathological depth distribution (some bucket holding
-// more than BUCKET_LIMIT entries) falls back to the bitonic network on the same buffer.
+// the typical tile and <= 4 at SMALL_MAX; buckets above LIGHT_BUCKET entries are sorted by a warp each
+// (warp_rank_sort), and a bucket above HEAVY_BUCKET by the CTA's bitonic network over that bucket alone.
 constexpr int NB = 1024;
-constexpr int BUCKET_LIMIT = 32;
 constexpr int EPT = SMALL_MAX / SMALL_THREADS;  // entries per thread
 
-__global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __grid_constant__ BinParams p) {
+__global__ void __launch_bounds__(SMALL_THREADS, 3) tile_sort_small_kernel(const __grid_constant__ BinParams p) {
     pdl_wait();     // first statement: see common.cuh
     pdl_trigger();
     __shared__ unsigned long long out[SMALL_MAX];
     __shared__ uint32_t hist[NB];
     __shared__ uint32_t wsum[SMALL_THREADS / 32];
-    __shared__ uint32_t s_min, s_max, s_maxcnt;
+    __shared__ uint32_t s_min, s_max, s_maxcnt, n_heavy;
+    __shared__ uint16_t heavy[SMALL_MAX / HEAVY_BUCKET];   // buckets above HEAVY_BUCKET entries
     const uint2 r = p.tile.ranges[blockIdx.x];
     const int n = (int)(r.y - r.x);
     if (n < 2 || n > SMALL_MAX || p.tile.misc[MISC_OVERFLOW]) return;
@@ -320,7 +349,7 @@ __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __
         }
     }
     for (int i = tid; i < NB; i += SMALL_THREADS) hist[i] = 0;
-    if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; }
+    if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; n_heavy = 0u; }
     __syncthreads();
     lo = __reduce_min_sync(0xffffffffu, lo);
     hi = __reduce_max_sync(0xffffffffu, hi);
@@ -369,15 +398,7 @@ __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __
         hist[2 * tid + 1] = excl + c0;
     }
     __syncthreads();
-    if (s_maxcnt > (uint32_t)BUCKET_LIMIT) {
-#pragma unroll
-        for (int e = 0; e < EPT; e++) {
-            const int i = tid + e * SMALL_THREADS;
-            if (i < n) out[i] = key[e];
-        }
-        __syncthreads();
-        bitonic_sort(out, n, tid, SMALL_THREADS);
-    } else {
+    {
 #pragma unroll
         for (int e = 0; e < EPT; e++) {
             const int i = tid + e * SMALL_THREADS;
@@ -386,6 +407,8 @@ __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __
         __syncthreads();
         for (int bkt = tid; bkt < NB; bkt += SMALL_THREADS) {
             const int s0 = (int)hist[bkt], e0 = bkt + 1 < NB ? (int)hist[bkt + 1] : n;
+            if (e0 - s0 > HEAVY_BUCKET) heavy[atomicAdd(&n_heavy, 1u)] = (uint16_t)bkt;
+            if (e0 - s0 > LIGHT_BUCKET) continue;
             for (int i = s0 + 1; i < e0; i++) {  // insertion sort of out[s0, e0)
                 const unsigned long long k = out[i];
                 int j = i - 1;
@@ -393,7 +416,20 @@ __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __
                 out[j + 1] = k;
             }
         }
+        if (s_maxcnt > (uint32_t)LIGHT_BUCKET) {   // (uniform) some bucket is not light: one warp per medium bucket
+            for (int bkt = warp; bkt < NB; bkt += SMALL_THREADS / 32) {
+                const int s0 = (int)hist[bkt], e0 = bkt + 1 < NB ? (int)hist[bkt + 1] : n;
+                if (e0 - s0 > LIGHT_BUCKET && e0 - s0 <= HEAVY_BUCKET) warp_rank_sort<HEAVY_BUCKET / 32>(out + s0, e0 - s0, lane);
+            }
+        }
         __syncthreads();
+        // heavy buckets (a pile of clones, a whole tile at one depth): the comparison network, over that bucket only
+        const int nh = (int)n_heavy;
+        for (int h = 0; h < nh; h++) {
+            const int bkt = (int)heavy[h];
+            const int s0 = (int)hist[bkt], e0 = bkt + 1 < NB ? (int)hist[bkt + 1] : n;
+            bitonic_sort(out + s0, e0 - s0, tid, SMALL_THREADS);
+        }
     }
     for (int i = tid; i < n; i += SMALL_THREADS) seg[i] = out[i];
 }
@@ -403,10 +439,10 @@ __global__ void __launch_bounds__(SMALL_THREADS) tile_sort_small_kernel(const __
 // they lie in global memory (L2-resident: the scatter kernel has just written them) -- min/max pass, histogram pass,
 // scan, scatter pass into shared memory through per-bucket cursors, insertion sort inside the buckets (expected
 // occupancy <= 3), write-back.  A 2 M-Gaussian scene at 640x480 has ~600 such tiles per view: the bitonic network this
-// replaces took 0.5 ms of a 1.3 ms view there (profiles/r02r_c5_rank0_launches.csv).  A bucket above
-// LARGE_BUCKET_LIMIT (pathological depth distribution) or a segment above LARGE_MAX falls back to the network.
+// replaces took 0.5 ms of a 1.3 ms view there (profiles/r02r_c5_rank0_launches.csv).  Buckets above LIGHT_BUCKET /
+// HEAVY_BUCKET entries are handled as in the small kernel; a segment above LARGE_MAX is sorted by the network in
+// global memory.
 constexpr int NBL = 8192;
-constexpr int LARGE_BUCKET_LIMIT = 64;
 constexpr size_t LARGE_SMEM = (size_t)LARGE_MAX * 8 + (size_t)NBL * 4;
 
 __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __grid_constant__ BinParams p) {
@@ -415,7 +451,8 @@ __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __
     extern __shared__ unsigned long long lkeys[];
     uint32_t* const lhist = reinterpret_cast<uint32_t*>(lkeys + LARGE_MAX);
     __shared__ uint32_t wsum[LARGE_THREADS / 32];
-    __shared__ uint32_t s_min, s_max, s_maxcnt;
+    __shared__ uint32_t s_min, s_max, s_maxcnt, n_heavy;
+    __shared__ uint16_t heavy[LARGE_MAX / HEAVY_BUCKET];
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int n_large = (int)p.tile.misc[MISC_N_LARGE];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -436,7 +473,7 @@ __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __
             hi = max(hi, d);
         }
         for (int i = tid; i < NBL; i += LARGE_THREADS) lhist[i] = 0;
-        if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; }
+        if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; n_heavy = 0u; }
         __syncthreads();
         lo = __reduce_min_sync(0xffffffffu, lo);
         hi = __reduce_max_sync(0xffffffffu, hi);
@@ -481,11 +518,7 @@ __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __
             for (int k = 0; k < BPT; k++) { lhist[BPT * tid + k] = excl; excl += c[k]; }
         }
         __syncthreads();
-        if (s_maxcnt > (uint32_t)LARGE_BUCKET_LIMIT) {
-            for (int i = tid; i < n; i += LARGE_THREADS) lkeys[i] = seg[i];
-            __syncthreads();
-            bitonic_sort(lkeys, n, tid, LARGE_THREADS);
-        } else {
+        {
             // pass 3: scatter through the cursors (lhist[b] ends at the END of bucket b)
             for (int i = tid; i < n; i += LARGE_THREADS) {
                 const unsigned long long key = __ldcg(seg + i);
@@ -496,12 +529,27 @@ __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __
             __syncthreads();
             for (int bkt = tid; bkt < NBL; bkt += LARGE_THREADS) {
                 const int s0 = bkt ? (int)lhist[bkt - 1] : 0, e0 = (int)lhist[bkt];
+                if (e0 - s0 > HEAVY_BUCKET) heavy[atomicAdd(&n_heavy, 1u)] = (uint16_t)bkt;
+                if (e0 - s0 > LIGHT_BUCKET) continue;
                 for (int i = s0 + 1; i < e0; i++) {  // insertion sort of lkeys[s0, e0): full 64-bit compare
                     const unsigned long long k = lkeys[i];
                     int j = i - 1;
                     while (j >= s0 && lkeys[j] > k) { lkeys[j + 1] = lkeys[j]; j--; }
                     lkeys[j + 1] = k;
                 }
+            }
+            if (s_maxcnt > (uint32_t)LIGHT_BUCKET) {   // medium buckets: one warp each
+                for (int bkt = warp; bkt < NBL; bkt += LARGE_THREADS / 32) {
+                    const int s0 = bkt ? (int)lhist[bkt - 1] : 0, e0 = (int)lhist[bkt];
+                    if (e0 - s0 > LIGHT_BUCKET && e0 - s0 <= HEAVY_BUCKET) warp_rank_sort<HEAVY_BUCKET / 32>(lkeys + s0, e0 - s0, lane);
+                }
+            }
+            __syncthreads();
+            const int nh = (int)n_heavy;
+            for (int h = 0; h < nh; h++) {   // heavy buckets: the comparison network over that bucket only
+                const int bkt = (int)heavy[h];
+                const int s0 = bkt ? (int)lhist[bkt - 1] : 0, e0 = (int)lhist[bkt];
+                bitonic_sort(lkeys + s0, e0 - s0, tid, LARGE_THREADS);
             }
             __syncthreads();
         }
