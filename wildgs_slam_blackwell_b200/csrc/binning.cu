@@ -307,8 +307,14 @@ __device__ __forceinline__ void warp_rank_sort(unsigned long long* a, int c, int
         if (lane + 32 * e < c) a[rank[e]] = key[e];
     __syncwarp();
 }
+// entries per lane sized to the bucket: the inner loop costs 1 + 3 MAXPL instructions per compared key
+__device__ __forceinline__ void warp_rank_sort_any(unsigned long long* a, int c, int lane) {
+    if (c <= 64) warp_rank_sort<2>(a, c, lane);
+    else if (c <= 128) warp_rank_sort<4>(a, c, lane);
+    else warp_rank_sort<8>(a, c, lane);
+}
 constexpr int LIGHT_BUCKET = 16;   // up to here: insertion sort by the bucket's thread
-constexpr int HEAVY_BUCKET = 256;  // up to here: warp_rank_sort<8>; above: comparison network over the whole segment
+constexpr int HEAVY_BUCKET = 256;  // up to here: warp_rank_sort (<= 8 entries per lane); above: comparison network over the whole segment
 
 // One CTA sorts one tile segment of up to SMALL_MAX entries.  Depth keys inside a tile are spread
 // over a range, so instead of a comparison network the segment is bucketed: a monotone linear map
@@ -328,8 +334,9 @@ __global__ void __launch_bounds__(SMALL_THREADS, 3) tile_sort_small_kernel(const
     __shared__ unsigned long long out[SMALL_MAX];
     __shared__ uint32_t hist[NB];
     __shared__ uint32_t wsum[SMALL_THREADS / 32];
-    __shared__ uint32_t s_min, s_max, s_maxcnt, n_heavy;
+    __shared__ uint32_t s_min, s_max, s_maxcnt, n_heavy, n_medium;
     __shared__ uint16_t heavy[SMALL_MAX / HEAVY_BUCKET];   // buckets above HEAVY_BUCKET entries
+    __shared__ uint16_t medium[SMALL_MAX / LIGHT_BUCKET];  // buckets of LIGHT_BUCKET + 1 .. HEAVY_BUCKET entries
     const uint2 r = p.tile.ranges[blockIdx.x];
     const int n = (int)(r.y - r.x);
     if (n < 2 || n > SMALL_MAX || p.tile.misc[MISC_OVERFLOW]) return;
@@ -349,7 +356,7 @@ __global__ void __launch_bounds__(SMALL_THREADS, 3) tile_sort_small_kernel(const
         }
     }
     for (int i = tid; i < NB; i += SMALL_THREADS) hist[i] = 0;
-    if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; n_heavy = 0u; }
+    if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; n_heavy = 0u; n_medium = 0u; }
     __syncthreads();
     lo = __reduce_min_sync(0xffffffffu, lo);
     hi = __reduce_max_sync(0xffffffffu, hi);
@@ -408,6 +415,7 @@ __global__ void __launch_bounds__(SMALL_THREADS, 3) tile_sort_small_kernel(const
         for (int bkt = tid; bkt < NB; bkt += SMALL_THREADS) {
             const int s0 = (int)hist[bkt], e0 = bkt + 1 < NB ? (int)hist[bkt + 1] : n;
             if (e0 - s0 > HEAVY_BUCKET) heavy[atomicAdd(&n_heavy, 1u)] = (uint16_t)bkt;
+            else if (e0 - s0 > LIGHT_BUCKET) medium[atomicAdd(&n_medium, 1u)] = (uint16_t)bkt;
             if (e0 - s0 > LIGHT_BUCKET) continue;
             for (int i = s0 + 1; i < e0; i++) {  // insertion sort of out[s0, e0)
                 const unsigned long long k = out[i];
@@ -416,10 +424,13 @@ __global__ void __launch_bounds__(SMALL_THREADS, 3) tile_sort_small_kernel(const
                 out[j + 1] = k;
             }
         }
-        if (s_maxcnt > (uint32_t)LIGHT_BUCKET) {   // (uniform) some bucket is not light: one warp per medium bucket
-            for (int bkt = warp; bkt < NB; bkt += SMALL_THREADS / 32) {
+        __syncthreads();
+        {   // medium buckets: one warp each
+            const int nm = (int)n_medium;
+            for (int m = warp; m < nm; m += SMALL_THREADS / 32) {
+                const int bkt = (int)medium[m];
                 const int s0 = (int)hist[bkt], e0 = bkt + 1 < NB ? (int)hist[bkt + 1] : n;
-                if (e0 - s0 > LIGHT_BUCKET && e0 - s0 <= HEAVY_BUCKET) warp_rank_sort<HEAVY_BUCKET / 32>(out + s0, e0 - s0, lane);
+                warp_rank_sort_any(out + s0, e0 - s0, lane);
             }
         }
         __syncthreads();
@@ -451,8 +462,10 @@ __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __
     extern __shared__ unsigned long long lkeys[];
     uint32_t* const lhist = reinterpret_cast<uint32_t*>(lkeys + LARGE_MAX);
     __shared__ uint32_t wsum[LARGE_THREADS / 32];
-    __shared__ uint32_t s_min, s_max, s_maxcnt, n_heavy;
+    __shared__ uint32_t s_min, s_max, s_maxcnt, n_heavy, n_medium;
     __shared__ uint16_t heavy[LARGE_MAX / HEAVY_BUCKET];
+    constexpr int MEDIUM_LIST = 1024;          // (2 KB: what the 227 KB of the SM leave; beyond that the buckets are scanned)
+    __shared__ uint16_t medium[MEDIUM_LIST];
     if (p.tile.misc[MISC_OVERFLOW]) return;
     const int n_large = (int)p.tile.misc[MISC_N_LARGE];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -473,7 +486,7 @@ __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __
             hi = max(hi, d);
         }
         for (int i = tid; i < NBL; i += LARGE_THREADS) lhist[i] = 0;
-        if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; n_heavy = 0u; }
+        if (tid == 0) { s_min = 0xffffffffu; s_max = 0u; s_maxcnt = 0u; n_heavy = 0u; n_medium = 0u; }
         __syncthreads();
         lo = __reduce_min_sync(0xffffffffu, lo);
         hi = __reduce_max_sync(0xffffffffu, hi);
@@ -529,7 +542,12 @@ __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __
             __syncthreads();
             for (int bkt = tid; bkt < NBL; bkt += LARGE_THREADS) {
                 const int s0 = bkt ? (int)lhist[bkt - 1] : 0, e0 = (int)lhist[bkt];
-                if (e0 - s0 > HEAVY_BUCKET) heavy[atomicAdd(&n_heavy, 1u)] = (uint16_t)bkt;
+                if (e0 - s0 > HEAVY_BUCKET) {
+                    heavy[atomicAdd(&n_heavy, 1u)] = (uint16_t)bkt;
+                } else if (e0 - s0 > LIGHT_BUCKET) {
+                    const uint32_t slot = atomicAdd(&n_medium, 1u);
+                    if (slot < (uint32_t)MEDIUM_LIST) medium[slot] = (uint16_t)bkt;
+                }
                 if (e0 - s0 > LIGHT_BUCKET) continue;
                 for (int i = s0 + 1; i < e0; i++) {  // insertion sort of lkeys[s0, e0): full 64-bit compare
                     const unsigned long long k = lkeys[i];
@@ -538,10 +556,18 @@ __global__ void __launch_bounds__(LARGE_THREADS) tile_sort_large_kernel(const __
                     lkeys[j + 1] = k;
                 }
             }
-            if (s_maxcnt > (uint32_t)LIGHT_BUCKET) {   // medium buckets: one warp each
+            __syncthreads();
+            if (n_medium <= (uint32_t)MEDIUM_LIST) {   // medium buckets: one warp each
+                const int nm = (int)n_medium;
+                for (int m = warp; m < nm; m += LARGE_THREADS / 32) {
+                    const int bkt = (int)medium[m];
+                    const int s0 = bkt ? (int)lhist[bkt - 1] : 0, e0 = (int)lhist[bkt];
+                    warp_rank_sort_any(lkeys + s0, e0 - s0, lane);
+                }
+            } else {                                   // (more of them than the list holds: scan the buckets)
                 for (int bkt = warp; bkt < NBL; bkt += LARGE_THREADS / 32) {
                     const int s0 = bkt ? (int)lhist[bkt - 1] : 0, e0 = (int)lhist[bkt];
-                    if (e0 - s0 > LIGHT_BUCKET && e0 - s0 <= HEAVY_BUCKET) warp_rank_sort<HEAVY_BUCKET / 32>(lkeys + s0, e0 - s0, lane);
+                    if (e0 - s0 > LIGHT_BUCKET && e0 - s0 <= HEAVY_BUCKET) warp_rank_sort_any(lkeys + s0, e0 - s0, lane);
                 }
             }
             __syncthreads();
