@@ -11,7 +11,8 @@ import torch.nn as nn
 
 from . import _lib
 
-EXPORTS = ("wgs_compact_workspace_bytes", "wgs_compact_plan", "wgs_compact_rows")
+EXPORTS = ("wgs_compact_workspace_bytes", "wgs_compact_plan", "wgs_compact_plan_static", "wgs_compact_rows")
+STATIC_MAX_ROWS = 1 << 24      # WGS_COMPACT_STATIC_MAX_ROWS
 MAX_TENSORS = 32
 
 
@@ -29,6 +30,7 @@ def _lib_compact():
         lib.wgs_compact_workspace_bytes.restype = C.c_size_t
         lib.wgs_compact_workspace_bytes.argtypes = [C.c_int32]
         lib.wgs_compact_plan.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.wgs_compact_plan_static.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.wgs_compact_rows.argtypes = [C.c_int32, C.c_void_p, C.POINTER(CompactTensor), C.c_int32, C.c_void_p]
         _proto_done = True
     return lib

@@ -4,6 +4,7 @@
 #include "../../include/wgs_compact.h"
 #include "../../include/wgs_rasterizer.h"
 #include "common.cuh"
+#include <mutex>
 
 namespace wgs {
 
@@ -144,6 +145,69 @@ int wgs_compact_plan(int32_t P, const uint8_t* keep, int32_t* dst_index, int32_t
     compact_scan_kernel<<<1, 1024, 0, s>>>(nb, sums, count);
     compact_index_kernel<<<nb, CP_BLOCK, 0, s>>>(P, keep, sums, dst_index);
     const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { wgs_set_error_message(cudaGetErrorString(e)); return WGS_ERR_CUDA; }
+    return WGS_OK;
+}
+
+// ---- wgs_compact_plan_static: the same plan with the block sums in library-owned static device memory ----
+// For callers that hold no allocator on the device they run on (see include/wgs_compact.h).  One array per GPU
+// that loads the library, resident until the process exits; sized for WGS_COMPACT_STATIC_MAX_ROWS rows.
+}  // extern "C"
+namespace wgs {
+constexpr int CP_STATIC_WORDS = WGS_COMPACT_STATIC_MAX_ROWS / CP_BLOCK + 2;
+static __device__ __align__(256) uint32_t g_static_block_sums[CP_STATIC_WORDS];
+
+// In host code `g_static_block_sums` is only a handle for the runtime's symbol table, not a device address, so it
+// is resolved once per device with cudaGetSymbolAddress (that device current) and the resolved pointer is what the
+// kernels receive.  No allocation: the array is part of the module image.
+constexpr int CP_MAX_DEVICES = 64;
+static uint32_t* g_static_ptr[CP_MAX_DEVICES] = {};
+static std::mutex g_static_mutex;
+
+static cudaError_t static_block_sums(uint32_t** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= CP_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_block_sums);
+        if (e != cudaSuccess) return e;
+        g_static_ptr[dev] = (uint32_t*)p;
+    }
+    *out = g_static_ptr[dev];
+    return cudaSuccess;
+}
+}  // namespace wgs
+extern "C" {
+
+int wgs_compact_plan_static(int32_t P, const uint8_t* keep, int32_t* dst_index, int32_t* count, void* cuda_stream) {
+    if (P < 0 || !count || (P > 0 && (!keep || !dst_index))) {
+        wgs_set_error_message("wgs_compact_plan_static: null pointer or negative P");
+        return WGS_ERR_INVALID_ARGUMENT;
+    }
+    if (P > WGS_COMPACT_STATIC_MAX_ROWS) {
+        wgs_set_error_message("wgs_compact_plan_static: P exceeds WGS_COMPACT_STATIC_MAX_ROWS (16777216 rows); "
+                              "use wgs_compact_plan with a caller-owned workspace");
+        return WGS_ERR_CAPACITY;
+    }
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    if (P == 0) {
+        const cudaError_t e0 = cudaMemsetAsync(count, 0, sizeof(int32_t), s);
+        if (e0 != cudaSuccess) { wgs_set_error_message(cudaGetErrorString(e0)); return WGS_ERR_CUDA; }
+        return WGS_OK;
+    }
+    uint32_t* sums = nullptr;
+    cudaError_t e = static_block_sums(&sums);   // first call on this device resolves the symbol (set-up)
+    if (e != cudaSuccess) { wgs_set_error_message(cudaGetErrorString(e)); return WGS_ERR_CUDA; }
+    // Nothing in the array has to start at zero: compact_count_kernel overwrites words [0, nb) -- every word the
+    // scan and the index kernel read -- so whatever the previous call left behind is never observed.
+    const int nb = (P + CP_BLOCK - 1) / CP_BLOCK;
+    compact_count_kernel<<<nb, CP_BLOCK, 0, s>>>(P, keep, sums);
+    compact_scan_kernel<<<1, 1024, 0, s>>>(nb, sums, count);
+    compact_index_kernel<<<nb, CP_BLOCK, 0, s>>>(P, keep, sums, dst_index);
+    e = cudaGetLastError();
     if (e != cudaSuccess) { wgs_set_error_message(cudaGetErrorString(e)); return WGS_ERR_CUDA; }
     return WGS_OK;
 }
