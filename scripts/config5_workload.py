@@ -159,6 +159,8 @@ class Config5Workload:
         before = self.trainer.bucket
         self.trainer.rebind(a.params, capacity=a.capacity)
         self.bucket_allocations += self.trainer.bucket is not before
+        if n_new:
+            self.trainer.reset_statistics()            # with arena.append: a new densification interval (:635-637)
         self._means2D = torch.zeros(a.P, 3, device=self.dev, requires_grad=True)
 
     # ---- the whole schedule ----

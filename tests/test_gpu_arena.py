@@ -53,8 +53,8 @@ class _TorchModel:
 
     def append(self, rows):      # densification_postfix / cat_tensors_to_optimizer
         self._surgery(lambda k, old: torch.cat([old, rows[k]], 0), lambda k, s: torch.cat([s, torch.zeros_like(rows[k])], 0))
-        n = rows["xyz"].shape[0]
-        self.stats = {k: torch.cat([v, torch.zeros(n, device=DEV)]) for k, v in self.stats.items()}
+        P = self.p["xyz"].shape[0]     # gaussian_model.py:635-637: all three re-created as zeros after every densify
+        self.stats = {k: torch.zeros(P, device=DEV) for k in self.stats}
 
     def prune(self, remove):     # prune_points / _prune_optimizer
         keep = ~remove
@@ -99,8 +99,15 @@ def test_arena_matches_the_torch_cat_boolean_index_procedure():
             bucket = GradBucket(arena.params, capacity=arena.capacity)
         else:
             bucket.retarget(arena.params)
-        arena.xyz_gradient_accum += 1.0                    # statistics travel with their rows
-        ref.stats["xyz_gradient_accum"] += 1.0
+        if n_new > 0:                                      # densification_postfix restarted the statistics of every row
+            assert all(float(getattr(arena, n).abs().max()) == 0.0 for n in GaussianArena.STATS)
+        rowval = torch.arange(arena.P, device=DEV, dtype=torch.float32) % 251 + s      # statistics travel with their rows
+        arena.xyz_gradient_accum += rowval[:, None] * 0.5
+        arena.denom += rowval[:, None]
+        torch.maximum(arena.max_radii2D, rowval * 2.0, out=arena.max_radii2D)
+        ref.stats["xyz_gradient_accum"] += rowval * 0.5
+        ref.stats["denom"] += rowval
+        ref.stats["max_radii2D"] = torch.maximum(ref.stats["max_radii2D"], rowval * 2.0)
         for _ in range(2):
             step_no += 1
             for i, k in enumerate(arena.names):
@@ -116,7 +123,8 @@ def test_arena_matches_the_torch_cat_boolean_index_procedure():
             # TERMS apart (|g| ~ 1 here), which is a large relative error where they cancel -> absolute tolerance
             torch.testing.assert_close(m, st["exp_avg"], rtol=1e-5, atol=2e-6)
             torch.testing.assert_close(v, st["exp_avg_sq"], rtol=1e-5, atol=1e-8)
-        torch.testing.assert_close(arena.xyz_gradient_accum.reshape(-1), ref.stats["xyz_gradient_accum"])
+        for n in GaussianArena.STATS:
+            assert torch.equal(getattr(arena, n).reshape(-1), ref.stats[n]), f"{n} at stage {s}"
     assert arena.allocations == 3 and ptr_changes == 2 and arena.capacity == 65536      # 16384 -> 32768 -> 65536
 
 

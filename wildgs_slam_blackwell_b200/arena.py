@@ -14,7 +14,8 @@ Here every leaf owns a SEGMENT of one flat buffer sized for `capacity` rows and 
     params / exp_avg / exp_avg_sq : three buffers with the SAME segment layout (and the gradient bucket of the mapping
                                     window, window.GradBucket(capacity=...), a fourth) -> one offset addresses a
                                     parameter, its gradient and its moments
-    append  (clone / split)       : rows written behind row P, zero moments and statistics, P += n   -- no allocation
+    append  (clone / split)       : rows written behind row P with zero moments, P += n, statistics of all rows
+                                    restart at zero (densification_postfix)                        -- no allocation
     prune                         : surviving rows gathered (one mask scan + one gather launch over all 21 tensors,
                                     compaction.compact_rows) and copied back to the front -- pointers unchanged
     capacity class exceeded       : buffers of the next class (power of two) are allocated once and the rows move over;
@@ -160,10 +161,13 @@ class GaussianArena:
     @torch.no_grad()
     def append(self, rows: Dict[str, torch.Tensor]):
         """densification_postfix + cat_tensors_to_optimizer (gaussian_model.py:566-644): the new Gaussians' rows go
-        behind row P; their Adam moments and densification statistics start at zero.  Returns True if the capacity
-        class changed."""
+        behind row P and their Adam moments start at zero; the densification statistics of ALL rows restart at zero,
+        as the reference re-creates xyz_gradient_accum, denom and max_radii2D after every densify (:635-637), also when
+        nothing was added.  A WindowTrainer feeding add_window_statistics keeps a running maximum of its own:
+        trainer.reset_statistics() goes with this call.  Returns True if the capacity class changed."""
         n = int(next(iter(rows.values())).shape[0])
         if n == 0:
+            self.reset_statistics()
             return False
         self._sync_moments()
         grew = self.reserve(self.P + n)
@@ -172,11 +176,17 @@ class GaussianArena:
             self._seg(self._param, k, n, start=P).copy_(rows[k].detach().reshape(-1))
             self._seg(self._m, k, n, start=P).zero_()
             self._seg(self._v, k, n, start=P).zero_()
-        for s in self.STATS:
-            self._stats[s][P:P + n].zero_()
         self.P = P + n
+        self.reset_statistics()
         self._refresh()
         return grew
+
+    @torch.no_grad()
+    def reset_statistics(self):
+        """xyz_gradient_accum, denom, max_radii2D <- 0 for every row: a new densification interval begins
+        (gaussian_model.py:635-637)."""
+        for s in self.STATS:
+            self._stats[s][:self.P].zero_()
 
     @torch.no_grad()
     def prune(self, remove_mask: torch.Tensor):

@@ -344,6 +344,16 @@ class WindowTrainer:
         from . import rasterizer
         return rasterizer.densification_stats(self.grad_accum, self.denom, self.max_radii)
 
+    @torch.no_grad()
+    def reset_statistics(self):
+        """Start a new densification interval: the running screen-space radius maximum (and the window sums, which
+        zero_grads clears anyway) return to zero -- densification_postfix re-creates max_radii2D as zeros after every
+        densify (gaussian_model.py:635-637); call it with GaussianArena.append / reset_statistics."""
+        if self._stats:
+            self.max_radii.zero_()
+            self.grad_accum.zero_()
+            self.denom.zero_()
+
     def reduce_max_radii(self):
         """max over the ranks of the running screen-space radius (GaussianModel.max_radii2D's update, mapper.py:1176-1179)"""
         if self.world > 1:
