@@ -173,3 +173,31 @@ def test_scoped_contexts_are_per_thread_on_the_forward_side():
         other = rasterizer.grad_sink({})
         assert rasterizer.grad_sink.current_for_backward(other) is other    # the forward's binding wins
     assert rasterizer.grad_sink.current_for_backward(None) is None
+
+
+def test_backward_only_scope_refuses_to_guess_between_threads():
+    """Two threads each hold a grad_sink and a backward arrives whose forward ran outside both: the autograd worker
+    cannot know whose it is.  It used to take the most recently entered one (silently another thread's buffers); it
+    raises now.  Nesting on ONE thread stays legal (innermost wins), and a forward-bound instance is never ambiguous."""
+    import threading
+    errors, ready, done = [], threading.Barrier(3), threading.Event()
+
+    def holder():
+        with rasterizer.grad_sink({}):
+            ready.wait()
+            done.wait()
+
+    ts = [threading.Thread(target=holder) for _ in range(2)]
+    [t.start() for t in ts]
+    ready.wait()
+    try:
+        with pytest.raises(RuntimeError, match="several threads"):
+            rasterizer.grad_sink.current_for_backward(None)
+        bound = rasterizer.grad_sink({})
+        assert rasterizer.grad_sink.current_for_backward(bound) is bound
+    finally:
+        done.set()
+        [t.join() for t in ts]
+    with rasterizer.grad_sink({}) as outer, rasterizer.grad_sink({}) as inner:
+        assert rasterizer.grad_sink.current_for_backward(None) is inner
+    assert rasterizer.grad_sink.current_for_backward(None) is None and not errors

@@ -56,6 +56,7 @@ def test_capacity_overflow_retries_and_matches_oracle():
     o = cpu_oracle.forward_backward(g, cams[0], cots[0], export=True)
     assert int(o["num_rendered"]) > max(4 * 3000, 1 << 16)
     rasterizer._capacity_hint.clear()
+    rasterizer._capacity_ratio.clear()
     ours = util.run_ours(g, cams[0], cots[0])
     assert int(ours["num_rendered"]) == int(o["num_rendered"])
     np.testing.assert_array_equal(ours["radii"], o["radii"])

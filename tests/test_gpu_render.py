@@ -256,12 +256,14 @@ def test_sticky_overflow_record_covers_every_no_wait_forward():
     mk = lambda gg: [util.to_dev(gg[k], DEV) for k in ("means3D", "sh")] + [torch.Tensor([])] + \
         [util.to_dev(gg[k], DEV) for k in ("opacities", "scales", "rotations")] + [torch.Tensor([]), s]
     rasterizer._capacity_hint.clear()
+    rasterizer._capacity_ratio.clear()
     rasterizer._capacity_floor.clear()
     graph.overflow_status(DEV, clear=True)
     ref = rasterizer.forward_raw(*mk(big))                   # blocking forward: grows and retries
     R_big = ref[-1].num_rendered
     assert R_big > max(4 * P, 1 << 16)
     rasterizer._capacity_hint.clear()
+    rasterizer._capacity_ratio.clear()
     with graph.async_forward(DEV):
         with graph.async_forward(DEV):                        # nests: the inner exit must not switch the mode off
             pass
@@ -283,3 +285,83 @@ def test_sticky_overflow_record_covers_every_no_wait_forward():
     assert graph.check_overflow(DEV) == R_big
     assert torch.equal(again[0], ref[0])
     rasterizer._capacity_floor.clear()
+
+
+def test_backward_of_an_overflowed_no_wait_forward_is_all_zero_and_counts_no_observation():
+    """The other half of the overflow contract: the backward of a forward that rendered the background only leaves zero
+    gradients (dL_dtau included) and does NOT touch the fused densification statistics -- the view was not observed.
+    (An optimiser step already taken with that view missing cannot be undone by rerunning the forward.)"""
+    from wildgs_slam_blackwell_b200 import graph, rasterizer
+    W, H, P = 200, 120, 3000
+    cam_d = scenes.make_camera(W, H, 21, bg=(0.2, 0.4, 0.6))
+    g = scenes.make_gaussians(P, W, H, 0, 21, cam_d)
+    big = dict(g, scales=g["scales"] * 12.0)
+    s = util.settings_from_cam(cam_d, 0, DEV)
+    leaves = {k: util.to_dev(big[k], DEV).requires_grad_(True) for k in ("means3D", "sh", "opacities", "scales", "rotations")}
+    m2 = torch.zeros(P, 3, device=DEV, requires_grad=True)
+    theta = torch.zeros(3, device=DEV, requires_grad=True)
+    rho = torch.zeros(3, device=DEV, requires_grad=True)
+    acc = torch.full((P, 1), 3.0, device=DEV)
+    den = torch.full((P, 1), 5.0, device=DEV)
+    mx = torch.full((P,), 7.0, device=DEV)
+    rasterizer._capacity_hint.clear()
+    rasterizer._capacity_ratio.clear()
+    rasterizer._capacity_floor.clear()
+    graph.overflow_status(DEV, clear=True)
+    rast = rasterizer.GaussianRasterizer(s)
+    with graph.async_forward(DEV), rasterizer.densification_stats(acc, den, mx):
+        color, radii, depth, opacity, n_touched = rast(leaves["means3D"], m2, leaves["opacities"], shs=leaves["sh"],
+                                                       scales=leaves["scales"], rotations=leaves["rotations"],
+                                                       theta=theta, rho=rho)
+        (color.sum() + depth.sum() + opacity.sum()).backward()
+    with pytest.raises(RuntimeError, match="instance capacity exceeded"):
+        graph.check_overflow(DEV)
+    assert (radii > 0).any()                                 # Gaussians were visible: only the overflow keeps them out
+    for k, t in leaves.items():
+        assert t.grad is not None and not t.grad.any(), k
+    assert not m2.grad.any() and not theta.grad.any() and not rho.grad.any()
+    assert torch.all(acc == 3.0) and torch.all(den == 5.0) and torch.all(mx == 7.0)
+    # the same view with room: gradients flow and the statistics move
+    for t in list(leaves.values()) + [m2, theta, rho]:
+        t.grad = None
+    with rasterizer.densification_stats(acc, den, mx):
+        color, radii, depth, opacity, n_touched = rast(leaves["means3D"], m2, leaves["opacities"], shs=leaves["sh"],
+                                                       scales=leaves["scales"], rotations=leaves["rotations"],
+                                                       theta=theta, rho=rho)
+        (color.sum() + depth.sum() + opacity.sum()).backward()
+    assert leaves["means3D"].grad.any() and theta.grad.any() and float(den.max()) == 6.0 and float(mx.max()) > 7.0
+    rasterizer._capacity_floor.clear()
+    rasterizer._capacity_hint.clear()
+    rasterizer._capacity_ratio.clear()
+
+
+def test_capacity_carries_over_when_the_row_count_changes():
+    """A densify / prune changes P.  The instances-per-Gaussian ratio learned by a blocking forward at this resolution
+    sizes the first forward at the new P, so a no-wait forward there fits instead of rendering background only."""
+    from wildgs_slam_blackwell_b200 import graph, rasterizer
+    W, H, P = 200, 120, 3000
+    cam_d = scenes.make_camera(W, H, 21, bg=(0.2, 0.4, 0.6))
+    g = scenes.make_gaussians(P, W, H, 0, 21, cam_d)
+    big = dict(g, scales=g["scales"] * 12.0)                 # R >> max(4 P, 65536)
+    s = util.settings_from_cam(cam_d, 0, DEV)
+    mk = lambda gg, n: [util.to_dev(gg[k][:n], DEV) for k in ("means3D", "sh")] + [torch.Tensor([])] + \
+        [util.to_dev(gg[k][:n], DEV) for k in ("opacities", "scales", "rotations")] + [torch.Tensor([]), s]
+    rasterizer._capacity_hint.clear()
+    rasterizer._capacity_ratio.clear()
+    rasterizer._capacity_floor.clear()
+    graph.overflow_status(DEV, clear=True)
+    ref = rasterizer.forward_raw(*mk(big, P - 200))          # blocking: learns the ratio at P - 200 rows
+    assert ref[-1].num_rendered > max(4 * P, 1 << 16)
+    with graph.async_forward(DEV):
+        out = rasterizer.forward_raw(*mk(big, P))            # another row count, no hint of its own
+    n = graph.check_overflow(DEV)                            # does not raise: the carried capacity was enough
+    assert n > ref[-1].num_rendered
+    want = rasterizer.forward_raw(*mk(big, P))
+    assert torch.equal(out[0], want[0])
+    for i in range(100):                                     # the table stays bounded
+        rasterizer._capacity_hint[(0, 1, 1, i)] = 1
+        rasterizer._capacity_hint.move_to_end((0, 1, 1, i))
+    rasterizer.forward_raw(*mk(g, P))
+    assert len(rasterizer._capacity_hint) <= rasterizer._HINT_KEEP
+    rasterizer._capacity_hint.clear()
+    rasterizer._capacity_ratio.clear()

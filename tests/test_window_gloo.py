@@ -320,3 +320,23 @@ def test_capacity_classes_are_powers_of_two_with_a_floor():
     # BASELINE config 5's schedule enters five classes
     sched = [int(round(100_000 * 20 ** (s / 39))) for s in range(40)]
     assert len({capacity_class(p) for p in sched}) == 5
+
+
+def test_rounding_pad_behind_the_used_rows_is_zero_after_a_prune():
+    """The exchange moves whole 4-float groups, so up to 3 floats behind row P of every segment ride along.  After a prune
+    they held a dead row's gradients and were summed over the ranks on every step: retarget() zeroes them, zero_grads() /
+    zero_stats() clear the padded length, and the floats in the exchanged segments are exactly the used rows."""
+    from wildgs_slam_blackwell_b200.window import GradBucket
+    mk = lambda P: {"xyz": torch.zeros(P, 3), "opacity": torch.zeros(P, 1)}
+    b = GradBucket(mk(11), capacity=16, stat_floats=22, side_floats=8)
+    b._all.fill_(9.0)                                  # gradients, statistics and side block of a step at 11 rows
+    b.retarget(mk(6))                                  # prune: 6 rows; 6*3 = 18 -> pad 18..19, 6*1 -> pad 6..7
+    for (o, n), used in zip(b._segments[:4], (18, 6, 6, 6)):
+        seg = b._all[o:o + n]
+        assert n == (used + 3) // 4 * 4 and torch.all(seg[:used] == 9.0) and not seg[used:].any()
+    b._all.fill_(9.0)
+    b.zero_grads()
+    b.zero_stats()
+    for o, n in b._segments[:4]:
+        assert not b._all[o:o + n].any()
+    assert torch.all(b.side == 9.0)                    # (the side block is the trainer's to clear)

@@ -331,6 +331,7 @@ int wgs_backward(WgsContext* ctx, const WgsBackwardArgs* a, void* cuda_stream) {
     pb.dL_drotations = a->dL_drotations; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dtau = a->dL_dtau;
     pb.act = a->activations; pb.sh_rest = use_sh ? a->sh_rest : nullptr; pb.dL_dsh_rest = a->dL_dsh_rest;
     pb.stat_grad_accum = a->stat_grad_accum; pb.stat_denom = a->stat_denom; pb.stat_max_radii = a->stat_max_radii;
+    pb.misc = tile.misc;
     if ((pb.stat_grad_accum || pb.stat_denom || pb.stat_max_radii) && (row0 != 0 || row1 != gy)) {
         set_err("wgs_backward: densification statistics need a whole-image backward (the gradient norm is per view)", cudaSuccess);
         return WGS_ERR_INVALID_ARGUMENT;

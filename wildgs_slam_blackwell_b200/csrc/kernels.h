@@ -60,6 +60,7 @@ struct PreBwdParams {
     const float* sh_rest;
     float* dL_dsh_rest;
     float *stat_grad_accum, *stat_denom, *stat_max_radii;   // fused densification statistics (may be null)
+    const uint32_t* misc;      // the forward's TileView::misc: statistics are skipped when MISC_OVERFLOW is set
     float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
     const float *means3D, *sh, *colors_precomp, *scales, *rotations, *cov3D_precomp;
     const float *viewmatrix, *projmatrix, *projmatrix_raw, *campos;

@@ -68,6 +68,10 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
     const int accm = p.accumulate;
     __shared__ float s_part[WGS_PRE_BWD_THREADS / 32][6];   // pose partials of the block's warps, summed over its chunks
     if ((threadIdx.x & 31) < 6) s_part[threadIdx.x >> 5][threadIdx.x & 31] = 0.f;   // (each warp only touches its own row)
+    __syncwarp();   // lanes 0-5 wrote the row, lane 0 read-modify-writes it below
+    // A forward that overflowed its instance capacity (no-wait mode) rendered the background only: its backward has
+    // zero gradients, and the view must not count as an observation in the densification statistics either.
+    const bool stats_on = (p.stat_grad_accum || p.stat_denom || p.stat_max_radii) && p.misc[MISC_OVERFLOW] == 0;
     // A block walks chunks of WGS_PRE_BWD_THREADS Gaussians, chunk = blockIdx.x, + gridDim.x, ... (the grid is sized to
     // the SMs, launch_preprocess_bwd), so the block-level epilogue (pose partials, fence, ticket atomic) is paid once per
     // block.  STAGED: a thread works on its own Gaussian of the chunk (the SH rows of a warp must stay one contiguous
@@ -452,7 +456,7 @@ __global__ void __launch_bounds__(WGS_PRE_BWD_THREADS, 768 / WGS_PRE_BWD_THREADS
 #pragma unroll
             for (int k = 0; k < 4; k++) drot[k] = (drot[k] - q4[k] * qd) * rcpf(qn);
         }
-        if (live && rad > 0) {   // mapper.py:1176-1182 + add_densification_stats (gaussian_model.py:745-749), visibility = radii > 0
+        if (live && rad > 0 && stats_on) {   // mapper.py:1176-1182 + add_densification_stats (gaussian_model.py:745-749), visibility = radii > 0
             const float gn = sqrtf(dm2x * dm2x + dm2y * dm2y);
             if (accm == 2) {   // views on several streams update the statistics concurrently
                 if (p.stat_grad_accum) atomicAdd(p.stat_grad_accum + idx, gn);

@@ -38,7 +38,9 @@ def cpu_deep_copy_tuple(input_tuple):
 
 
 # ---- host state: instance-capacity hint per (device, W, H, P) and the self-cleaning gradient workspaces ----
-_capacity_hint = {}
+_capacity_hint = collections.OrderedDict()      # (device, W, H, P) -> instances to reserve; least recently used beyond _HINT_KEEP go
+_capacity_ratio = {}        # (device, W, H) -> instances per Gaussian of the last forward that read its count back
+_HINT_KEEP = 64
 _capacity_floor = {}        # device -> instance count a no-wait forward was seen to need (graph.check_overflow)
 # (device, stream, P) -> accumulator workspace.  One per STREAM: two backwards in flight on two streams of a device
 # never share accumulators / the pose ticket; one per P: a masked render or a densified model next to the full one
@@ -133,7 +135,10 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
         n_touched = torch.empty((P,), dtype=torch.int32, device=device)
 
         key = (device.index, W, H, P)
-        cap = max(_capacity_hint.get(key, 0), _capacity_floor.get(device.index, 0), 4 * P, 1 << 16)
+        # A densify or prune changes P: the instances-per-Gaussian ratio seen at this resolution carries the learned
+        # size over to the new row count, so a no-wait forward at the new P does not start from the 4 P guess.
+        carried = int(_capacity_ratio.get(key[:3], 0.0) * P * 1.5)
+        cap = max(_capacity_hint.get(key, 0), carried, _capacity_floor.get(device.index, 0), 4 * P, 1 << 16)
         st = ForwardState()
         a = _lib.ForwardArgs()
         a.P, a.sh_degree, a.M, a.width, a.height = P, int(s.sh_degree), M, W, H
@@ -170,6 +175,12 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
             old = _capacity_hint.get(key, 0)
             if not (R.value * 1.2 <= old <= R.value * 4):
                 _capacity_hint[key] = int(R.value * 1.5)
+            if key in _capacity_hint:
+                _capacity_hint.move_to_end(key)
+                while len(_capacity_hint) > _HINT_KEEP:
+                    _capacity_hint.popitem(last=False)
+            if P > 0 and strip is None:
+                _capacity_ratio[key[:3]] = R.value / P
         st.args = a
         st.num_rendered = int(R.value)
         # what is active around the FORWARD is bound to its backward (the backward runs on autograd's worker thread)
@@ -234,6 +245,7 @@ class _Scoped:
 
     def __enter__(self):
         self._token = self._var.set(self)
+        self._thread = threading.get_ident()
         self._stack.append(self)
         return self
 
@@ -249,10 +261,19 @@ class _Scoped:
 
     @classmethod
     def current_for_backward(cls, bound):
-        """`bound` (what the forward saw) wins; else the innermost instance entered anywhere in the process"""
+        """`bound` (what the forward saw) wins; else the innermost instance entered anywhere in the process -- unless
+        instances entered by different threads are active: the worker thread that runs this backward cannot tell whose
+        it is, and guessing would hand one thread's buffers to another thread's backward, so that raises."""
         if bound is not None:
             return bound
-        return cls._stack[-1] if cls._stack else None
+        stack = list(cls._stack)
+        if not stack:
+            return None
+        if len({inst._thread for inst in stack}) > 1:
+            raise RuntimeError(f"{cls.__name__}: instances entered by several threads are active and this backward's "
+                               f"forward ran outside all of them; issue the forward inside `with {cls.__name__}(...)` "
+                               "(that binds it to its backward), or run one backward-only block at a time")
+        return stack[-1]
 
 
 class tile_rows(_Scoped):

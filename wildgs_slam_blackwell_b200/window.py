@@ -177,7 +177,8 @@ class GradBucket:
             self.stat_views = (self.stats[:P], self.stats[P:2 * P]) if self._with_stats else None
             self._segments = None
         else:
-            self.flat = self._all[:self._grad_floats]      # (includes the unused rows of every segment)
+            self.flat = self._all[:self._grad_floats]      # (includes the unused rows of every segment: zero up to the
+                                                           #  4-float pad, stale beyond it -- reduce over `views`, not `flat`)
             r4 = lambda n: (n + 3) // 4 * 4
             self._segments = [(self.offsets[k], r4(P * self.widths[k])) for k in self.names]
             if self._with_stats:
@@ -189,6 +190,19 @@ class GradBucket:
             self.stats = self._all[self._stat_off:self._side_off]
             if self.side.numel():
                 self._segments.append((self._side_off, r4(self.side.numel())))
+            # The exchange works on whole 4-float groups, so up to 3 floats behind row P of every segment are summed
+            # over the ranks on every step.  After a prune they would hold a dead row's gradients (and grow by the
+            # world size per step): zero them here, and let zero_grads / zero_stats clear the padded length.
+            n_leaf = len(self.names)
+            self._zero_views = [self._all[o:o + n] for o, n in self._segments[:n_leaf]]
+            self._zero_stat_views = [self._all[o:o + n] for o, n in self._segments[n_leaf:n_leaf + 2]] if self._with_stats else []
+            with torch.no_grad():
+                for (o, n), k in zip(self._segments[:n_leaf], self.names):
+                    if n > P * self.widths[k]:
+                        self._all[o + P * self.widths[k]:o + n].zero_()
+                for o, n in (self._segments[n_leaf:n_leaf + 2] if self._with_stats else []):
+                    if n > P:
+                        self._all[o + P:o + n].zero_()
 
     @property
     def device(self):
@@ -206,12 +220,12 @@ class GradBucket:
         if self.capacity is None:
             self.flat.zero_()
         else:
-            for v in self.views.values():
+            for v in self._zero_views:       # the P rows and the 4-float rounding pad behind them
                 v.zero_()
 
     def zero_stats(self):
         if self.stat_views is not None:
-            for v in self.stat_views:
+            for v in (self.stat_views if self.capacity is None else self._zero_stat_views):
                 v.zero_()
 
     def install(self, zero=True):
