@@ -504,9 +504,15 @@ def window_entry(a, dev, world, rank, flush):
                         plan="auto", streams=2, use_graph=os.environ.get("WGS_ALLREDUCE", "auto") != "nccl")
     ms, out = wl.time(a.window_steps, max(a.warmup, 3), flush)
     par = wl.parity() if world > 1 else None
+    desc = wl.describe(out)
+    # the same step ending like a mapping iteration (src/mapper.py:1212-1219): optimizer.step() inside the captured step
+    wl.enable_optimizer()
+    ms_opt, _ = wl.time(a.window_steps, max(a.warmup, 3), flush)
+    with_opt = {"optimizer": "replicated fused Adam over the 5 leaves (1 launch, inside the captured step) on the exchanged bucket",
+                "ms_per_step": round(ms_opt, 4), "value": round(1e3 / ms_opt, 3)}
     # (the long description first, the numbers last: the driver's record keeps the END of the line)
-    entry = {"config": wl.describe(out), "metric": "mapping-window iterations/sec (config 3)", "scaling": "strong",
-             "steps": a.window_steps, "overflow_checked": True, "unit": "window steps/s",
+    entry = {"config": desc, "metric": "mapping-window iterations/sec (config 3)", "scaling": "strong",
+             "steps": a.window_steps, "overflow_checked": True, "with_optimizer": with_opt, "unit": "window steps/s",
              "frames_per_s": round(wl.n_views * 1e3 / ms, 2), "ms_per_step": round(ms, 4), "value": round(1e3 / ms, 3)}
     del wl
     torch.cuda.empty_cache()
@@ -631,7 +637,12 @@ def main():
 
     bucket_floats = wl.bucket_floats
     peer_desc = ("peer-memory allreduce kernel (" + ("NVLS multimem" if wl.peer.multicast else "P2P two-shot") + ")") if wl.peer is not None else "NCCL allreduce"
-    window = parity = None
+    window = parity = checks = None
+    if a.impl == "ours" and world > 1:
+        # the 2-GPU tests of tests/test_gpu_peer.py in a form that runs here, where the ranks exist: the exchange kernel
+        # (both paths) against ncclAllReduce, sharded against replicated Adam across an append and a prune
+        from wildgs_slam_blackwell_b200.selfcheck import multi_gpu_checks
+        checks = multi_gpu_checks(dev)
     if not a.no_window and a.workload == "config2":
         del wl                      # free the headline workload's buffers (and its symmetric bucket) first
         torch.cuda.empty_cache()
@@ -681,10 +692,15 @@ def main():
             line["window"] = window
         if parity:
             line["multi_gpu_parity"] = parity
+        if checks:
+            line["multi_gpu_checks"] = checks
         print(json.dumps(line), flush=True)
     rc = 0
     if rank == 0 and parity is not None and not parity.get("ok", False):
         sys.stderr.write(f"bench.py: multi-GPU gradient parity FAILED: {json.dumps(parity)}\n")
+        rc = 3
+    if rank == 0 and checks is not None and not checks.get("ok", False):
+        sys.stderr.write(f"bench.py: multi-GPU self-checks FAILED: {json.dumps(checks)}\n")
         rc = 3
     if world > 1:
         dist.barrier()

@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--peer", default="auto", choices=["off", "auto", "nvls", "p2p"])
     ap.add_argument("--sharded", action="store_true", help="reduce-scatter + Adam on 1/world + allgather of the parameters")
     ap.add_argument("--streams", type=int, default=2)
+    ap.add_argument("--reserve", action="store_true", help="allocate the final capacity class once, before the run")
     ap.add_argument("--eager", action="store_true")
     ap.add_argument("--small", action="store_true", help="10 k -> 200 k over 12 steps (smoke)")
     ap.add_argument("--profile-last", action="store_true", help="cudaProfilerStart before the timed steps of the last stage")
@@ -51,7 +52,7 @@ def main():
     if a.stop_at:
         from config5_workload import schedule
         kw["sched"] = schedule()[:a.stop_at]
-    wl = Config5Workload(dev, peer=a.peer, streams=a.streams, sharded=a.sharded, use_graph=not a.eager, **kw)
+    wl = Config5Workload(dev, peer=a.peer, streams=a.streams, sharded=a.sharded, use_graph=not a.eager, reserve=a.reserve, **kw)
     recs = wl.run(reps=a.reps, profile_last=a.profile_last)
     if rank == 0:
         stages = [recs[i] for i in sorted({0, len(recs) // 4, len(recs) // 2, 3 * len(recs) // 4, len(recs) - 1})]
@@ -62,6 +63,14 @@ def main():
             "stages": [{k: r[k] for k in ("step", "rows", "capacity", "ms_per_window_step", "steps_per_s", "densify_ms")} for r in stages],
             "all_steps_ms": [r["ms_per_window_step"] for r in recs], "rows": [r["rows"] for r in recs],
             "densify_ms": [r["densify_ms"] for r in recs], "loss_sums": [r["loss_sum"] for r in recs],
+            # everything the schedule costs, one window step per growth stage: the densify / prune (incl. any capacity-class
+            # change: allocation + peer rendezvous), the first step at the new row count (eager pass + graph capture, host
+            # wall clock), and the replayed step -- max over ranks each
+            "totals_ms": {"window_steps": round(sum(r["ms_per_window_step"] for r in recs), 2),
+                          "densify": round(sum(r["densify_ms"] for r in recs), 2),
+                          "first_steps": round(sum(r["first_step_ms"] for r in recs), 2),
+                          "all_in": round(sum(r["ms_per_window_step"] + r["densify_ms"] + r["first_step_ms"] for r in recs), 2)},
+            "first_step_ms": [r["first_step_ms"] for r in recs], "reserved_capacity": bool(a.reserve),
             "capacity_classes_entered": wl.arena.allocations, "bucket_allocations": wl.bucket_allocations,
             "growth_steps": len(recs),
             "config": {"optimizer": "sharded Adam (reduce-scatter, 1/world slice per rank, parameter allgather)" if wl.sharded

@@ -23,6 +23,7 @@ Identical on every rank without communication: parameters are replicated bit for
 functions of them (topk / kthvalue on the device) and the jitter comes from a seeded device generator.
 """
 import math
+import time
 import os
 import sys
 
@@ -50,7 +51,7 @@ def schedule(p0=100_000, p1=2_000_000, steps=40):
 class Config5Workload:
     def __init__(self, dev, p0=100_000, p1=2_000_000, steps=40, n_views=16, W=640, H=480, peer="auto", plan="balanced",
                  streams=2, sharded=False, prune_every=10, prune_frac=0.05, use_graph=True, seed=1005, emulate=None,
-                 sched=None):
+                 sched=None, reserve=False):
         self.dev, self.W, self.H, self.n_views = dev, W, H, n_views
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
@@ -69,8 +70,10 @@ class Config5Workload:
         leaves = {"xyz": t(g["means3D"]), "f_dc": t(g["sh"][:, :1]), "opacity": t(np.log(o / (1 - o))),
                   "scaling": t(np.log(g["scales"])), "rotation": t(g["rotations"])}
         group = dist.group.WORLD if self.peer != "off" else None
+        # reserve: the final capacity class is allocated (and, in peer memory, rendezvoused) ONCE, before the run -- 2 M rows
+        # x 14 floats x 4 buffers is 450 MB of 180 GB -- so no growth step pays an allocation or a symmetric-memory exchange
         self.arena = GaussianArena(leaves, group=group, peer_mode=self.peer if self.peer != "off" else "auto",
-                                   capturable=True)
+                                   capturable=True, capacity=max(self.sched) if reserve else None)
         self.trainer = WindowTrainer(self.arena.params, sink_names=SINK_NAMES, peer=self.peer != "off",
                                      peer_mode=self.peer if self.peer != "off" else "auto", densify_stats=True,
                                      streams=streams, capacity=self.arena.capacity, emulate=emulate,
@@ -91,6 +94,7 @@ class Config5Workload:
         self.gen.manual_seed(seed)
         self.tile_rows = (H + 15) // 16
         self._it = None
+        self._captured_before = False
         self._means2D = None
 
     # ---- one window step (+ optimiser) ----
@@ -128,8 +132,12 @@ class Config5Workload:
             with graph.async_forward(self.dev):
                 return self._step()
         if self._it is None:
-            self._step()                                # eager once: sizes the instance capacity at this row count
-            self._it = graph.CapturedIteration(self._step, self.dev, warmup=1)
+            # The capture's own warm-up pass is the eager (blocking) step that sizes the instance capacity at this row
+            # count; the arena's leaves are new views after every grow_to and are first stepped there, on the capture's
+            # side stream, so no full garbage collection is needed to drop accumulators bound to another stream
+            # (profiles/r03d_capture_breakdown.json: eager pass 12 ms + gc 22-34 ms of the ~90 ms a first step cost).
+            self._it = graph.CapturedIteration(self._step, self.dev, warmup=1, collect=0 if self._captured_before else 2)
+            self._captured_before = True
         return self._it.replay()
 
     def check(self):
@@ -174,7 +182,13 @@ class Config5Workload:
             e0.record()
             self.grow_to(rows, prune=(s > 0 and s % self.prune_every == 0))
             e1.record()
-            self.step()                                 # untimed (capture happens here)
+            torch.cuda.synchronize()
+            w0 = time.perf_counter()
+            self.step()                                 # not in ms_per_window_step: eager pass + graph capture at this row count
+            torch.cuda.synchronize()
+            first_ms = torch.tensor([1e3 * (time.perf_counter() - w0), e0.elapsed_time(e1)], dtype=torch.float64, device=self.dev)
+            if self.world > 1:
+                dist.all_reduce(first_ms, op=dist.ReduceOp.MAX)
             if profile_last and s == len(self.sched) - 1:
                 torch.cuda.synchronize()
                 torch.cuda.profiler.start()             # ncu --profile-from-start off: only the last stage's steps
@@ -192,7 +206,8 @@ class Config5Workload:
             if self.world > 1:
                 dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             rec = {"step": s, "rows": self.arena.P, "capacity": self.arena.capacity, "ms_per_window_step": round(float(ms), 4),
-                   "steps_per_s": round(1e3 / float(ms), 2), "densify_ms": round(e0.elapsed_time(e1), 3),
+                   "steps_per_s": round(1e3 / float(ms), 2), "densify_ms": round(float(first_ms[1]), 3),
+                   "first_step_ms": round(float(first_ms[0]), 3),
                    "loss_sum": round(float(losses.sum()), 6)}
             records.append(rec)
             if log and self.rank == 0:

@@ -67,6 +67,19 @@ class WindowWorkload:
         self.tile_rows = (self.H + 15) // 16
         self._it = None
         self._eager_out = None
+        self.opt = None
+
+    def enable_optimizer(self, lrs=None):
+        """From here on a step ends like the reference's mapping iteration (src/mapper.py:1212-1219): optimizer.step() on
+        the window's summed gradients -- replicated fused Adam (adam.FusedAdam, capturable: ONE launch over the five
+        leaves, inside the captured step), every rank updating all rows from the exchanged bucket.  Learning rates: the
+        reference's (configs/wildgs_slam.yaml opt_params) scaled by 1e-2 so that the synthetic scene stays where the
+        instance capacities were sized over a timed run; the work per step does not depend on them."""
+        from wildgs_slam_blackwell_b200.adam import FusedAdam
+        lrs = lrs or {"means3D": 1.6e-6, "sh": 2.5e-5, "opacities": 5e-4, "scales": 1e-5, "rotations": 1e-5}
+        self.opt = FusedAdam([{"params": [self.params[k]], "lr": lrs[k], "name": k} for k in LEAVES], lr=0.0, eps=1e-15,
+                             capturable=True)
+        self._it = None
 
     # ---- one window step ----
     def render_loss(self, v):
@@ -99,12 +112,22 @@ class WindowWorkload:
         return self.trainer.step(self.n_views, self.render_loss, tile_rows=self.tile_rows,
                                  plan=self.plan if plan is None else plan)
 
+    def full_step(self):
+        """eager_step + (after enable_optimizer) the optimiser step on the exchanged gradients"""
+        out = self.eager_step()
+        if self.opt is not None:
+            for k in LEAVES:                               # (sink mode leaves .grad unset: the bucket holds the gradient)
+                if self.params[k].grad is None:
+                    self.params[k].grad = self.trainer.bucket.views[k]
+            self.opt.step()
+        return out
+
     def step(self):
         if not self.use_graph:
-            return self.eager_step()
+            return self.full_step()
         if self._it is None:
-            self._eager_out = self.eager_step()            # also sizes the instance capacity per view
-            self._it = graph.CapturedIteration(lambda: self.eager_step()["losses"], self.dev, warmup=2)
+            self._eager_out = self.full_step()             # also sizes the instance capacity per view
+            self._it = graph.CapturedIteration(lambda: self.full_step()["losses"], self.dev, warmup=2)
         self._it.replay()
         return self._eager_out
 

@@ -121,7 +121,14 @@ class CapturedIteration:
         it.check()                      # covers all 100 replays (sticky overflow record)
     """
 
-    def __init__(self, step, device, warmup=3):
+    def __init__(self, step, device, warmup=3, pool=None, collect=2):
+        """collect: generation handed to gc.collect before the warm-up (see below); a full collection walks every Python
+        object of the process (20-35 ms beside a 2 M-row model, measured: profiles/r03d_capture_breakdown.json).  A loop
+        that re-captures over FRESH leaf tensors, never stepped on the default stream, has no stale accumulator to drop and
+        may pass 0 (young objects only) -- if it was wrong the capture fails loudly, it cannot record a wrong graph.
+        pool: a memory-pool handle (`previous.pool()`) to capture into instead of a fresh private pool -- for a loop that
+        RE-captures its step (the row count changed) and no longer replays the previous graph: the blocks that graph's
+        capture allocated are reused instead of paying cudaMalloc / cudaFree per capture."""
         import gc
         from . import rasterizer
         self.device = torch.device("cuda", _index(device))
@@ -129,7 +136,7 @@ class CapturedIteration:
         # it while any graph references it; drop dead graphs from earlier eager iterations so that the warm-up below
         # (on the side stream) creates fresh ones -- a live graph built on the default stream would make the captured
         # backward launch on that stream and invalidate the capture
-        gc.collect()
+        gc.collect(collect)
         side = torch.cuda.Stream(self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(side):       # eager warm-up: contexts, workspaces, capacity hint
@@ -139,11 +146,14 @@ class CapturedIteration:
         torch.cuda.synchronize(self.device)
         rasterizer.take_capture_pins()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        with torch.cuda.graph(self.graph, pool=pool):
             self.out = step()
         # the recorded kernels hold raw pointers into the gradient-accumulator workspaces: keep those alive as long
         # as the graph (the cache in rasterizer.py may evict them)
         self._pins = rasterizer.take_capture_pins()
+
+    def pool(self):
+        return self.graph.pool()
 
     def replay(self):
         self.graph.replay()
