@@ -340,3 +340,10 @@ def test_rounding_pad_behind_the_used_rows_is_zero_after_a_prune():
     for o, n in b._segments[:4]:
         assert not b._all[o:o + n].any()
     assert torch.all(b.side == 9.0)                    # (the side block is the trainer's to clear)
+
+
+def test_multi_gpu_checks_need_a_process_group():
+    """selfcheck.multi_gpu_checks is what `bench.py --gpus N` runs where the ranks exist; alone it refuses to pretend."""
+    from wildgs_slam_blackwell_b200 import selfcheck
+    with pytest.raises(RuntimeError, match="process group"):
+        selfcheck.multi_gpu_checks(torch.device("cpu"))
