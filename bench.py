@@ -510,6 +510,15 @@ def window_entry(a, dev, world, rank, flush):
     ms_opt, _ = wl.time(a.window_steps, max(a.warmup, 3), flush)
     with_opt = {"optimizer": "replicated fused Adam over the 5 leaves (1 launch, inside the captured step) on the exchanged bucket",
                 "ms_per_step": round(ms_opt, 4), "value": round(1e3 / ms_opt, 3)}
+    if world > 1 and wl.peer != "off":
+        # and with the SHARDED optimiser step: reduce-scatter -> Adam on the owned 1/world of the rows -> allgather
+        plan_used = wl.plan
+        wl.enable_optimizer(sharded=True)
+        wl.plan = plan_used
+        ms_sh, _ = wl.time(a.window_steps, max(a.warmup, 3), flush)
+        with_opt["sharded"] = {"optimizer": "reduce-scatter of the bucket, Adam on the rank's 1/world slice of the arena, "
+                                            "allgather of the updated parameters (peer kernels)",
+                               "ms_per_step": round(ms_sh, 4), "value": round(1e3 / ms_sh, 3)}
     # (the long description first, the numbers last: the driver's record keeps the END of the line)
     entry = {"config": desc, "metric": "mapping-window iterations/sec (config 3)", "scaling": "strong",
              "steps": a.window_steps, "overflow_checked": True, "with_optimizer": with_opt, "unit": "window steps/s",

@@ -48,6 +48,7 @@ class WindowWorkload:
         self.plan, self.use_graph, self.emulate, self.loss = plan, use_graph, emulate, loss
         if use_graph and self.world > 1 and self.peer == "off":
             raise SystemExit("a captured window step needs the peer exchange (an NCCL allreduce is not captured here)")
+        self.streams, self.sink = streams, sink
         self.trainer = WindowTrainer(self.params, sink_names=SINK_NAMES if sink else None, peer=self.peer != "off",
                                      peer_mode=self.peer if self.peer != "off" else "auto", streams=streams, emulate=emulate)
         self.means2D = torch.zeros(self.P, 3, device=dev, requires_grad=True)
@@ -67,9 +68,9 @@ class WindowWorkload:
         self.tile_rows = (self.H + 15) // 16
         self._it = None
         self._eager_out = None
-        self.opt = None
+        self.opt = self.arena = None
 
-    def enable_optimizer(self, lrs=None):
+    def enable_optimizer(self, lrs=None, sharded=False):
         """From here on a step ends like the reference's mapping iteration (src/mapper.py:1212-1219): optimizer.step() on
         the window's summed gradients -- replicated fused Adam (adam.FusedAdam, capturable: ONE launch over the five
         leaves, inside the captured step), every rank updating all rows from the exchanged bucket.  Learning rates: the
@@ -77,6 +78,22 @@ class WindowWorkload:
         instance capacities were sized over a timed run; the work per step does not depend on them."""
         from wildgs_slam_blackwell_b200.adam import FusedAdam
         lrs = lrs or {"means3D": 1.6e-6, "sh": 2.5e-5, "opacities": 5e-4, "scales": 1e-5, "rotations": 1e-5}
+        self._it, self.lrs = None, lrs
+        if sharded:
+            # SHARDED form (arena.GaussianArena.sharded_adam_step): the leaves move into an arena in peer memory, the
+            # window's exchange becomes a reduce-scatter, each rank runs Adam on the 1/world of the rows it owns and the
+            # updated rows return by an allgather -- the same bytes over NVLink as the one allreduce before, Adam's 28 B
+            # per element of HBM traffic divided by the world size.
+            if self.world < 2 or self.peer == "off" or self.emulate is not None or not self.sink:
+                raise SystemExit("the sharded optimiser step needs >= 2 ranks, the peer exchange and the gradient sink")
+            from wildgs_slam_blackwell_b200.arena import GaussianArena
+            self.arena = GaussianArena({k: self.params[k].detach() for k in LEAVES}, group=dist.group.WORLD,
+                                       peer_mode=self.peer, capturable=True)
+            self.params = self.arena.params
+            self.trainer = WindowTrainer(self.params, sink_names=SINK_NAMES, peer=True, peer_mode=self.peer,
+                                         streams=self.streams, capacity=self.arena.capacity, exchange="reduce_scatter")
+            self.opt = None
+            return
         self.opt = FusedAdam([{"params": [self.params[k]], "lr": lrs[k], "name": k} for k in LEAVES], lr=0.0, eps=1e-15,
                              capturable=True)
         self._it = None
@@ -115,6 +132,8 @@ class WindowWorkload:
     def full_step(self):
         """eager_step + (after enable_optimizer) the optimiser step on the exchanged gradients"""
         out = self.eager_step()
+        if self.arena is not None:
+            self.arena.sharded_adam_step(self.trainer.bucket, self.lrs)
         if self.opt is not None:
             for k in LEAVES:                               # (sink mode leaves .grad unset: the bucket holds the gradient)
                 if self.params[k].grad is None:
